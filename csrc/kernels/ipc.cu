@@ -1,0 +1,53 @@
+// Symmetric receive-arena plumbing: device allocation outside the torch caching allocator (so the
+// whole allocation can be exported), CUDA IPC handle export / import, and peer-access checks.
+//
+// Reference behaviour being replaced: one big registered memory region per process plus an rkey
+// exchanged in the RDMA-CM private data (src/DataNet/RDMAComm.cc:67-154,178-218,
+// src/DataNet/RDMAComm.h:35-39 connreq_data). Here the "registration" is a cudaMalloc'd arena whose IPC
+// handle is all-gathered through the torch process group once at start-up; after that every rank holds
+// a plain device pointer into every peer's arena and the transport is st.global over NVLink.
+#include "common.cuh"
+#include "../../include/uda_b200.h"
+#include <string.h>
+
+extern "C" int uda_dev_malloc(void** ptr, long long bytes) {
+    UDA_CUDA(cudaMalloc(ptr, (size_t)bytes));
+    return 0;
+}
+extern "C" int uda_dev_free(void* ptr) {
+    UDA_CUDA(cudaFree(ptr));
+    return 0;
+}
+extern "C" int uda_ipc_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
+extern "C" int uda_ipc_get_handle(void* ptr, void* handle_out) {
+    cudaIpcMemHandle_t h;
+    UDA_CUDA(cudaIpcGetMemHandle(&h, ptr));
+    memcpy(handle_out, &h, sizeof(h));
+    return 0;
+}
+extern "C" int uda_ipc_open_handle(const void* handle_in, void** ptr_out) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle_in, sizeof(h));
+    UDA_CUDA(cudaIpcOpenMemHandle(ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+extern "C" int uda_ipc_close_handle(void* ptr) {
+    UDA_CUDA(cudaIpcCloseMemHandle(ptr));
+    return 0;
+}
+extern "C" int uda_can_access_peer(int dev, int peer, int* out) {
+    UDA_CUDA(cudaDeviceCanAccessPeer(out, dev, peer));
+    return 0;
+}
+extern "C" int uda_memset_async(void* ptr, int value, long long bytes, cudaStream_t stream) {
+    UDA_CUDA(cudaMemsetAsync(ptr, value, (size_t)bytes, stream));
+    return 0;
+}
+extern "C" int uda_host_alloc_pinned(void** ptr, long long bytes) {
+    UDA_CUDA(cudaHostAlloc(ptr, (size_t)bytes, cudaHostAllocPortable));
+    return 0;
+}
+extern "C" int uda_host_free_pinned(void* ptr) {
+    UDA_CUDA(cudaFreeHost(ptr));
+    return 0;
+}

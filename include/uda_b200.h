@@ -1,0 +1,134 @@
+/* uda_b200 — C ABI of the sm_100a kernel library (libuda_kernels.so).
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on and returns 0 or a
+ * cudaError_t value (negative values are argument errors raised by this library, see UDA_E_*).
+ * Unless stated otherwise an entry point allocates nothing: scratch is passed in by the caller and
+ * its required size is returned by the matching *_scratch_bytes() function.
+ *
+ * Reference citations name the CPU code path of chaoyang223/UDA whose behaviour the kernel replaces.
+ */
+#ifndef UDA_B200_H
+#define UDA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __DRIVER_TYPES_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+#define UDA_E_INVALID (-1)   /* bad argument */
+#define UDA_E_TOO_LARGE (-2) /* size exceeds a documented maximum */
+
+/* 16-byte sort entry, compared as the 128-bit integer (w0:w1); see csrc/kernels/common.cuh. */
+typedef struct {
+    unsigned long long w0; /* key bytes 0..7 big-endian */
+    unsigned long long w1; /* key bytes 8..9 << 48 | run << 32 | record index in run */
+} UdaEntry;
+
+/* One sorted run (= one fetched map-output segment) as seen by the reducer-side kernels. */
+typedef struct {
+    const void* base;   /* first record of the run (device pointer, may be a peer/arena address) */
+    long long nrec;     /* records in the run */
+    long long out_off;  /* first entry of this run in the concatenated entry array */
+    unsigned run_id;    /* stable-order rank of the run (map index) */
+    unsigned idx0;      /* record index assigned to the first record */
+} UdaRunDesc;
+
+/* One contiguous copy of the fused shuffle: MOF partition segment -> peer receive arena. */
+typedef struct {
+    const void* src;              /* local MOF bytes (segment start) */
+    void* dst;                    /* destination in the (peer-mapped) receive arena */
+    long long bytes;              /* segment length (partLength) */
+    unsigned long long* flag;     /* landed-bytes counter in the destination rank's arena */
+} UdaPushDesc;
+
+/* ---- synthetic data + validation (no reference counterpart: Hadoop teragen/teravalidate,
+ *      scripts/regression/sortcountRunner.sh:123-241) ------------------------------------------ */
+int uda_teragen(void* out, long long n, unsigned long long seed, unsigned long long first_row, int framed,
+                int key_bits, cudaStream_t stream);
+int uda_validate_fixed(const void* recs, long long n, int stride, int key_off, unsigned long long* result3,
+                       cudaStream_t stream);
+
+/* ---- K3 key normalise (reference: src/Merger/CompareFunc.cc:70-113) ---------------------------- */
+int uda_extract_keys_fixed(const UdaRunDesc* runs_dev, int nruns, long long max_nrec, int stride, int key_off,
+                           int key_len, void* entries_out, cudaStream_t stream);
+int uda_extract_keys_var(const void* data, const long long* rec_off_dev, long long n, int key_kind, unsigned run_id,
+                         unsigned idx0, void* entries_out, unsigned* long_key_flag_dev, cudaStream_t stream);
+
+/* ---- K2 map-side LSD radix sort of entries (reference: Hadoop MapTask sort, implied by the sorted
+ *      MOFs consumed at src/Merger/MergeQueue.h:299-321) ------------------------------------------ */
+long long uda_radix_sort_scratch_bytes(long long n);
+/* Sorts by the top key_bytes (1..10) bytes of the 80-bit key prefix; stable. Result ends in `a`
+ * (b is the ping-pong buffer of the same size). */
+int uda_radix_sort_entries(void* a, void* b, long long n, int key_bytes, void* scratch, cudaStream_t stream);
+
+/* ---- K4 reducer-side k-way merge of sorted runs (reference: src/Merger/MergeQueue.h:126-321 heap +
+ *      src/Merger/StreamRW.cc:151-225 write_kv_to_stream hot loop) ------------------------------- */
+long long uda_merge_scratch_bytes(long long n, int nruns);
+/* entries: runs concatenated, run r = [run_off[r], run_off[r+1]); each run sorted. sorted_out gets all
+ * n entries in (key, run, index) order. nruns <= 4096, n < 2^32. */
+int uda_kway_merge_entries(const void* entries, const long long* run_off_dev, int nruns, long long n,
+                           void* sorted_out, void* scratch, cudaStream_t stream);
+/* synchronises the stream; out2_host = {oversize buckets, bisection iterations} of the last merge */
+int uda_merge_stats(const void* scratch, unsigned long long* out2_host, cudaStream_t stream);
+
+/* ---- merged-stream materialisation (reference: src/Merger/StreamRW.cc:184-201,216-218) ---------- */
+/* dst must be 16-byte aligned and hold n*stride (+2 if write_eof) bytes. run_base_dev[run] = device
+ * address of record 0 of that run; source buffers need 32 readable bytes before and after. */
+int uda_gather_fixed(const void* sorted_entries, long long n, const unsigned long long* run_base_dev, int stride,
+                     void* dst, int write_eof, cudaStream_t stream);
+int uda_gather_var_lengths(const void* sorted_entries, long long n, const unsigned long long* run_recoff_dev,
+                           unsigned* rec_len_out, cudaStream_t stream);
+int uda_gather_var(const void* sorted_entries, long long n, const unsigned long long* run_base_dev,
+                   const unsigned long long* run_recoff_dev, const unsigned long long* dst_off_dev, void* dst,
+                   cudaStream_t stream);
+
+/* ---- K1 fused shuffle push over peer memory (reference: src/DataNet/RDMAClient.cc:559-600 request,
+ *      src/MOFServer/IndexInfo.cc:237-335 chunk read, src/DataNet/RDMAServer.cc:537-631 write+ack,
+ *      :44-136 credits) --------------------------------------------------------------------------- */
+long long uda_push_scratch_bytes(int nseg);
+int uda_shuffle_push(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, cudaStream_t stream);
+int uda_wait_flags(const unsigned long long* flags_dev, const unsigned long long* expect_dev, int n,
+                   unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream);
+int uda_barrier_all(unsigned long long* const* pads_dev, int rank, int world, unsigned long long epoch,
+                    unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream);
+
+/* ---- K7 CRC32, zlib polynomial (no reference counterpart: the reference transfers Hadoop's IFile
+ *      checksum and ignores it, src/MOFServer/IndexInfo.cc:308-310, src/Merger/StreamRW.cc:361-367) - */
+int uda_crc32(const void* data, long long n, unsigned* acc_scratch, unsigned* out_dev, void* out_be4_dev,
+              cudaStream_t stream);
+
+/* ---- K5/K6 IFile decode / encode (reference: src/Merger/StreamRW.cc:334-404 nextKVInternal,
+ *      :184-201 serialise, src/CommUtils/IOUtility.cc:167-196 VInt) ------------------------------- */
+int uda_ifile_frame_fixed(const void* raw, long long n, int klen, int vlen, void* out, cudaStream_t stream);
+int uda_ifile_unframe_fixed(const void* framed, long long n, int klen, int vlen, void* raw, cudaStream_t stream);
+long long uda_ifile_decode_scratch_bytes(long long seg_len);
+int uda_ifile_decode_offsets(const void* seg, long long seg_len, long long* rec_off_out, unsigned long long* nrec_dev,
+                             void* scratch, cudaStream_t stream);
+int uda_ifile_encoded_sizes(const int* klen_dev, const int* vlen_dev, long long n, unsigned* sizes_out,
+                            cudaStream_t stream);
+int uda_ifile_encode_var(const void* keys, const long long* key_off, const int* klen, const void* vals,
+                         const long long* val_off, const int* vlen, long long n, const unsigned long long* out_off_dev,
+                         void* out, cudaStream_t stream);
+
+/* ---- symmetric receive arena plumbing (reference: registered MR + rkey exchange,
+ *      src/DataNet/RDMAComm.cc:67-154,178-218, src/DataNet/RDMAComm.h:35-39). These allocate. ---- */
+int uda_dev_malloc(void** ptr, long long bytes);
+int uda_dev_free(void* ptr);
+int uda_ipc_handle_bytes(void);
+int uda_ipc_get_handle(void* ptr, void* handle_out);
+int uda_ipc_open_handle(const void* handle_in, void** ptr_out);
+int uda_ipc_close_handle(void* ptr);
+int uda_can_access_peer(int dev, int peer, int* out);
+int uda_memset_async(void* ptr, int value, long long bytes, cudaStream_t stream);
+int uda_host_alloc_pinned(void** ptr, long long bytes);
+int uda_host_free_pinned(void* ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UDA_B200_H */

@@ -1,0 +1,294 @@
+"""GPU numerics tests: every kernel against a plain NumPy / Python restatement of the same op."""
+import random
+import zlib
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+from uda_b200.models import teragen as tg  # noqa: E402
+from uda_b200.utils import ifile, vint  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K(built):
+    from uda_b200.ops import kernels
+
+    return kernels
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _entries_np(framed: np.ndarray, run: int = 0, idx0: int = 0):
+    """NumPy restatement of key normalise for fixed 10-byte keys."""
+    n = framed.shape[0]
+    w0 = np.zeros(n, dtype=np.uint64)
+    for i in range(8):
+        w0 = (w0 << np.uint64(8)) | framed[:, 2 + i].astype(np.uint64)
+    tail = (framed[:, 10].astype(np.uint64) << np.uint64(8)) | framed[:, 11].astype(np.uint64)
+    w1 = (tail << np.uint64(48)) | (np.uint64(run) << np.uint64(32)) | (np.arange(n, dtype=np.uint64) + np.uint64(idx0))
+    return w0, w1
+
+
+def _sort_order(w0, w1):
+    return np.lexsort((w1, w0))
+
+
+# ------------------------------------------------------------------------------------------- teragen / validate
+@pytest.mark.parametrize("framed", [True, False])
+def test_teragen_matches_numpy(K, framed):
+    n = 5000
+    t = K.teragen(n, seed=11, first_row=123, framed=framed, device=_dev())
+    stride = 102 if framed else 100
+    got = t[: n * stride].cpu().numpy().reshape(n, stride)
+    want = tg.teragen_framed(n, 11, 123) if framed else tg.teragen_raw(n, 11, 123)
+    assert (got == want).all()
+
+
+def test_validate_fingerprint_and_order(K):
+    n = 20000
+    t = K.teragen(n, seed=5, framed=True, device=_dev())
+    bad, fp, cnt = K.validate_fixed(t, n, 102, 2)
+    raw = tg.teragen_raw(n, 5)
+    assert cnt == n and fp == tg.fingerprint_sum(raw)
+    keys = [bytes(r[:10]) for r in raw]
+    assert bad == sum(1 for i in range(n - 1) if keys[i] > keys[i + 1])
+
+
+# ------------------------------------------------------------------------------------------- keys + radix sort
+@pytest.mark.parametrize("n,key_bits", [(1, 0), (777, 0), (100_000, 0), (50_000, 6)])
+def test_extract_and_radix_sort(K, n, key_bits):
+    dev = _dev()
+    t = K.teragen(n, seed=3, framed=True, key_bits=key_bits, device=dev)
+    desc, _ = K.make_run_descs([t.data_ptr()], [n], run_ids=[7], idx0=[5])
+    ent = torch.empty((n, 2), dtype=torch.int64, device=dev)
+    K.extract_keys_fixed(K.to_device_struct(desc, dev), 1, n, 102, 2, 10, ent)
+    framed = tg.teragen_framed(n, 3, key_bits=key_bits)
+    w0, w1 = _entries_np(framed, run=7, idx0=5)
+    got = ent.cpu().numpy().view(np.uint64)
+    assert (got[:, 0] == w0).all() and (got[:, 1] == w1).all()
+    K.radix_sort_entries(ent, 10)
+    got = ent.cpu().numpy().view(np.uint64)
+    order = _sort_order(w0, w1)  # idx ascending inside equal keys == stable
+    assert (got[:, 0] == w0[order]).all() and (got[:, 1] == w1[order]).all()
+
+
+# ------------------------------------------------------------------------------------------- crc32
+@pytest.mark.parametrize("n,off", [(0, 0), (1, 0), (3, 1), (4, 0), (2047, 3), (2048, 0), (2049, 2), (100_003, 1), (5_000_000, 0)])
+def test_crc32_matches_zlib(K, n, off):
+    rng = np.random.RandomState(n + off)
+    host = rng.randint(0, 256, size=n + off + 8, dtype=np.uint8)
+    d = torch.from_numpy(host).to(_dev())
+    be = torch.zeros(4, dtype=torch.uint8, device=_dev())
+    got = K.crc32(d[off:], n, out_be4=be)
+    want = zlib.crc32(host[off:off + n].tobytes()) & 0xFFFFFFFF
+    assert (int(got.item()) & 0xFFFFFFFF) == want
+    assert int.from_bytes(bytes(be.cpu().numpy()), "big") == want
+
+
+# ------------------------------------------------------------------------------------------- ifile codec
+def test_ifile_frame_unframe_fixed(K):
+    n = 3000
+    raw = tg.teragen_raw(n, 21)
+    d = torch.from_numpy(raw.reshape(-1)).to(_dev())
+    out = torch.zeros(n * 102 + 2 + 16, dtype=torch.uint8, device=_dev())
+    K.ifile_frame_fixed(d, n, 10, 90, out)
+    host = out.cpu().numpy()
+    assert (host[: n * 102].reshape(n, 102) == tg.teragen_framed(n, 21)).all()
+    assert bytes(host[n * 102: n * 102 + 2]) == b"\xff\xff"
+    assert ifile.decode_segment(bytes(host[: n * 102 + 2]))[5] == (bytes(raw[5, :10]), bytes(raw[5, 10:]))
+    back = torch.zeros(n * 100, dtype=torch.uint8, device=_dev())
+    K.ifile_unframe_fixed(out, n, 10, 90, back)
+    assert (back.cpu().numpy().reshape(n, 100) == raw).all()
+
+
+def _random_var_records(seed, n, kmax=60, vmax=700):
+    rng = random.Random(seed)
+    recs = []
+    for _ in range(n):
+        kl = rng.choice([0, 1, 5, 10, 130, rng.randint(0, kmax)])
+        vl = rng.choice([0, 3, 127, 128, 300, rng.randint(0, vmax)])
+        recs.append((bytes(rng.getrandbits(8) for _ in range(kl)), bytes(rng.getrandbits(8) for _ in range(vl))))
+    return recs
+
+
+@pytest.mark.parametrize("n,seed", [(0, 1), (1, 2), (500, 3), (4000, 4)])
+def test_ifile_decode_offsets(K, n, seed):
+    recs = _random_var_records(seed, n)
+    if n == 4000:
+        recs[1234] = (b"K" * 20, b"V" * 20000)  # a record spanning several 4 KiB chunks
+    seg = ifile.encode_segment(recs)
+    d = torch.from_numpy(np.frombuffer(seg, dtype=np.uint8).copy()).to(_dev())
+    rec_off, nrec = K.ifile_decode_offsets(d, len(seg) - 4, n + 8)
+    assert int(nrec.item()) == n
+    want, pos = [], 0
+    for k, v in recs:
+        want.append(pos)
+        pos += len(ifile.encode_record(k, v))
+    want.append(pos)  # EOF marker position
+    assert rec_off[: n + 1].cpu().numpy().tolist() == want
+
+
+def test_ifile_encode_var(K):
+    recs = _random_var_records(9, 800)
+    keys = b"".join(k for k, _ in recs)
+    vals = b"".join(v for _, v in recs)
+    klen = np.array([len(k) for k, _ in recs], dtype=np.int32)
+    vlen = np.array([len(v) for _, v in recs], dtype=np.int32)
+    koff = np.concatenate([[0], np.cumsum(klen)[:-1]]).astype(np.int64)
+    voff = np.concatenate([[0], np.cumsum(vlen)[:-1]]).astype(np.int64)
+    dev = _dev()
+    tk = torch.from_numpy(np.frombuffer(keys + b"\0", dtype=np.uint8).copy()).to(dev)
+    tv = torch.from_numpy(np.frombuffer(vals + b"\0", dtype=np.uint8).copy()).to(dev)
+    out = K.ifile_encode_var(tk, torch.from_numpy(koff).to(dev), torch.from_numpy(klen).to(dev), tv,
+                             torch.from_numpy(voff).to(dev), torch.from_numpy(vlen).to(dev))
+    assert bytes(out.cpu().numpy()) == ifile.encode_segment(recs, with_crc=False)
+
+
+def test_extract_keys_var_text(K):
+    rng = random.Random(4)
+    words = [bytes(rng.choice(b"abcdefgh") for _ in range(rng.randint(0, 14))) for _ in range(300)]
+    recs = [(vint.encode_vlong(len(w)) + w, b"\x00\x00\x00\x01") for w in words]  # Text key, IntWritable value
+    seg = ifile.encode_segment(recs)
+    dev = _dev()
+    d = torch.from_numpy(np.frombuffer(seg, dtype=np.uint8).copy()).to(dev)
+    rec_off, nrec = K.ifile_decode_offsets(d, len(seg) - 4, len(recs) + 1)
+    ent = torch.empty((len(recs), 2), dtype=torch.int64, device=dev)
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    K.extract_keys_var(d, rec_off, len(recs), 1, 3, 0, ent, flag)
+    got = ent.cpu().numpy().view(np.uint64)
+    for i, w in enumerate(words):
+        p = (w + b"\0" * 10)[:10]
+        assert int(got[i, 0]) == int.from_bytes(p[:8], "big")
+        assert int(got[i, 1]) == (int.from_bytes(p[8:10], "big") << 48) | (3 << 32) | i
+    assert int(flag.item()) == 1
+
+
+# ------------------------------------------------------------------------------------------- merge + gather
+def _make_runs(K, sizes, seed, key_bits):
+    """Sorted runs of framed records on the device + the NumPy truth."""
+    dev = _dev()
+    bufs, host_runs, row = [], [], 0
+    for r, n in enumerate(sizes):
+        framed = tg.teragen_framed(n, seed, first_row=row, key_bits=key_bits)
+        row += n
+        w0, w1 = _entries_np(framed)
+        order = _sort_order(w0, w1)
+        framed = framed[order]
+        host_runs.append(framed)
+        buf = torch.zeros(K.GATHER_SLACK + n * 102 + K.GATHER_SLACK + 16, dtype=torch.uint8, device=dev)
+        if n:
+            buf[K.GATHER_SLACK: K.GATHER_SLACK + n * 102] = torch.from_numpy(framed.reshape(-1)).to(dev)
+        bufs.append(buf)
+    return bufs, host_runs
+
+
+@pytest.mark.parametrize("sizes,key_bits", [
+    ([1000], 0), ([0, 5, 0], 0), ([3000, 1, 2500, 0, 4000], 0), ([20000] * 24, 0), ([1500] * 300, 0),
+    ([6000, 7000, 5000], 3),     # 8 distinct keys -> oversize buckets -> bisection fallback
+    ([4000] * 9, 10),
+])
+def test_kway_merge_and_gather(K, sizes, key_bits):
+    dev = _dev()
+    bufs, host_runs = _make_runs(K, sizes, seed=17, key_bits=key_bits)
+    k, n = len(sizes), sum(sizes)
+    desc, run_off = K.make_run_descs([b.data_ptr() + K.GATHER_SLACK for b in bufs], sizes)
+    ent = torch.empty((max(n, 1), 2), dtype=torch.int64, device=dev)
+    K.extract_keys_fixed(K.to_device_struct(desc, dev), k, max(sizes), 102, 2, 10, ent)
+    out = torch.empty_like(ent)
+    scratch = torch.empty(K.merge_scratch_bytes(n, k), dtype=torch.uint8, device=dev)
+    K.kway_merge_entries(ent, torch.from_numpy(run_off).to(dev), k, n, out, scratch)
+    fb, iters = K.merge_stats(scratch)
+    # truth
+    w0 = np.concatenate([_entries_np(h, run=r)[0] for r, h in enumerate(host_runs)]) if n else np.zeros(0, np.uint64)
+    w1 = np.concatenate([_entries_np(h, run=r)[1] for r, h in enumerate(host_runs)]) if n else np.zeros(0, np.uint64)
+    order = _sort_order(w0, w1)
+    got = out[:n].cpu().numpy().view(np.uint64)
+    assert (got[:, 0] == w0[order]).all()
+    assert (got[:, 1] == w1[order]).all()
+    if key_bits == 3:
+        assert fb > 0 and iters > 0
+    # gather into the merged stream
+    dst = torch.zeros(n * 102 + 2 + 64, dtype=torch.uint8, device=dev)
+    run_base = torch.tensor([b.data_ptr() + K.GATHER_SLACK for b in bufs], dtype=torch.int64, device=dev)
+    K.gather_fixed(out, n, run_base, 102, dst, True)
+    allrec = np.concatenate(host_runs) if n else np.zeros((0, 102), np.uint8)
+    host = dst.cpu().numpy()
+    assert (host[: n * 102].reshape(n, 102) == allrec[order]).all()
+    assert bytes(host[n * 102: n * 102 + 2]) == b"\xff\xff"
+
+
+@pytest.mark.parametrize("stride", [16, 30, 100, 102, 257])
+def test_gather_generic_strides(K, stride):
+    dev = _dev()
+    n = 2111
+    rng = np.random.RandomState(stride)
+    src = rng.randint(0, 256, size=(n, stride), dtype=np.uint8)
+    buf = torch.zeros(K.GATHER_SLACK + 1 + n * stride + K.GATHER_SLACK + 16, dtype=torch.uint8, device=dev)
+    base_off = K.GATHER_SLACK + 1  # odd base address: exercises every byte phase
+    buf[base_off: base_off + n * stride] = torch.from_numpy(src.reshape(-1)).to(dev)
+    perm = rng.permutation(n).astype(np.uint64)
+    ent = np.zeros((n, 2), dtype=np.uint64)
+    ent[:, 1] = perm
+    dst = torch.zeros(n * stride + 64, dtype=torch.uint8, device=dev)
+    run_base = torch.tensor([buf.data_ptr() + base_off], dtype=torch.int64, device=dev)
+    K.gather_fixed(torch.from_numpy(ent.view(np.int64)).to(dev), n, run_base, stride, dst, False)
+    assert (dst[: n * stride].cpu().numpy().reshape(n, stride) == src[perm.astype(np.int64)]).all()
+
+
+# ------------------------------------------------------------------------------------------- shuffle push (loopback)
+def test_shuffle_push_loopback(K):
+    dev = _dev()
+    rng = np.random.RandomState(1)
+    sizes = [0, 1, 15, 16, 17, 4096, 65536, 65537, 300_001, 1_000_000]
+    src = torch.from_numpy(rng.randint(0, 256, size=sum(sizes) + 64 * len(sizes) + 64, dtype=np.uint8)).to(dev)
+    dst = torch.zeros_like(src)
+    flags = torch.zeros(len(sizes), dtype=torch.int64, device=dev)
+    d = np.zeros(len(sizes), dtype=K.PUSH_DESC_DTYPE)
+    so = do = 0
+    spans = []
+    for i, s in enumerate(sizes):
+        so = (so + 15) // 16 * 16 + (i % 16)           # arbitrary source phase
+        do = (do + 15) // 16 * 16 + (so % 16)           # same phase at the destination
+        d[i] = (src.data_ptr() + so, dst.data_ptr() + do, s, flags.data_ptr() + 8 * i)
+        spans.append((so, do, s))
+        so += s
+        do += s
+    scratch = torch.empty(K.push_scratch_bytes(len(sizes)), dtype=torch.uint8, device=dev)
+    K.shuffle_push(K.to_device_struct(d, dev), len(sizes), scratch)
+    status = torch.zeros(2, dtype=torch.int32, device=dev)
+    K.wait_flags(flags, torch.tensor(sizes, dtype=torch.int64, device=dev), len(sizes), status)
+    torch.cuda.synchronize()
+    assert int(status[0].item()) == 0
+    assert flags.cpu().numpy().tolist() == sizes
+    hs, hd = src.cpu().numpy(), dst.cpu().numpy()
+    for so, do, s in spans:
+        assert (hs[so:so + s] == hd[do:do + s]).all()
+    assert int(hd.astype(np.int64).sum()) == sum(int(hs[so:so + s].astype(np.int64).sum()) for so, _, s in spans)
+
+
+# ------------------------------------------------------------------------------------------- end to end
+@pytest.mark.parametrize("n,maps,key_bits", [(50_000, 4, 0), (200_000, 7, 0), (30_000, 3, 5)])
+def test_terasort_job_single_gpu(built, n, maps, key_bits):
+    from uda_b200.models.terasort import TeraSortJob
+    from uda_b200.utils import ifile as _if
+
+    job = TeraSortJob(n, maps, device=_dev(), key_bits=key_bits).setup()
+    try:
+        # every MOF is a valid Hadoop file.out + index with correct CRCs
+        mof = job.mofs[0]
+        recs = _if.read_partition(mof.file_bytes(), mof.index_records()[0], verify_crc=True)
+        assert len(recs) == int(mof.nrec[0]) and all(len(k) == 10 and len(v) == 90 for k, v in recs[:10])
+        assert [k for k, _ in recs] == sorted(k for k, _ in recs)
+        for _ in range(2):  # second step checks the cumulative flag protocol
+            out = job.step()
+        res = job.check(out)
+        assert res["ok"], res
+        assert out.numel() == n * 102 + 2
+    finally:
+        job.close()

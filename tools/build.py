@@ -1,0 +1,112 @@
+#!/usr/bin/env python
+"""In-tree native build (replaces the reference's autotools flow: src/premake.sh:22-36,
+src/configure.ac:31-114, src/Makefile.am:25-63 — ``-std=gnu++0x -Wall -Werror -O3 -g`` and a
+``VERSION_UDA`` define derived from release + git revision count).
+
+Outputs (git-ignored, shipped to the GPU box by gpurun):
+  uda_b200/lib/libuda_kernels.so   sm_100a CUDA kernels behind the C ABI in include/uda_b200.h
+  uda_b200/lib/libuda.so           C++ runtime + JNI bridge (same file name as the reference's library)
+
+Only sm_100a code is generated (``-gencode arch=compute_100a,code=sm_100a``); ``-lineinfo`` keeps the
+ncu source page usable.
+"""
+from __future__ import annotations
+
+import concurrent.futures as cf
+import hashlib
+import os
+import shlex
+import subprocess
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+LIB_DIR = ROOT / "uda_b200" / "lib"
+OBJ_DIR = ROOT / "build" / "obj"
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+CXX = os.environ.get("CXX", "g++")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-O3", "-lineinfo", "-std=c++17", "--expt-relaxed-constexpr",
+    "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
+    "-Xptxas", "-v",
+    "-I", str(ROOT / "include"),
+]
+CXX_FLAGS = ["-O2", "-g", "-std=c++17", "-fPIC", "-Wall", "-Werror", "-pthread",
+             "-I", str(ROOT / "include"), "-I", str(ROOT / "csrc" / "runtime"), "-I", str(ROOT / "csrc" / "jni")]
+
+
+def uda_version() -> str:
+    """``<release>-<git rev count>`` like the reference's VERSION_UDA (src/configure.ac:31-39)."""
+    try:
+        n = subprocess.run(["git", "rev-list", "--count", "HEAD"], cwd=ROOT, capture_output=True, text=True, timeout=10).stdout.strip()
+    except Exception:
+        n = ""
+    return f"b200-1.0.{n or '0'}"
+
+
+def _run(cmd, log_path: Path | None = None) -> str:
+    p = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True)
+    out = p.stdout + p.stderr
+    if log_path is not None:
+        log_path.write_text(" ".join(shlex.quote(c) for c in cmd) + "\n" + out)
+    if p.returncode != 0:
+        sys.stderr.write(out)
+        raise RuntimeError(f"build step failed: {' '.join(cmd[:3])} ... (see output above)")
+    return out
+
+
+def _stamp(src: Path, flags) -> str:
+    h = hashlib.sha256()
+    h.update(src.read_bytes())
+    h.update(" ".join(flags).encode())
+    for hdr in sorted(list((ROOT / "include").glob("*.h")) + list(src.parent.glob("*.cuh")) + list(src.parent.glob("*.h"))
+                      + list((ROOT / "csrc" / "runtime").glob("*.h"))):
+        h.update(hdr.read_bytes())
+    return h.hexdigest()
+
+
+def _compile(src: Path, compiler: str, flags) -> Path:
+    obj = OBJ_DIR / (src.parent.name + "_" + src.stem + ".o")
+    stamp_file = obj.with_suffix(".stamp")
+    stamp = _stamp(src, flags)
+    if obj.exists() and stamp_file.exists() and stamp_file.read_text() == stamp:
+        return obj
+    _run([compiler, *flags, "-c", str(src), "-o", str(obj)], obj.with_suffix(".log"))
+    stamp_file.write_text(stamp)
+    return obj
+
+
+def build(verbose: bool = False) -> dict:
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    OBJ_DIR.mkdir(parents=True, exist_ok=True)
+    version = uda_version()
+    cu = sorted((ROOT / "csrc" / "kernels").glob("*.cu"))
+    cc = sorted((ROOT / "csrc" / "runtime").glob("*.cc")) + sorted((ROOT / "csrc" / "jni").glob("*.cc"))
+    vflag = [f'-DVERSION_UDA="{version}"']
+    with cf.ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
+        cu_objs = list(ex.map(lambda s: _compile(s, NVCC, NVCC_FLAGS + vflag), cu))
+        cc_objs = list(ex.map(lambda s: _compile(s, CXX, CXX_FLAGS + vflag), cc))
+    out = {}
+    klib = LIB_DIR / "libuda_kernels.so"
+    _run([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(klib), *map(str, cu_objs)])
+    out["kernels"] = klib
+    if cc_objs:
+        rlib = LIB_DIR / "libuda.so"
+        _run([CXX, "-shared", "-pthread", "-o", str(rlib), *map(str, cc_objs), "-ldl"])
+        out["runtime"] = rlib
+    if verbose:
+        for o in cu_objs:
+            log = o.with_suffix(".log")
+            if log.exists():
+                for line in log.read_text().splitlines():
+                    if "registers" in line or "spill" in line.lower() and "0 bytes spill" not in line:
+                        print(f"[{o.stem}] {line.strip()}")
+    return out
+
+
+if __name__ == "__main__":
+    res = build(verbose="-v" in sys.argv)
+    for k, v in res.items():
+        print(f"built {k}: {v}")

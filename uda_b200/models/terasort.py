@@ -1,0 +1,144 @@
+"""TeraSort on the engine: the flagship workload (BASELINE.json config 2).
+
+Phases::
+
+    setup   teragen on device -> MapTask per map (sort + partition + IFile/CRC) -> MOFs in HBM
+            -> all-gather index tables -> symmetric arena -> push descriptors / run tables
+    step    [timed]  fused shuffle push (every MOF partition -> its reducer's arena over NVLink)
+                     -> landed-flag acquire -> key normalise -> k-way merge -> record gather
+    check   TeraValidate equivalent: order inside every reducer, key range per reducer, record
+            count and order-independent fingerprint equal to the generated input.
+
+One reducer per rank, one process per GPU (the reference has the same limit:
+"we only support 1 reducer per process", src/Merger/reducer.h:137).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ..mof import TERA_STRIDE, DeviceMOF, MapTask, uniform_splitters_w0
+from ..ops import kernels as K
+from ..ops.merger import DeviceMerger
+from ..parallel.arena import SymmetricArena
+from ..parallel.shuffle import ShufflePlan
+
+
+class TeraSortJob:
+    def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 1234,
+                 key_bits: int = 0, group=None, push_ctas: int = 0):
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.group = group
+        self.n_local = records_per_rank
+        self.maps = maps_per_rank
+        self.seed, self.key_bits = seed, key_bits
+        self.push_ctas = push_ctas
+        self.mofs: List[DeviceMOF] = []
+        self.input_fingerprint = 0
+        self.steps_run = 0
+
+    # ------------------------------------------------------------------------------------ setup
+    def setup(self) -> "TeraSortJob":
+        dev, P = self.device, self.world
+        per_map = [self.n_local // self.maps + (1 if i < self.n_local % self.maps else 0) for i in range(self.maps)]
+        splitters = uniform_splitters_w0(P)
+        task = MapTask(max(per_map), P, dev)
+        row0 = self.rank * self.n_local
+        fp = 0
+        for m, nm in enumerate(per_map):
+            recs = K.teragen(nm, self.seed, first_row=row0, framed=True, key_bits=self.key_bits, device=dev)
+            _bad, f, cnt = K.validate_fixed(recs, nm, TERA_STRIDE, 2)
+            assert cnt == nm
+            fp = (fp + f) & 0xFFFFFFFFFFFFFFFF
+            self.mofs.append(task.run(recs, nm, splitters))
+            row0 += nm
+            del recs
+        self.input_fingerprint = fp
+        del task
+        torch.cuda.synchronize(dev)
+
+        # ---- index exchange (plumbing over the process group)
+        local_idx = np.stack([m.index for m in self.mofs])  # [maps, P, 3]
+        if P > 1:
+            t = torch.from_numpy(local_idx).to(dev)
+            allt = torch.empty((P,) + tuple(t.shape), dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(allt, t, group=self.group)
+            index = allt.cpu().numpy()
+        else:
+            index = local_idx[None]
+        self.plan = ShufflePlan(index, record_stride=TERA_STRIDE)
+
+        # ---- arena + tables
+        self.arena = SymmetricArena(self.plan.max_arena_bytes(), self.plan.nruns, dev, self.group)
+        descs = self.plan.push_descs(self.rank, [m.data.data_ptr() for m in self.mofs],
+                                     [self.arena.peer_data_ptr(p) for p in range(P)],
+                                     [self.arena.peer_flag_ptr(p, 0) for p in range(P)])
+        self.nseg = len(descs)
+        self.push_descs_dev = K.to_device_struct(descs, dev)
+        self.push_scratch = torch.empty(K.push_scratch_bytes(self.nseg), dtype=torch.uint8, device=dev)
+        rd, run_off, run_base, run_bytes = self.plan.run_descs(self.rank, self.arena.peer_data_ptr(self.rank))
+        self.n_out = int(run_off[-1])
+        self.expect_step = torch.from_numpy(run_bytes.astype(np.int64)).to(dev)
+        self.expect = torch.zeros_like(self.expect_step)
+        self.merger = DeviceMerger(max(self.n_out, 1), self.plan.nruns, TERA_STRIDE, dev)
+        self.merger.set_runs(rd, run_off, run_base)
+        self.bytes_in = int(sum(int(m.index[:, 2].sum()) for m in self.mofs))
+        self.record_bytes_local = self.n_local * 100
+        torch.cuda.synchronize(dev)
+        if P > 1:
+            dist.barrier(group=self.group)
+        return self
+
+    # ------------------------------------------------------------------------------------ step
+    def step(self) -> torch.Tensor:
+        """One shuffle + merge. Flags are cumulative counters, so step ``i`` waits for ``i * bytes``; the
+        all-rank barrier at the top keeps a fast rank from overwriting an arena that is still being merged."""
+        self.steps_run += 1
+        if self.world > 1:
+            self.arena.barrier()
+        K.shuffle_push(self.push_descs_dev, self.nseg, self.push_scratch, self.push_ctas)
+        self.expect.add_(self.expect_step)
+        K.wait_flags(self.arena.flags(), self.expect, self.plan.nruns, self.arena.status)
+        return self.merger.merge_fixed()
+
+    #: kernel launches of this library inside one step (barrier, plan, push, add_, wait, merge chain)
+    @property
+    def launches_per_step(self) -> int:
+        return (1 if self.world > 1 else 0) + 2 + 1 + DeviceMerger.LAUNCHES_PER_MERGE
+
+    # ------------------------------------------------------------------------------------ check
+    def check(self, out: Optional[torch.Tensor] = None) -> dict:
+        out = self.merger.out if out is None else out
+        dev = self.device
+        status = int(self.arena.status[0].item())
+        bad, fp, cnt = K.validate_fixed(out, self.n_out, TERA_STRIDE, 2)
+        eof_ok = bool((out[self.n_out * TERA_STRIDE: self.n_out * TERA_STRIDE + 2].cpu().numpy() == 0xFF).all())
+        # key range of this reducer
+        lo = 0 if self.rank == 0 else ((1 << 64) * self.rank) // self.world
+        hi = (1 << 64) if self.rank == self.world - 1 else ((1 << 64) * (self.rank + 1)) // self.world
+        range_ok = True
+        if self.n_out:
+            first = int.from_bytes(bytes(out[2:10].cpu().numpy()), "big")
+            last_off = (self.n_out - 1) * TERA_STRIDE + 2
+            last = int.from_bytes(bytes(out[last_off:last_off + 8].cpu().numpy()), "big")
+            range_ok = lo <= first and last < hi
+        tot = torch.tensor([cnt, np.uint64(fp).astype(np.int64), self.n_local, np.uint64(self.input_fingerprint).astype(np.int64)],
+                           dtype=torch.int64, device=dev)
+        if self.world > 1:
+            dist.all_reduce(tot, group=self.group)
+        t = tot.cpu().numpy()
+        res = {
+            "misordered": bad, "count_out_local": cnt, "eof_ok": eof_ok, "range_ok": range_ok, "status": status,
+            "count_match": int(t[0]) == int(t[2]), "fingerprint_match": int(t[1]) == int(t[3]),
+        }
+        res["ok"] = bad == 0 and eof_ok and range_ok and status == 0 and res["count_match"] and res["fingerprint_match"]
+        return res
+
+    def close(self) -> None:
+        if hasattr(self, "arena"):
+            self.arena.close()

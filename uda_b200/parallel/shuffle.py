@@ -1,0 +1,115 @@
+"""Shuffle plan: which bytes go where, derived from the all-gathered MOF index tables.
+
+Reference behaviour being replaced: the reducer learns a segment's size only from the first ack
+(``rawLen:partLen:sent:offset:path`` parsed in src/Merger/MergeManager.cc:367-409) and the provider
+learns the destination address from each fetch request (src/MOFServer/MOFServlet.cc:28-96). With the
+push model both sides need the full picture up front, so the per-map index tables
+(``[P,3] = startOffset, rawLength, partLength`` — the ``file.out.index`` content) are
+all-gathered once per job. Every rank then derives, with the same deterministic function,
+
+* the layout of every reducer's receive arena (run ``(src_rank, map)`` -> offset), and
+* its own push descriptor list (segment -> peer pointer + flag pointer),
+
+so no addresses are ever exchanged at fetch time.
+
+Peer rotation: rank ``s`` orders its descriptors by destination ``(s+1+i) % P`` — at any moment the
+ranks target a permutation of the peers, which replaces the reference's randomised fetch order
+(``list_shuffle_in_vector``, src/include/UdaUtil.h:97-101) as the hot-spot avoidance mechanism.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Sequence
+
+import numpy as np
+
+from ..ops.kernels import GATHER_SLACK, PUSH_DESC_DTYPE, RUN_DESC_DTYPE
+
+ALIGN = 16
+
+
+def _align(x: int, a: int = ALIGN) -> int:
+    return (x + a - 1) // a * a
+
+
+@dataclass
+class ReducerLayout:
+    """Receive-side view for one reducer rank."""
+
+    run_offsets: np.ndarray  # [nruns] byte offset of each run's segment in the arena data region
+    run_bytes: np.ndarray    # [nruns] partLength
+    run_nrec: np.ndarray     # [nruns] records (fixed-stride jobs) or -1
+    total_bytes: int
+
+
+class ShufflePlan:
+    """``index[s][m][p] = (startOffset, rawLength, partLength)`` for every rank ``s``, local map ``m``,
+    partition ``p``; all ranks hold the same array. ``record_stride`` > 0 marks a fixed-stride job."""
+
+    def __init__(self, index: np.ndarray, record_stride: int = 0):
+        index = np.asarray(index, dtype=np.int64)
+        assert index.ndim == 4 and index.shape[3] == 3, "index must be [world, maps, P, 3]"
+        self.index = index
+        self.world, self.maps, self.P = index.shape[:3]
+        assert self.P == self.world, "one reducer per rank (reference: src/Merger/reducer.h:137)"
+        self.stride = record_stride
+        self.nruns = self.world * self.maps
+        self.layouts: List[ReducerLayout] = [self._layout(r) for r in range(self.P)]
+
+    def run_id(self, src_rank: int, m: int) -> int:
+        return src_rank * self.maps + m
+
+    def _layout(self, r: int) -> ReducerLayout:
+        offs = np.zeros(self.nruns, dtype=np.int64)
+        nbytes = np.zeros(self.nruns, dtype=np.int64)
+        nrec = np.full(self.nruns, -1, dtype=np.int64)
+        cur = _align(GATHER_SLACK)
+        for s in range(self.world):
+            for m in range(self.maps):
+                start, raw, part = (int(x) for x in self.index[s, m, r])
+                rid = self.run_id(s, m)
+                # keep the source's 16-byte phase so the copy is vectorised end to end
+                cur = _align(cur) + (start % ALIGN)
+                offs[rid] = cur
+                nbytes[rid] = part
+                if self.stride:
+                    body = raw - 2  # rawLength includes the 2-byte EOF marker
+                    assert body % self.stride == 0, "fixed-stride job with a ragged segment"
+                    nrec[rid] = body // self.stride
+                cur += part
+        return ReducerLayout(offs, nbytes, nrec, _align(cur + GATHER_SLACK))
+
+    def max_arena_bytes(self) -> int:
+        return max(l.total_bytes for l in self.layouts)
+
+    # ---- sender side ------------------------------------------------------------------------
+    def push_descs(self, rank: int, mof_ptrs: Sequence[int], peer_data_ptrs: Sequence[int],
+                   peer_flag_base: Sequence[int]) -> np.ndarray:
+        """Descriptor table for ``rank``: ``mof_ptrs[m]`` = device address of local map ``m``'s file.out bytes;
+        ``peer_data_ptrs[p]`` / ``peer_flag_base[p]`` = rank ``p``'s arena data / flag region as mapped here."""
+        d = np.zeros(self.maps * self.P, dtype=PUSH_DESC_DTYPE)
+        i = 0
+        for step in range(self.P):
+            p = (rank + 1 + step) % self.P
+            lay = self.layouts[p]
+            for m in range(self.maps):
+                start, _raw, part = (int(x) for x in self.index[rank, m, p])
+                rid = self.run_id(rank, m)
+                d[i] = (mof_ptrs[m] + start, peer_data_ptrs[p] + int(lay.run_offsets[rid]), part, peer_flag_base[p] + 8 * rid)
+                i += 1
+        return d
+
+    # ---- receiver side ----------------------------------------------------------------------
+    def run_descs(self, rank: int, arena_data_ptr: int):
+        """``(UdaRunDesc table, run_off[nruns+1], run_base[nruns], expected_flag_bytes[nruns])`` for reducer ``rank``."""
+        lay = self.layouts[rank]
+        d = np.zeros(self.nruns, dtype=RUN_DESC_DTYPE)
+        base = arena_data_ptr + lay.run_offsets
+        d["base"] = base.astype(np.uint64)
+        d["nrec"] = np.maximum(lay.run_nrec, 0)
+        off = np.zeros(self.nruns + 1, dtype=np.int64)
+        np.cumsum(d["nrec"], out=off[1:])
+        d["out_off"] = off[:-1]
+        d["run_id"] = np.arange(self.nruns, dtype=np.uint32)
+        d["idx0"] = 0
+        return d, off, base.astype(np.uint64), lay.run_bytes.copy()
