@@ -17,12 +17,30 @@
 
 namespace uda {
 
-// 16 bytes starting at arbitrary address a (reads [a&~3, (a&~3)+20))
+// 16 bytes starting at arbitrary address a (reads [a&~3, (a&~3)+20): up to 22 bytes past the record end,
+// which is why source buffers need GATHER_SLACK readable bytes after their last record)
 __device__ __forceinline__ uint4 load16_unaligned(const uint8_t* a) {
     const uintptr_t ai = (uintptr_t)a;
     const uint32_t* w = (const uint32_t*)(ai & ~(uintptr_t)3);
     const uint32_t sh = (uint32_t)(ai & 3) * 8;
     uint32_t x0 = __ldg(w), x1 = __ldg(w + 1), x2 = __ldg(w + 2), x3 = __ldg(w + 3), x4 = __ldg(w + 4);
+    uint4 r;
+    r.x = __funnelshift_r(x0, x1, sh);
+    r.y = __funnelshift_r(x1, x2, sh);
+    r.z = __funnelshift_r(x2, x3, sh);
+    r.w = __funnelshift_r(x3, x4, sh);
+    return r;
+}
+
+// same, but never touches memory below `floor` (4-byte aligned down): words below it read as zero.
+// Used for the second piece of a straddling word, whose window starts before the record.
+__device__ __forceinline__ uint4 load16_unaligned_floor(const uint8_t* a, const uint8_t* floor) {
+    const uintptr_t ai = (uintptr_t)a;
+    const uint32_t* w = (const uint32_t*)(ai & ~(uintptr_t)3);
+    const uint32_t* f = (const uint32_t*)((uintptr_t)floor & ~(uintptr_t)3);
+    const uint32_t sh = (uint32_t)(ai & 3) * 8;
+    uint32_t x0 = w >= f ? __ldg(w) : 0u, x1 = w + 1 >= f ? __ldg(w + 1) : 0u, x2 = w + 2 >= f ? __ldg(w + 2) : 0u,
+             x3 = w + 3 >= f ? __ldg(w + 3) : 0u, x4 = __ldg(w + 4);
     uint4 r;
     r.x = __funnelshift_r(x0, x1, sh);
     r.y = __funnelshift_r(x1, x2, sh);
@@ -55,7 +73,8 @@ __global__ void __launch_bounds__(256) gather_fixed_kernel(const Entry* __restri
         const int len0 = stride - o0 < 16 ? stride - o0 : 16;
         uint4 v = load16_unaligned(record_ptr(S, j0, run_base, stride) + o0);
         if (len0 < 16) {  // word straddles two records (stride >= 16 so never three)
-            uint4 u = load16_unaligned(record_ptr(S, j0 + 1, run_base, stride) - len0);
+            const uint8_t* nx = record_ptr(S, j0 + 1, run_base, stride);
+            uint4 u = load16_unaligned_floor(nx - len0, nx);
             uint32_t m0 = low_bytes_mask(len0), m1 = low_bytes_mask(len0 - 4), m2 = low_bytes_mask(len0 - 8),
                      m3 = low_bytes_mask(len0 - 12);
             v.x = (v.x & m0) | (u.x & ~m0);

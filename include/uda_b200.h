@@ -78,7 +78,7 @@ int uda_merge_stats(const void* scratch, unsigned long long* out2_host, cudaStre
 
 /* ---- merged-stream materialisation (reference: src/Merger/StreamRW.cc:184-201,216-218) ---------- */
 /* dst must be 16-byte aligned and hold n*stride (+2 if write_eof) bytes. run_base_dev[run] = device
- * address of record 0 of that run; source buffers need 32 readable bytes before and after. */
+ * address of record 0 of that run; source buffers need 32 readable bytes after their last record. */
 int uda_gather_fixed(const void* sorted_entries, long long n, const unsigned long long* run_base_dev, int stride,
                      void* dst, int write_eof, cudaStream_t stream);
 int uda_gather_var_lengths(const void* sorted_entries, long long n, const unsigned long long* run_recoff_dev,

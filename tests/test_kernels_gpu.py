@@ -273,7 +273,7 @@ def test_shuffle_push_loopback(K):
 
 
 # ------------------------------------------------------------------------------------------- end to end
-@pytest.mark.parametrize("n,maps,key_bits", [(50_000, 4, 0), (200_000, 7, 0), (30_000, 3, 5)])
+@pytest.mark.parametrize("n,maps,key_bits", [(50_000, 4, 0), (200_000, 7, 0), (30_000, 3, 5), (6_000_000, 2, 0)])
 def test_terasort_job_single_gpu(built, n, maps, key_bits):
     from uda_b200.models.terasort import TeraSortJob
     from uda_b200.utils import ifile as _if
