@@ -51,3 +51,12 @@ extern "C" int uda_host_free_pinned(void* ptr) {
     UDA_CUDA(cudaFreeHost(ptr));
     return 0;
 }
+
+// Human-readable text for a return code of this library (negative: UDA_E_*, positive: cudaError_t).
+extern "C" const char* uda_error_string(int rc) {
+    if (rc == 0) return "success";
+    if (rc == UDA_E_INVALID) return "uda: invalid argument";
+    if (rc == UDA_E_TOO_LARGE) return "uda: size exceeds the documented maximum of this entry point";
+    if (rc > 0) return cudaGetErrorString((cudaError_t)rc);
+    return "uda: unknown error";
+}

@@ -160,3 +160,68 @@ extern "C" int uda_barrier_all(unsigned long long* const* pads_dev, int rank, in
     UDA_CHECK_LAUNCH();
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------
+// uda_shuffle_push_static — the same push as uda_shuffle_push, for callers that may not allocate.
+//
+// Who needs it: a shuffle provider embedded in a process whose device memory is owned by someone
+// else. Typical cases are a JNI plugin inside a Hadoop/YARN container where another runtime has
+// already reserved the GPU's free memory, a service that sizes all of its buffers once at start-up and
+// treats any later cudaMalloc as a bug (allocation synchronises the device and can fail under
+// fragmentation), and code that runs between other people's kernels where an implicit device
+// synchronisation is not acceptable. Such a caller still owns the MOF bytes, the arena and the
+// descriptor table (inputs and outputs), but has nowhere to get the kernel's chunk-prefix scratch
+// from. Here that scratch is a fixed array inside the library image.
+//
+// Limit: at most UDA_PUSH_STATIC_MAX_SEGMENTS descriptors per call ((max+1) * 4 bytes = 64 KiB + 4 B of
+// device memory, held by every GPU that loads this library until the process exits).
+//
+// Set-up: the first call on each device looks up the array's device address
+// (cudaGetSymbolAddress, with that device current) and caches it; make that first call outside any
+// stream capture. Later calls on the same device only launch kernels.
+//
+// Sharing: every call on a device uses the same array and finds the previous call's prefix table in
+// it. Nothing in it has to start at zero (the plan kernel rewrites entries [0, nseg] before the push
+// kernel reads them), so there is nothing to clear; but two calls whose kernels overlap on the GPU
+// (different streams, no dependency between them) race on the table. Issue them on one stream or
+// order them with events.
+constexpr int PUSH_STATIC_MAX_SEG = UDA_PUSH_STATIC_MAX_SEGMENTS;
+static __device__ __align__(256) unsigned g_push_static_prefix[PUSH_STATIC_MAX_SEG + 1];
+
+#include <mutex>
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_push_static_mu;
+unsigned* g_push_static_ptr[kMaxDevices] = {nullptr};
+}  // namespace
+
+extern "C" int uda_shuffle_push_static(const UdaPushDesc* descs_dev, int nseg, int max_ctas, cudaStream_t stream) {
+    using namespace uda;
+    if (nseg < 0) return UDA_E_INVALID;
+    if (nseg > PUSH_STATIC_MAX_SEG) return UDA_E_TOO_LARGE;  // "nseg exceeds UDA_PUSH_STATIC_MAX_SEGMENTS"
+    if (nseg == 0) return 0;
+    int dev = -1;
+    UDA_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return UDA_E_INVALID;
+    unsigned* prefix = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_push_static_mu);
+        if (!g_push_static_ptr[dev]) {
+            // In host code the array's name is only a handle for the symbol, not a device address:
+            // resolve it once per device, with that device current.
+            unsigned* p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress((void**)&p, g_push_static_prefix);
+            if (e != cudaSuccess) return (int)e;
+            if (!p) return UDA_E_INVALID;
+            g_push_static_ptr[dev] = p;
+        }
+        prefix = g_push_static_ptr[dev];
+    }
+    push_plan_kernel<<<1, 1024, 0, stream>>>(descs_dev, nseg, prefix);
+    int grid = max_ctas > 0 ? max_ctas : kNumSMs * 8;
+    push_kernel<<<grid, PUSH_THREADS, 0, stream>>>(descs_dev, nseg, prefix);
+    UDA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int uda_shuffle_push_static_max_segments(void) { return PUSH_STATIC_MAX_SEG; }

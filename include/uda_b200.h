@@ -92,6 +92,17 @@ int uda_gather_var(const void* sorted_entries, long long n, const unsigned long 
  *      :44-136 credits) --------------------------------------------------------------------------- */
 long long uda_push_scratch_bytes(int nseg);
 int uda_shuffle_push(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, cudaStream_t stream);
+/* No counterpart in the reference (it has no device code and nothing that must avoid allocation).
+ * Same push as uda_shuffle_push, but the chunk-prefix scratch is a fixed array inside the library,
+ * so the call never allocates: for providers embedded in a process that does not own the GPU's free
+ * memory (JNI plugin next to another runtime, fixed-budget services) or that must not trigger the
+ * implicit device synchronisation of cudaMalloc. At most UDA_PUSH_STATIC_MAX_SEGMENTS descriptors per
+ * call (returns UDA_E_TOO_LARGE beyond that). The first call on each device resolves the array's
+ * address and must be made outside stream capture. All calls on a device share the array: calls
+ * whose kernels overlap on the GPU race; keep them on one stream or order them with events. */
+#define UDA_PUSH_STATIC_MAX_SEGMENTS 16384
+int uda_shuffle_push_static(const UdaPushDesc* descs_dev, int nseg, int max_ctas, cudaStream_t stream);
+int uda_shuffle_push_static_max_segments(void);
 int uda_wait_flags(const unsigned long long* flags_dev, const unsigned long long* expect_dev, int n,
                    unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream);
 int uda_barrier_all(unsigned long long* const* pads_dev, int rank, int world, unsigned long long epoch,
@@ -127,6 +138,8 @@ int uda_can_access_peer(int dev, int peer, int* out);
 int uda_memset_async(void* ptr, int value, long long bytes, cudaStream_t stream);
 int uda_host_alloc_pinned(void** ptr, long long bytes);
 int uda_host_free_pinned(void* ptr);
+/* text for a return code of this library (negative: UDA_E_*, positive: cudaError_t) */
+const char* uda_error_string(int rc);
 
 #ifdef __cplusplus
 }
