@@ -1,0 +1,42 @@
+"""Multi-rank TeraSort correctness script (launched by torchrun, one process per GPU)."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+
+import torch
+import torch.distributed as dist
+
+
+def main():
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 200_000
+    maps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+    steps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
+    lr = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dev = torch.device("cuda", lr)
+    dist.init_process_group("nccl", device_id=dev)
+    from uda_b200.models.terasort import TeraSortJob
+
+    job = TeraSortJob(n, maps, device=dev).setup()
+    out = None
+    for _ in range(steps):
+        out = job.step()
+    res = job.check(out)
+    torch.cuda.synchronize()
+    # P2P sanity: arena peer pointers differ and the barrier works
+    job.arena.barrier()
+    torch.cuda.synchronize()
+    res["barrier_status"] = int(job.arena.status[0].item())
+    res["rank"] = dist.get_rank()
+    res["n_out"] = job.n_out
+    print("MPRESULT " + json.dumps(res), flush=True)
+    ok = res["ok"] and res["barrier_status"] == 0
+    job.close()
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()

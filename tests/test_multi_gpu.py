@@ -1,0 +1,31 @@
+"""Multi-GPU tests (need >= 2 visible GPUs; run with `gpurun --gpus N`). One process per GPU via torchrun."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+torch = pytest.importorskip("torch")
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpu():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+def _torchrun(n, script, *args, timeout=600):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", str(29500 + n), os.path.join(ROOT, "tests", "scripts", script), *map(str, args)]
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_terasort_multi_rank(built, world):
+    if _ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    p = _torchrun(world, "mp_terasort.py", 300_000, 3, 2)
+    lines = [l for l in p.stdout.splitlines() if l.startswith("MPRESULT")]
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-3000:]
+    assert len(lines) == world
