@@ -117,6 +117,8 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if not os.environ.get("UDA_KEEP_NCCL_DEBUG"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -201,7 +203,8 @@ def main():
             "gpu_launches": int(getattr(job, "launches_per_step", 0)) * a.steps,
             "validated": None if check is None else check["ok"],
         }
-        print(json.dumps(out))
+        sys.stdout.flush()
+        print(json.dumps(out), flush=True)
     job.close()
     if world > 1:
         dist.destroy_process_group()

@@ -160,6 +160,18 @@ __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned l
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// first 10 compared key bytes -> (w0, 16-bit tail); shorter keys are zero padded
+__device__ __forceinline__ void key_prefix(const uint8_t* k, int len, unsigned long long* w0, uint32_t* tail16) {
+    unsigned long long a = 0;
+    uint32_t t = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a = (a << 8) | (i < len ? k[i] : 0u);
+#pragma unroll
+    for (int i = 8; i < 10; ++i) t = (t << 8) | (i < len ? k[i] : 0u);
+    *w0 = a;
+    *tail16 = t;
+}
+
 __device__ __forceinline__ unsigned long long bswap64(unsigned long long x) {
     uint32_t lo = (uint32_t)x, hi = (uint32_t)(x >> 32);
     return ((unsigned long long)__byte_perm(lo, 0, 0x0123) << 32) | __byte_perm(hi, 0, 0x0123);

@@ -14,17 +14,6 @@
 
 namespace uda {
 
-__device__ __forceinline__ void key_prefix(const uint8_t* k, int len, unsigned long long* w0, uint32_t* tail16) {
-    unsigned long long a = 0;
-    uint32_t t = 0;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) a = (a << 8) | (i < len ? k[i] : 0u);
-#pragma unroll
-    for (int i = 8; i < 10; ++i) t = (t << 8) | (i < len ? k[i] : 0u);
-    *w0 = a;
-    *tail16 = t;
-}
-
 // Fixed-stride records (TeraSort fast path). One launch covers many runs: blockIdx.y = run.
 __global__ void extract_keys_fixed_kernel(const UdaRunDesc* __restrict__ runs, int stride, int key_off, int key_len,
                                           Entry* __restrict__ out) {

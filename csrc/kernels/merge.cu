@@ -80,6 +80,62 @@ __global__ void merge_hist_kernel(const Entry* __restrict__ E, long long n, cons
     }
 }
 
+// ------------------------------------------------------------------------------------- 1+2 fused
+// Fixed-stride front end: the key range comes straight from the first/last record of every run, so the
+// histogram can be accumulated by the same pass that normalises the keys (saves one 16 B/entry pass).
+__global__ void merge_range_records_kernel(const UdaRunDesc* __restrict__ runs, int k, int stride, int key_off, int key_len,
+                                           MergeParams* __restrict__ prm) {
+    __shared__ unsigned long long smin, smax;
+    if (threadIdx.x == 0) { smin = ~0ull; smax = 0ull; }
+    __syncthreads();
+    for (int r = threadIdx.x; r < k; r += blockDim.x) {
+        const UdaRunDesc rd = runs[r];
+        if (rd.nrec > 0) {
+            const uint8_t* base = (const uint8_t*)rd.base;
+            unsigned long long w0;
+            uint32_t t;
+            key_prefix(base + key_off, key_len, &w0, &t);
+            atomicMin(&smin, w0);
+            key_prefix(base + (rd.nrec - 1) * stride + key_off, key_len, &w0, &t);
+            atomicMax(&smax, w0);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long lo = smin, hi = smax;
+        if (lo > hi) { lo = 0; hi = 0; }
+        unsigned long long range = hi - lo;
+        int shift = 0;
+        while (shift < 64 && (range >> shift) >= (unsigned long long)MG_NB) ++shift;
+        prm->kmin = lo;
+        prm->kmax = hi;
+        prm->shift = shift;
+        prm->fallback_buckets = 0;
+        prm->fallback_iters = 0;
+    }
+}
+
+__global__ void extract_hist_fixed_kernel(const UdaRunDesc* __restrict__ runs, int stride, int key_off, int key_len,
+                                          const MergeParams* __restrict__ prm, Entry* __restrict__ out,
+                                          uint32_t* __restrict__ hist) {
+    const UdaRunDesc rd = runs[blockIdx.y];
+    const uint8_t* base = (const uint8_t*)rd.base;
+    Entry* o = out + rd.out_off;
+    const unsigned long long hi_bits = ((unsigned long long)rd.run_id & 0xFFFFull) << 32;
+    const unsigned long long kmin = prm->kmin;
+    const int shift = prm->shift;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < rd.nrec; i += (long long)gridDim.x * blockDim.x) {
+        unsigned long long w0;
+        uint32_t t;
+        key_prefix(base + i * stride + key_off, key_len, &w0, &t);
+        Entry e;
+        e.w0 = w0;
+        e.w1 = ((unsigned long long)t << 48) | hi_bits | (unsigned long long)(uint32_t)(rd.idx0 + i);
+        o[i] = e;
+        atomicAdd(&hist[(w0 - kmin) >> shift], 1u);
+    }
+}
+
 // ------------------------------------------------------------------------------------------- 3
 // device-wide exclusive scan of m (<= 1024*1024) u32 values, three launches
 constexpr int SC_THREADS = 1024;
@@ -450,22 +506,10 @@ extern "C" long long uda_merge_scratch_bytes(long long n, int nruns) {
     return (long long)uda::merge_scratch_layout(nullptr, n, nruns).bytes;
 }
 
-extern "C" int uda_kway_merge_entries(const void* entries, const long long* run_off_dev, int nruns, long long n,
-                                      void* sorted_out, void* scratch, cudaStream_t stream) {
+static int merge_back(const uda::Entry* E, const long long* run_off_dev, int nruns, long long n, void* sorted_out,
+                      const uda::MergeScratch& s, cudaStream_t stream) {
     using namespace uda;
-    if (nruns < 1 || nruns > MG_KMAX || n < 0 || n >= (1LL << 32) - MG_TILE) return UDA_E_INVALID;
-    if (n == 0) return 0;
-    const Entry* E = (const Entry*)entries;
-    MergeScratch s = merge_scratch_layout(scratch, n, nruns);
     const int G = merge_num_buckets(n);
-
-    merge_range_kernel<<<1, 256, 0, stream>>>(E, run_off_dev, nruns, s.prm);
-    UDA_CUDA(cudaMemsetAsync(s.hist, 0, (size_t)(MG_NB + 1) * 4, stream));
-    {
-        long long b = (n + 255) / 256;
-        if (b > kNumSMs * 16) b = kNumSMs * 16;
-        merge_hist_kernel<<<(int)b, 256, 0, stream>>>(E, n, s.prm, s.hist);
-    }
     int rc = scan_u32_exclusive(s.hist, MG_NB, s.hist, s.sums, stream);
     if (rc) return rc;
     {
@@ -490,6 +534,47 @@ extern "C" int uda_kway_merge_entries(const void* entries, const long long* run_
     }
     UDA_CHECK_LAUNCH();
     return 0;
+}
+
+extern "C" int uda_kway_merge_entries(const void* entries, const long long* run_off_dev, int nruns, long long n,
+                                      void* sorted_out, void* scratch, cudaStream_t stream) {
+    using namespace uda;
+    if (nruns < 1 || nruns > MG_KMAX || n < 0 || n >= (1LL << 32) - MG_TILE) return UDA_E_INVALID;
+    if (n == 0) return 0;
+    const Entry* E = (const Entry*)entries;
+    MergeScratch s = merge_scratch_layout(scratch, n, nruns);
+    merge_range_kernel<<<1, 256, 0, stream>>>(E, run_off_dev, nruns, s.prm);
+    UDA_CUDA(cudaMemsetAsync(s.hist, 0, (size_t)(MG_NB + 1) * 4, stream));
+    {
+        long long b = (n + 255) / 256;
+        if (b > kNumSMs * 16) b = kNumSMs * 16;
+        merge_hist_kernel<<<(int)b, 256, 0, stream>>>(E, n, s.prm, s.hist);
+    }
+    return merge_back(E, run_off_dev, nruns, n, sorted_out, s, stream);
+}
+
+// Fused fixed-stride pipeline: key normalise + histogram in one pass over the landed records, then the
+// merge proper. entries_tmp and sorted_out hold n entries each.
+extern "C" int uda_merge_runs_fixed(const UdaRunDesc* runs_dev, const long long* run_off_dev, int nruns, long long n,
+                                    long long max_nrec, int stride, int key_off, int key_len, void* entries_tmp,
+                                    void* sorted_out, void* scratch, cudaStream_t stream) {
+    using namespace uda;
+    if (nruns < 1 || nruns > MG_KMAX || n < 0 || n >= (1LL << 32) - MG_TILE) return UDA_E_INVALID;
+    if (n == 0) return 0;
+    Entry* E = (Entry*)entries_tmp;
+    MergeScratch s = merge_scratch_layout(scratch, n, nruns);
+    merge_range_records_kernel<<<1, 256, 0, stream>>>(runs_dev, nruns, stride, key_off, key_len, s.prm);
+    UDA_CUDA(cudaMemsetAsync(s.hist, 0, (size_t)(MG_NB + 1) * 4, stream));
+    {
+        long long bx = (max_nrec + 255) / 256;
+        long long cap = (kNumSMs * 16 + nruns - 1) / nruns;
+        if (cap < 1) cap = 1;
+        if (bx > cap) bx = cap;
+        if (bx < 1) bx = 1;
+        dim3 grid((unsigned)bx, (unsigned)nruns);
+        extract_hist_fixed_kernel<<<grid, 256, 0, stream>>>(runs_dev, stride, key_off, key_len, s.prm, E, s.hist);
+    }
+    return merge_back(E, run_off_dev, nruns, n, sorted_out, s, stream);
 }
 
 extern "C" int uda_merge_stats(const void* scratch, unsigned long long* out2_host, cudaStream_t stream) {

@@ -73,6 +73,11 @@ long long uda_merge_scratch_bytes(long long n, int nruns);
  * n entries in (key, run, index) order. nruns <= 4096, n < 2^32. */
 int uda_kway_merge_entries(const void* entries, const long long* run_off_dev, int nruns, long long n,
                            void* sorted_out, void* scratch, cudaStream_t stream);
+/* Fused front end for fixed-stride records: key normalise + histogram in one pass over the landed
+ * segments (described by runs_dev), then the same merge. entries_tmp / sorted_out: n entries each. */
+int uda_merge_runs_fixed(const UdaRunDesc* runs_dev, const long long* run_off_dev, int nruns, long long n,
+                         long long max_nrec, int stride, int key_off, int key_len, void* entries_tmp,
+                         void* sorted_out, void* scratch, cudaStream_t stream);
 /* synchronises the stream; out2_host = {oversize buckets, bisection iterations} of the last merge */
 int uda_merge_stats(const void* scratch, unsigned long long* out2_host, cudaStream_t stream);
 

@@ -27,7 +27,31 @@ from ..parallel.arena import SymmetricArena
 from ..parallel.shuffle import ShufflePlan
 
 
+def _host_mem_available():
+    """MemAvailable from /proc/meminfo, capped by the cgroup limit when there is one (bytes)."""
+    avail = None
+    try:
+        with open("/proc/meminfo") as f:
+            for line in f:
+                if line.startswith("MemAvailable:"):
+                    avail = int(line.split()[1]) * 1024
+                    break
+        for path in ("/sys/fs/cgroup/memory.max", "/sys/fs/cgroup/memory/memory.limit_in_bytes"):
+            try:
+                v = open(path).read().strip()
+                if v.isdigit() and int(v) < (1 << 60):
+                    avail = min(avail, int(v)) if avail is not None else int(v)
+            except OSError:
+                pass
+    except OSError:
+        return None
+    return avail
+
+
 class TeraSortJob:
+    #: bytes of one slot of the pinned host ring that receives the merged stream
+    E2E_RING_BYTES = 256 << 20
+
     def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 1234,
                  key_bits: int = 0, group=None, push_ctas: int = 0):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
@@ -95,16 +119,91 @@ class TeraSortJob:
         return self
 
     # ------------------------------------------------------------------------------------ step
-    def step(self) -> torch.Tensor:
+    def step(self, descs: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One shuffle + merge. Flags are cumulative counters, so step ``i`` waits for ``i * bytes``; the
         all-rank barrier at the top keeps a fast rank from overwriting an arena that is still being merged."""
         self.steps_run += 1
         if self.world > 1:
             self.arena.barrier()
-        K.shuffle_push(self.push_descs_dev, self.nseg, self.push_scratch, self.push_ctas)
+        K.shuffle_push(self.push_descs_dev if descs is None else descs, self.nseg, self.push_scratch, self.push_ctas)
         self.expect.add_(self.expect_step)
         K.wait_flags(self.arena.flags(), self.expect, self.plan.nruns, self.arena.status)
-        return self.merger.merge_fixed()
+        return self.merger.merge_fixed(out=out)
+
+    # ------------------------------------------------------------------------------------ end to end
+    def e2e_setup(self) -> None:
+        """End-to-end path: map outputs start in pinned host memory (what a provider that just read
+        ``file.out`` from disk holds) and the merged stream must end in pinned host memory (the buffer a
+        JVM would wrap as a direct ByteBuffer, reference: src/UdaBridge.cc:535-551). Device input and
+        output buffers are double-buffered so H2D of step i+1, compute of step i and D2H of step i-1
+        overlap on three streams."""
+        dev = self.device
+        out_bytes = self.n_out * TERA_STRIDE + 2
+        need = sum(int(m.index[-1, 0] + m.index[-1, 2]) for m in self.mofs) + 2 * self.E2E_RING_BYTES
+        avail = _host_mem_available()
+        if avail is not None and need * self.world > 0.7 * avail:
+            raise RuntimeError(f"not enough host memory to pin the e2e staging buffers: need {need * self.world >> 30} GiB "
+                               f"across {self.world} ranks, {avail >> 30} GiB available")
+        self.h_mofs = []
+        for m in self.mofs:
+            nb = int(m.index[-1, 0] + m.index[-1, 2])
+            h = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
+            h.copy_(m.data[:nb])
+            self.h_mofs.append(h)
+        self.e2e_h2d_bytes = sum(h.numel() for h in self.h_mofs)
+        self.e2e_d2h_bytes = out_bytes
+        # The merged stream is consumed in blocks and never materialised on the host (the reference hands
+        # Java 1 MiB blocks out of two staging buffers, src/include/NetlevComm.h:33): a two-slot pinned ring.
+        self.h_ring = [torch.empty(self.E2E_RING_BYTES, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
+        # second device buffer set
+        self.d_mofs = [[m.data for m in self.mofs], [torch.empty_like(m.data) for m in self.mofs]]
+        descs2 = self.plan.push_descs(self.rank, [t.data_ptr() for t in self.d_mofs[1]],
+                                      [self.arena.peer_data_ptr(p) for p in range(self.world)],
+                                      [self.arena.peer_flag_ptr(p, 0) for p in range(self.world)])
+        self.d_descs = [self.push_descs_dev, K.to_device_struct(descs2, dev)]
+        self.d_out = [self.merger.out, torch.empty_like(self.merger.out)]
+        self.s_h2d, self.s_d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        self.ev_h2d = [torch.cuda.Event(), torch.cuda.Event()]
+        self.ev_comp = [torch.cuda.Event(), torch.cuda.Event()]
+        self.ev_d2h = [torch.cuda.Event(), torch.cuda.Event()]
+        self.e2e_i = 0
+        torch.cuda.synchronize(dev)
+
+    def e2e_step(self) -> torch.Tensor:
+        i, b = self.e2e_i, self.e2e_i % 2
+        self.e2e_i += 1
+        cur = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self.s_h2d):
+            if i >= 2:
+                self.s_h2d.wait_event(self.ev_comp[b])      # step i-2 has finished reading this MOF set
+            for h, d in zip(self.h_mofs, self.d_mofs[b]):
+                d[: h.numel()].copy_(h, non_blocking=True)
+            self.ev_h2d[b].record(self.s_h2d)
+        cur.wait_event(self.ev_h2d[b])
+        if i >= 2:
+            cur.wait_event(self.ev_d2h[b])                   # step i-2's result has left this output buffer
+        out = self.step(self.d_descs[b], self.d_out[b])
+        self.ev_comp[b].record(cur)
+        with torch.cuda.stream(self.s_d2h):
+            self.s_d2h.wait_event(self.ev_comp[b])
+            nb, ring = out.numel(), self.E2E_RING_BYTES
+            for k, off in enumerate(range(0, nb, ring)):
+                ln = min(ring, nb - off)
+                self.h_ring[k % 2][:ln].copy_(out[off:off + ln], non_blocking=True)
+            self.ev_d2h[b].record(self.s_d2h)
+        self._e2e_last = b
+        return out
+
+    def e2e_check(self) -> bool:
+        """Validate the device stream the host blocks were copied from, and that the last block that
+        reached host memory is byte-identical to its device source."""
+        torch.cuda.synchronize(self.device)
+        out = self.d_out[self._e2e_last]
+        nb, ring = self.n_out * TERA_STRIDE + 2, self.E2E_RING_BYTES
+        nblk = (nb + ring - 1) // ring
+        off = (nblk - 1) * ring
+        last_ok = bool(torch.equal(self.h_ring[(nblk - 1) % 2][: nb - off], out[off:nb].cpu()))
+        return bool(self.check(out)["ok"]) and last_ok
 
     #: kernel launches of this library inside one step (barrier, plan, push, add_, wait, merge chain)
     @property

@@ -113,6 +113,14 @@ def kway_merge_entries(entries: torch.Tensor, run_off_dev: torch.Tensor, nruns: 
                                            scratch.data_ptr(), _stream()), "uda_kway_merge_entries")
 
 
+def merge_runs_fixed(run_descs_dev: torch.Tensor, run_off_dev: torch.Tensor, nruns: int, n: int, max_nrec: int, stride: int,
+                     key_off: int, key_len: int, entries_tmp: torch.Tensor, sorted_out: torch.Tensor, scratch: torch.Tensor) -> None:
+    """Fused key normalise + histogram + k-way merge for fixed-stride runs."""
+    check(kernels().uda_merge_runs_fixed(run_descs_dev.data_ptr(), run_off_dev.data_ptr(), nruns, n, max_nrec, stride, key_off,
+                                         key_len, entries_tmp.data_ptr(), sorted_out.data_ptr(), scratch.data_ptr(), _stream()),
+          "uda_merge_runs_fixed")
+
+
 def merge_stats(scratch: torch.Tensor) -> Tuple[int, int]:
     out = (C.c_ulonglong * 2)()
     check(kernels().uda_merge_stats(scratch.data_ptr(), out, _stream()), "uda_merge_stats")

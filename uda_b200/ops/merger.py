@@ -39,14 +39,17 @@ class DeviceMerger:
         self.run_off_dev = torch.from_numpy(run_off.astype(np.int64)).to(self.device)
         self.run_base_dev = torch.from_numpy(run_base.astype(np.uint64).view(np.int64)).to(self.device)
 
-    def merge_fixed(self, key_off: int = 2, key_len: int = 10, write_eof: bool = True) -> torch.Tensor:
-        """Merge the runs described by :meth:`set_runs`; returns the merged stream (view of ``self.out``)."""
+    def merge_fixed(self, key_off: int = 2, key_len: int = 10, write_eof: bool = True,
+                    out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Merge the runs described by :meth:`set_runs`; returns the merged stream (view of ``out`` /
+        ``self.out``)."""
         n = self.n
+        out = self.out if out is None else out
         if n:
-            K.extract_keys_fixed(self.run_descs_dev, self.nruns, self.max_nrec, self.stride, key_off, key_len, self.entries)
-            K.kway_merge_entries(self.entries, self.run_off_dev, self.nruns, n, self.sorted, self.scratch)
-        K.gather_fixed(self.sorted, n, self.run_base_dev, self.stride, self.out, write_eof)
-        return self.out[: n * self.stride + (2 if write_eof else 0)]
+            K.merge_runs_fixed(self.run_descs_dev, self.run_off_dev, self.nruns, n, self.max_nrec, self.stride, key_off, key_len,
+                               self.entries, self.sorted, self.scratch)
+        K.gather_fixed(self.sorted, n, self.run_base_dev, self.stride, out, write_eof)
+        return out[: n * self.stride + (2 if write_eof else 0)]
 
-    #: kernels launched by one merge_fixed() call (extract, range, hist, 3 scan, partition, tiles, gather, eof)
-    LAUNCHES_PER_MERGE = 10
+    #: kernels launched by one merge_fixed() call (range, extract+hist, 3 scan, partition, tiles, gather, eof)
+    LAUNCHES_PER_MERGE = 9
