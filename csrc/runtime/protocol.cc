@@ -154,14 +154,21 @@ bool parse_fetch_request(const std::string& s, FetchRequest* r) {
     std::string f;
     if (!next_field(s, &pos, &r->job_id)) return false;
     if (!next_field(s, &pos, &r->map_id)) return false;
-    if (!next_field(s, &pos, &f)) return false; r->map_offset = atoll(f.c_str());
-    if (!next_field(s, &pos, &f)) return false; r->reduce_id = atoi(f.c_str());
-    if (!next_field(s, &pos, &f)) return false; r->remote_addr = strtoull(f.c_str(), nullptr, 10);
-    if (!next_field(s, &pos, &f)) return false; r->request_ptr = strtoull(f.c_str(), nullptr, 10);
-    if (!next_field(s, &pos, &f)) return false; r->chunk_size = atoi(f.c_str());
-    if (!next_field(s, &pos, &f)) return false; r->file_offset = atoll(f.c_str());
+    if (!next_field(s, &pos, &f)) return false;
+    r->map_offset = atoll(f.c_str());
+    if (!next_field(s, &pos, &f)) return false;
+    r->reduce_id = atoi(f.c_str());
+    if (!next_field(s, &pos, &f)) return false;
+    r->remote_addr = strtoull(f.c_str(), nullptr, 10);
+    if (!next_field(s, &pos, &f)) return false;
+    r->request_ptr = strtoull(f.c_str(), nullptr, 10);
+    if (!next_field(s, &pos, &f)) return false;
+    r->chunk_size = atoi(f.c_str());
+    if (!next_field(s, &pos, &f)) return false;
+    r->file_offset = atoll(f.c_str());
     if (!next_field(s, &pos, &r->path)) return false;
-    if (!next_field(s, &pos, &f)) return false; r->raw_length = atoll(f.c_str());
+    if (!next_field(s, &pos, &f)) return false;
+    r->raw_length = atoll(f.c_str());
     r->part_length = atoll(s.substr(pos).c_str());
     return true;
 }
@@ -176,10 +183,14 @@ std::string format_fetch_ack(const FetchAck& a) {
 bool parse_fetch_ack(const std::string& s, FetchAck* a) {
     size_t pos = 0;
     std::string f;
-    if (!next_field(s, &pos, &f)) return false; a->raw_length = atoll(f.c_str());
-    if (!next_field(s, &pos, &f)) return false; a->part_length = atoll(f.c_str());
-    if (!next_field(s, &pos, &f)) return false; a->sent = atoll(f.c_str());
-    if (!next_field(s, &pos, &f)) return false; a->file_offset = atoll(f.c_str());
+    if (!next_field(s, &pos, &f)) return false;
+    a->raw_length = atoll(f.c_str());
+    if (!next_field(s, &pos, &f)) return false;
+    a->part_length = atoll(f.c_str());
+    if (!next_field(s, &pos, &f)) return false;
+    a->sent = atoll(f.c_str());
+    if (!next_field(s, &pos, &f)) return false;
+    a->file_offset = atoll(f.c_str());
     if (!next_field(s, &pos, &a->path)) return false;
     return true;
 }
