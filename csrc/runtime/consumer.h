@@ -1,0 +1,245 @@
+// Consumer role ("NetMerger"): fetches one partition from every map output and streams the merged
+// key/value sequence to the reducer.
+//
+// Reference behaviour covered:
+//   * MergeManager_main / reduce_downcall_handler / finalize  (src/Merger/NetMergerMain.cc:44-77,
+//     src/Merger/reducer.cc:56-217,354-410): INIT -> comparator, codec, buffer sizing with page alignment
+//     and minimum check, memory pool; FETCH -> queue a map output; FINAL -> flag
+//   * calculateMemPool (src/Merger/reducer.cc:453-496): (num_kv_bufs + 10) buffer pairs; with
+//     compression the pair is split by mapred.rdma.compression.buffer.ratio
+//   * MergeManager online and hybrid modes (src/Merger/MergeManager.cc:47-365): fetching phase with a
+//     fetchOverMessage up-call every 20 segments, merging phase that emits blocks of whole records through
+//     dataFromUda; hybrid = sqrt(N) bounded groups (LPQs) merged to local spill files
+//     <dir>/uda.<task>.lpq-NNN, then a final merge (RPQ) over those files
+//   * MergeQueue / PriorityQueue (src/Merger/MergeQueue.h:126-427): binary min-heap on the current key
+//   * Segment double buffering, straddling-record join, next-chunk prefetch (src/Merger/StreamRW.cc:240-662)
+//   * block framing of compressed segments and the decompress thread
+//     (src/Merger/DecompressorWrapper.cc:27-383; Snappy/LZO via dlopen, SnappyDecompressor.cc, LzoDecompressor.cc)
+// The data structures are new: a segment is a pull-based byte source (network double buffer, file, or a
+// decompressing adaptor) under a record reader that joins straddling records in a carry buffer.
+#pragma once
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <list>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "compare.h"
+#include "protocol.h"
+#include "queues.h"
+#include "transport.h"
+#include "uda_rt.h"
+
+namespace uda {
+
+constexpr size_t kStagingBytes = 1u << 20;  // NETLEV_KV_POOL_EXPO 20: merged blocks handed to the host
+constexpr int kExtraBuffers = 10;           // EXTRA_RDMA_BUFFERS (src/Merger/reducer.cc:50)
+constexpr int kProgressEvery = 20;          // fetchOverMessage cadence (src/Merger/MergeManager.cc:124-130)
+
+// ---- byte sources -------------------------------------------------------------------------------------
+class ByteSource {
+public:
+    virtual ~ByteSource() = default;
+    // Next block of the logical stream; the previous block becomes invalid. false = end of stream.
+    // Throws UdaError when the underlying fetch failed.
+    virtual bool next_block(const uint8_t** data, size_t* len) = 0;
+};
+
+struct BufferPair {
+    uint8_t* buf[2];
+    size_t size[2];
+};
+
+// (num_kv_bufs + 10) pairs carved from one region (the reference registers it as one MR)
+class BufferPool {
+public:
+    BufferPool(int pairs, size_t size0, size_t size1);
+    ~BufferPool();
+    BufferPair borrow();  // blocks until a pair is free
+    void give_back(const BufferPair& p);
+    int pairs() const { return pairs_; }
+    size_t total_bytes() const { return total_; }
+
+private:
+    uint8_t* region_ = nullptr;
+    size_t total_ = 0;
+    int pairs_;
+    std::vector<BufferPair> free_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+};
+
+enum class Codec { NONE, SNAPPY, LZO };
+
+// Decompress one Hadoop codec block; returns false on corrupt input. Uses the system library when it
+// can be dlopen()ed (like the reference) and a built-in decoder otherwise (Snappy only).
+bool codec_decompress(Codec c, const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len, const HostCallbacks* host);
+Codec codec_for_class(const std::string& java_class);  // "null" -> NONE; unknown -> throws (fallback contract)
+bool snappy_uncompress_builtin(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len);
+size_t snappy_compress_literal(const uint8_t* in, size_t n, std::vector<uint8_t>* out);  // test helper: valid, uncompressed stream
+
+// One map output partition being fetched chunk by chunk into a borrowed buffer pair.
+class FetchSource : public ByteSource {
+public:
+    FetchSource(InputClient* client, BufferPool* pool, std::string host, FetchRequest first, size_t chunk_size);
+    ~FetchSource() override;
+    void start();                       // issue the first fetch
+    bool wait_first_chunk();            // true when the first chunk has landed (false: failed)
+    bool next_block(const uint8_t** data, size_t* len) override;
+    long long raw_length() const { return raw_len_; }
+    long long part_length() const { return part_len_; }
+    const std::string& map_id() const { return req_.map_id; }
+
+private:
+    enum State { EMPTY, FETCHING, READY, BUSY };
+    FetchRequest prepare(int slot);
+    void send(int slot, const FetchRequest& r);
+    InputClient* client_;
+    BufferPool* pool_;
+    std::string host_;
+    FetchRequest req_;
+    size_t chunk_;
+    BufferPair pair_{};
+    bool have_pair_ = false;
+    State state_[2] = {EMPTY, EMPTY};
+    size_t filled_[2] = {0, 0};
+    long long fetched_ = 0, requested_ = 0, part_len_ = -1, raw_len_ = -1;
+    int next_slot_ = 0;   // slot the consumer reads next
+    int busy_slot_ = -1;
+    bool failed_ = false;
+    std::mutex mu_;
+    std::condition_variable cv_;
+};
+
+// Hadoop block-compressed stream -> plain bytes: [u32 BE rawLen][u32 BE compLen][compLen bytes]...
+class DecompressingSource : public ByteSource {
+public:
+    DecompressingSource(std::unique_ptr<ByteSource> inner, Codec codec, long long raw_total, const HostCallbacks* host);
+    bool next_block(const uint8_t** data, size_t* len) override;
+
+private:
+    bool read_exact(uint8_t* dst, size_t n);
+    std::unique_ptr<ByteSource> inner_;
+    Codec codec_;
+    long long raw_left_;
+    const HostCallbacks* host_;
+    const uint8_t* cur_ = nullptr;
+    size_t cur_len_ = 0;
+    std::vector<uint8_t> comp_, plain_;
+};
+
+// Spill file written by an LPQ merge (plain merged-stream framing, EOF marker at the end)
+class FileSource : public ByteSource {
+public:
+    FileSource(std::string path, bool delete_on_close);
+    ~FileSource() override;
+    bool next_block(const uint8_t** data, size_t* len) override;
+
+private:
+    std::string path_;
+    bool del_;
+    FILE* f_ = nullptr;
+    std::vector<uint8_t> buf_;
+};
+
+// ---- records ------------------------------------------------------------------------------------------
+struct Record {
+    const uint8_t* key = nullptr; int klen = 0;
+    const uint8_t* val = nullptr; int vlen = 0;
+};
+
+// Iterates the records of one source; a record that straddles two blocks is joined in a carry buffer.
+class Segment {
+public:
+    Segment(std::unique_ptr<ByteSource> src, int id) : src_(std::move(src)), id_(id) {}
+    bool next();                      // advance; false at the EOF marker / end of stream
+    const Record& cur() const { return rec_; }
+    int id() const { return id_; }
+    ByteSource* source() { return src_.get(); }
+
+private:
+    bool refill();
+    std::unique_ptr<ByteSource> src_;
+    int id_;
+    const uint8_t* p_ = nullptr;
+    const uint8_t* end_ = nullptr;
+    std::vector<uint8_t> carry_;
+    Record rec_;
+    bool done_ = false;
+};
+
+// Binary min-heap of segments ordered by (current key, segment id)
+class MergeHeap {
+public:
+    explicit MergeHeap(KeyKind kind) : kind_(kind) {}
+    void insert(std::unique_ptr<Segment> s);   // primes the segment; empty segments are dropped
+    bool empty() const { return heap_.empty(); }
+    size_t size() const { return heap_.size(); }
+    const Record& top() const { return heap_.front()->cur(); }
+    void advance();                            // pop-or-sift after the top record has been consumed
+
+private:
+    bool less(const Segment* a, const Segment* b) const;
+    void sift_down(size_t i);
+    void sift_up(size_t i);
+    KeyKind kind_;
+    std::vector<std::unique_ptr<Segment>> heap_;
+};
+
+// ---- the reduce task ----------------------------------------------------------------------------------
+struct MemoryPlan {
+    int num_kv_bufs = 0;
+    size_t buffer_size = 0;    // page aligned chunk size used for fetches
+    size_t pair_size[2] = {0, 0};
+    int pairs = 0;
+};
+// throws UdaError("Not enough memory for rdma buffers") / ("RDMA Buffer is too small")
+MemoryPlan plan_memory(const InitParams& init, int num_kv_bufs, Codec codec, double compression_ratio, long long max_buf_cfg);
+
+class Consumer {
+public:
+    Consumer(const Options& opt, const HostCallbacks* host);
+    ~Consumer();
+    void start();                                  // MergeManager_main
+    void handle_command(const std::string& cmd);   // reduce_downcall_handler
+    void exit_msg();                               // reduce_exit_msg_handler -> finalize
+    // statistics for tests
+    uint64_t records_emitted() const { return emitted_.load(); }
+    int lpqs_spilled() const { return spilled_.load(); }
+
+private:
+    struct FetchOrder { std::string host, job, map; int reduce; };
+    void on_init(const HadoopCmd& cmd);
+    void merge_thread_main();
+    void merge_online();
+    void merge_hybrid();
+    // fetch `count` map outputs into `heap`; reports progress every kProgressEvery segments
+    void fetching_phase(MergeHeap* heap, int count, int* progress);
+    void merging_phase(MergeHeap* heap, const std::function<void(const uint8_t*, size_t)>& sink, bool final_stream);
+    std::unique_ptr<ByteSource> make_source(const FetchOrder& o);
+    void fail(const UdaError& e);
+
+    Options opt_;
+    const HostCallbacks* host_;
+    InitParams init_;
+    KeyKind key_kind_ = KeyKind::RAW_BYTES;
+    Codec codec_ = Codec::NONE;
+    MemoryPlan plan_;
+    std::unique_ptr<InputClient> client_;
+    std::unique_ptr<BufferPool> pool_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::list<FetchOrder> fetch_list_;
+    std::atomic<bool> stop_{false}, failed_{false}, initialised_{false};
+    std::thread merge_thread_;
+    std::vector<uint8_t> staging_[2];
+    std::atomic<uint64_t> emitted_{0};
+    std::atomic<int> spilled_{0};
+    int segment_seq_ = 0;
+};
+
+}  // namespace uda

@@ -1,0 +1,313 @@
+"""CPU tests of the C++ host runtime (libuda.so) through its C API: protocol goldens with the reference's
+quirks, queues, comparators, memory planning, Snappy, and the provider<->consumer plumbing path over TCP
+loop-back with Python playing Hadoop (BASELINE.json config 1 in miniature)."""
+import ctypes as C
+import os
+import random
+import struct
+import time
+
+import pytest
+
+from uda_b200 import bridge
+from uda_b200.oracle import kway_merge, merged_stream, parse_stream
+from uda_b200.utils import ifile, vint
+
+
+@pytest.fixture(scope="module")
+def L(built):
+    return bridge.lib()
+
+
+def _buf(n=4096):
+    return C.create_string_buffer(n)
+
+
+# ------------------------------------------------------------------------------------------ vint
+@pytest.mark.parametrize("v", [0, 1, 127, 128, -1, -112, -113, 255, 256, 65535, 65536, -129, 2**31 - 1, -(2**31), 2**63 - 1, -(2**63), 10, 90])
+def test_vint_matches_python(L, v):
+    out = _buf(16)
+    n = L.uda_rt_vint_encode(v, out)
+    assert out.raw[:n] == vint.encode_vlong(v) and n == L.uda_rt_vint_size(v)
+    got = C.c_longlong()
+    assert L.uda_rt_vint_decode(out.raw[:n], n, C.byref(got)) == n and got.value == v
+    assert L.uda_rt_vint_decode(out.raw[:n], max(0, n - 1), C.byref(got)) == 0  # truncated
+
+
+# ------------------------------------------------------------------------------------------ commands
+def _parse(L, s):
+    out = _buf()
+    n = L.uda_rt_parse_cmd(s.encode(), out, len(out))
+    if n < 0:
+        return None
+    parts = out.value.decode().split("\n")
+    return int(parts[0]), int(parts[1]), parts[2:]
+
+
+def test_command_golden(L):
+    assert _parse(L, "") == (1, 0, [])                       # empty string == EXIT
+    assert _parse(L, "1:0") == (1, 0, [])
+    assert _parse(L, "5:4:host1:job_1:attempt_1_m_0:3") == (5, 4, ["host1", "job_1", "attempt_1_m_0", "3"])
+    # the last parameter swallows the rest of the string, colons included
+    assert _parse(L, "3:7:a:/path/with:colons:inside") == (3, 7, ["a", "/path/with:colons:inside"])
+    assert _parse(L, "nocolon") is None
+    assert _parse(L, "4:7:onlyone") is None                  # announces 3 params, provides 1
+    s = bridge.form_cmd(bridge.FETCH, ["h", "j", "m", "2"])
+    assert s == "5:4:h:j:m:2"
+    arr = (C.c_char_p * 4)(b"h", b"j", b"m", b"2")
+    out = _buf()
+    L.uda_rt_form_cmd(4, 4, arr, out, len(out))
+    assert out.value.decode() == s
+
+
+def test_options_golden(L):
+    def parse(argv):
+        arr = (C.c_char_p * len(argv))(*[a.encode() for a in argv])
+        out = (C.c_longlong * 7)()
+        d = _buf(512)
+        L.uda_rt_parse_options(len(argv), arr, out, d, len(d))
+        return list(out), d.value.decode()
+
+    # Java passes no program name, so getopt skips "-w": its value never takes effect (reference quirk)
+    o, d = parse(["-w", "99", "-r", "9012", "-a", "2", "-m", "1", "-g", "/logs/", "-s", "1024"])
+    assert o[0] == 256 and o[1] == 9012 and o[2] == 2 and o[3] == 1 and o[4] == 1024 * 1024 and d == "/logs/"
+    o, _ = parse(["prog", "-w", "99", "-s", "5"])            # with a program name -w is honoured
+    assert o[0] == 99 and o[4] == 4096                       # 5 KiB -> rounded down to 4 KiB
+    o, _ = parse(["prog", "-s", "1"])
+    assert o[4] == 4096                                      # minimum one 4 KiB block
+    o, _ = parse(["prog", "--dataport", "777", "--rdmabufsize=33", "-t", "6", "-b", "x"])
+    assert o[1] == 777 and o[4] == 32 * 1024 and o[5] == 6
+
+
+def test_fetch_request_and_ack_golden(L):
+    req = "job_201_0001:attempt_201_0001_m_000003_0:1048576:7:140000:42:1048576:8192:/data/x/file.out:5000:5004"
+    out = _buf()
+    assert L.uda_rt_fetch_request_roundtrip(req.encode(), out, len(out)) == len(req) and out.value.decode() == req
+    assert L.uda_rt_fetch_request_roundtrip(b"a:b:c", out, len(out)) == -1
+    long_path = "/p" * 400
+    assert L.uda_rt_fetch_request_roundtrip(f"j:m:0:1:2:3:4:5:{long_path}:6:7".encode(), out, len(out)) == -3  # >= 800 bytes
+    ack = "5000:5004:4096:8192:/data/x/file.out:"
+    assert L.uda_rt_fetch_ack_roundtrip(ack.encode(), out, len(out)) == len(ack) and out.value.decode() == ack
+    assert L.uda_rt_fetch_ack_roundtrip(b"1:2:3", out, len(out)) == -1
+
+
+# ------------------------------------------------------------------------------------------ comparators / queues / planning
+def test_comparators(L):
+    assert L.uda_rt_key_kind(b"org.apache.hadoop.io.Text") == 1
+    assert L.uda_rt_key_kind(b"org.apache.hadoop.io.LongWritable") == 0
+    assert L.uda_rt_key_kind(b"org.apache.hadoop.hbase.io.ImmutableBytesWritable") == 2
+    assert L.uda_rt_key_kind(b"org.apache.hadoop.io.DoubleWritable") == -1
+    t = lambda w: vint.encode_vlong(len(w)) + w
+    cmp = lambda k, a, b: L.uda_rt_compare_keys(k, a, len(a), b, len(b))
+    assert cmp(1, t(b"ab"), t(b"abc")) < 0 and cmp(1, t(b"b"), t(b"abc")) > 0 and cmp(1, t(b"x" * 200), t(b"x" * 200)) == 0
+    assert cmp(0, b"\x00\x01", b"\x00\x02") < 0 and cmp(0, b"\xff", b"\x01") > 0   # unsigned bytes
+    assert cmp(2, b"\x00\x00\x00\x09zz", b"\x00\x00\x00\x01zza") < 0
+
+
+def test_queues_selftest(L):
+    assert L.uda_rt_selftest_queues() == 0
+
+
+def test_memory_plan(L):
+    out = (C.c_longlong * 4)()
+    MiB = 1 << 20
+    assert L.uda_rt_plan_memory(10, MiB, 16 * 1024, 1 << 30, 0, 0.2, out) == 0
+    assert list(out) == [MiB, 20, MiB, MiB]                  # (num_maps + 10) pairs of full-size buffers
+    # shuffle memory too small for 1 MiB buffers: shrink, page aligned
+    assert L.uda_rt_plan_memory(100, MiB, 16 * 1024, 100 * MiB, 0, 0.2, out) == 0
+    assert out[0] == (100 * MiB // 200) // 4096 * 4096
+    assert L.uda_rt_plan_memory(1000, MiB, 64 * 1024, 10 * MiB, 0, 0.2, out) == 1     # "Not enough memory for rdma buffers"
+    assert L.uda_rt_plan_memory(1, 1000, 16, 1 << 30, 0, 0.2, out) == 2              # "RDMA Buffer is too small" (< one page)
+    assert L.uda_rt_plan_memory(10, MiB, 16 * 1024, 1 << 30, 1, 0.2, out) == 0
+    assert out[0] == int(2 * MiB * 0.2) // 4096 * 4096
+
+
+def test_snappy_builtin(L):
+    data = bytes(random.Random(0).getrandbits(8) for _ in range(70000))
+    comp = _buf(len(data) + 1024)
+    n = L.uda_rt_snappy_store(data, len(data), comp, len(comp))
+    out = _buf(len(data))
+    assert L.uda_rt_snappy_uncompress(comp.raw[:n], n, out, len(data)) == 0 and out.raw == data
+    # hand-made stream with copies: "abcd" + copy(offset 4, len 8) + 2-byte-offset copy
+    stream = bytes([16]) + bytes([3 << 2]) + b"abcd" + bytes([((8 - 4) << 2) | 1, 4]) + bytes([(4 - 1) << 2 | 2, 12, 0])
+    out = _buf(16)
+    assert L.uda_rt_snappy_uncompress(stream, len(stream), out, 16) == 0 and out.raw == b"abcdabcdabcdabcd"
+    assert L.uda_rt_snappy_uncompress(stream[:-1], len(stream) - 1, out, 16) == -1
+
+
+# ------------------------------------------------------------------------------------------ plumbing end to end
+def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress=None):
+    rng = random.Random(seed)
+    mofs = {}
+    truth = [[] for _ in range(n_reduces)]
+    for m in range(n_maps):
+        parts = []
+        for r in range(n_reduces):
+            n = rng.randint(0, recs_per_part)
+            recs = sorted(((bytes(rng.getrandbits(8) for _ in range(key_len)), bytes(rng.getrandbits(8) for _ in range(rng.randint(0, 200))))
+                           for _ in range(n)), key=lambda kv: kv[0])
+            parts.append(recs)
+            truth[r].append(recs)
+        if compress is None:
+            data, index = ifile.write_mof(parts)
+        else:
+            out, idx = bytearray(), []
+            for recs in parts:
+                plain = ifile.encode_segment(recs, with_crc=False)
+                seg = bytearray()
+                for off in range(0, len(plain), 3000):      # several codec blocks per segment
+                    blk = plain[off:off + 3000]
+                    seg += struct.pack(">II", len(blk), len(compress(blk))) + compress(blk)
+                seg += b"\0\0\0\0"                           # trailing checksum bytes (ignored by readers)
+                idx.append(ifile.IndexRecord(len(out), len(plain), len(seg)))
+                out += seg
+            data, index = bytes(out), ifile.write_index(idx)
+        path = os.path.join(tmp, f"map_{m}.out")
+        with open(path, "wb") as f:
+            f.write(data)
+        mofs[f"attempt_m_{m:06d}_0"] = (path, ifile.read_index(index))
+    return mofs, truth
+
+
+def _run_job(tmp, n_maps, n_reduces, recs, approach=1, buf_kb=8, key_class="org.apache.hadoop.io.LongWritable", key_len=10,
+             lpq_size=0, compress=None, codec="null", seed=1):
+    mofs, truth = _make_mofs(tmp, n_maps, n_reduces, recs, seed, key_len, compress)
+
+    def get_path(job, mapid, reduce):
+        path, idx = mofs[mapid]
+        r = idx[reduce]
+        return r.start_offset, r.raw_length, r.part_length, path
+
+    prov = bridge.NativeRole(False, bridge.build_argv(port=0, buf_kb=buf_kb, provider=True), get_path=get_path)
+    assert not prov.failed, prov.last_error
+    port = prov.port
+    assert port > 0
+    streams, consumers = [], []
+    try:
+        for r in range(n_reduces):
+            cons = bridge.NativeRole(True, bridge.build_argv(port=port, approach=approach, buf_kb=buf_kb))
+            consumers.append(cons)
+            init = [str(n_maps), "job_1", f"attempt_r_{r:06d}_0", str(lpq_size), str(buf_kb * 1024), str(4096), key_class, codec,
+                    str(256 * 1024), str(64 << 20), "1", tmp]
+            assert cons.command(bridge.form_cmd(bridge.INIT, init)) == 0, cons.last_error
+            for mapid in mofs:
+                assert cons.command(bridge.form_cmd(bridge.FETCH, ["127.0.0.1", "job_1", mapid, str(r)])) == 0
+        for r, cons in enumerate(consumers):
+            deadline = time.time() + 60
+            want = sum(len(x) for x in truth[r])
+            while time.time() < deadline and not cons.failed:
+                s = cons.stream()
+                if s.endswith(b"\xff\xff") and cons.stat("records_emitted") == want:
+                    break
+                time.sleep(0.02)
+            assert not cons.failed and cons.failures == 0, cons.last_error
+            streams.append(cons.stream())
+            assert all(len(b) <= (1 << 20) for b in cons.blocks)
+            assert cons.fetch_over >= 1
+        return streams, truth, consumers, prov
+    finally:
+        for c in consumers:
+            c.reduce_exit()
+            c.close()
+        prov.command(bridge.form_cmd(bridge.EXIT, []))
+        prov.close()
+
+
+def test_plumbing_online_4_maps_2_reducers(built, tmp_path):
+    streams, truth, consumers, prov = _run_job(str(tmp_path), 4, 2, 400)
+    for r, s in enumerate(streams):
+        want = list(kway_merge(truth[r]))
+        assert parse_stream(s) == want
+        assert s == merged_stream(want)
+
+
+def test_plumbing_small_buffers_straddling_records(built, tmp_path):
+    # 4 KiB chunks with values up to 200 B: many records straddle chunk boundaries
+    streams, truth, _, _ = _run_job(str(tmp_path), 7, 1, 900, buf_kb=4, seed=5)
+    assert parse_stream(streams[0]) == list(kway_merge(truth[0]))
+
+
+def test_plumbing_hybrid_spills_lpqs(built, tmp_path):
+    streams, truth, consumers, _ = _run_job(str(tmp_path), 9, 1, 300, approach=2, seed=9)
+    assert parse_stream(streams[0]) == list(kway_merge(truth[0]))
+    assert not [f for f in os.listdir(tmp_path) if ".lpq-" in f]       # spill files are deleted once consumed
+
+
+def test_plumbing_text_keys(built, tmp_path):
+    rng = random.Random(3)
+    # Text keys: ordering must ignore the VInt length prefix
+    def text(n):
+        w = bytes(rng.choice(b"abc") for _ in range(n))
+        return vint.encode_vlong(len(w)) + w
+    tmp = str(tmp_path)
+    runs = [sorted(((text(rng.randint(0, 5)), b"v") for _ in range(50)), key=lambda kv: kv[0][1:]) for _ in range(3)]
+    mofs = {}
+    for m, recs in enumerate(runs):
+        data, index = ifile.write_mof([recs])
+        p = os.path.join(tmp, f"t{m}.out")
+        open(p, "wb").write(data)
+        mofs[f"m{m}"] = (p, ifile.read_index(index))
+    prov = bridge.NativeRole(False, bridge.build_argv(port=0, provider=True),
+                             get_path=lambda j, m, r: (mofs[m][1][r].start_offset, mofs[m][1][r].raw_length, mofs[m][1][r].part_length, mofs[m][0]))
+    cons = bridge.NativeRole(True, bridge.build_argv(port=prov.port))
+    try:
+        init = ["3", "job_1", "attempt_r_0", "0", str(1 << 20), "4096", "org.apache.hadoop.io.Text", "null", "262144", str(64 << 20), "0"]
+        assert cons.command(bridge.form_cmd(bridge.INIT, init)) == 0
+        for m in mofs:
+            cons.command(bridge.form_cmd(bridge.FETCH, ["127.0.0.1", "job_1", m, "0"]))
+        t0 = time.time()
+        while not cons.stream().endswith(b"\xff\xff") and time.time() - t0 < 30:
+            time.sleep(0.02)
+        got = parse_stream(cons.stream())
+        assert [k[1:] for k, _ in got] == sorted(k[1:] for run in runs for k, _ in run)
+    finally:
+        cons.reduce_exit(); cons.close(); prov.close()
+
+
+def test_plumbing_snappy_compressed_segments(built, tmp_path, L):
+    def store(b):
+        out = _buf(len(b) + 64)
+        n = L.uda_rt_snappy_store(bytes(b), len(b), out, len(out))
+        return out.raw[:n]
+    streams, truth, _, _ = _run_job(str(tmp_path), 3, 1, 200, compress=store, codec="org.apache.hadoop.io.compress.SnappyCodec", seed=4)
+    assert parse_stream(streams[0]) == list(kway_merge(truth[0]))
+
+
+def test_unsupported_key_class_fails_init_for_fallback(built):
+    cons = bridge.NativeRole(True, bridge.build_argv(port=1))
+    try:
+        init = ["1", "job_1", "attempt_r_0", "0", str(1 << 20), "4096", "org.apache.hadoop.io.DoubleWritable", "null", "0", str(1 << 20), "0"]
+        assert cons.command(bridge.form_cmd(bridge.INIT, init)) == -1       # exception in init => Java falls back
+        assert cons.failed and "unsupported type" in cons.last_error
+        assert cons.command(bridge.form_cmd(bridge.FETCH, ["h", "j", "m", "0"])) == 0   # ignored after the failure
+    finally:
+        cons.close()
+
+
+def test_missing_provider_raises_failure_upcall(built):
+    cons = bridge.NativeRole(True, bridge.build_argv(port=1))   # nothing listens on port 1
+    try:
+        init = ["1", "job_1", "attempt_r_0", "0", str(1 << 20), "4096", "org.apache.hadoop.io.LongWritable", "null", "0", str(64 << 20), "0"]
+        assert cons.command(bridge.form_cmd(bridge.INIT, init)) == 0
+        cons.command(bridge.form_cmd(bridge.FETCH, ["127.0.0.1", "job_1", "m0", "0"]))
+        t0 = time.time()
+        while cons.failures == 0 and time.time() - t0 < 20:
+            time.sleep(0.02)
+        assert cons.failures == 1                                # failureInUda: native-thread failure => fallback
+    finally:
+        cons.close()
+
+
+def test_log_line_contract(built, tmp_path):
+    prov = bridge.NativeRole(False, bridge.build_argv(port=0, provider=True), log_level=4)
+    cons = bridge.NativeRole(True, bridge.build_argv(port=prov.port), log_level=4)
+    try:
+        ver = bridge.lib().uda_rt_version().decode()
+        assert any(m.startswith(f"The version is {ver}") for _, m in prov.logs)
+        assert any(m.startswith(f"UDA version is {ver}") for _, m in cons.logs)
+        init = ["1", "job_1", "attempt_r_0", "0", str(1 << 20), "4096", "org.apache.hadoop.io.LongWritable", "null", "0", str(64 << 20), "0"]
+        cons.command(bridge.form_cmd(bridge.INIT, init))
+        assert any("After RDMA buffers registration: buffer1 = 1048576 bytes , buffer2 = 1048576 bytes , buffers count = 11" in m
+                   for _, m in cons.logs)
+    finally:
+        cons.close(); prov.close()
