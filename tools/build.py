@@ -96,6 +96,14 @@ def build(verbose: bool = False) -> dict:
         rlib = LIB_DIR / "libuda.so"
         _run([CXX, "-shared", "-pthread", "-o", str(rlib), *map(str, cc_objs), "-ldl"])
         out["runtime"] = rlib
+    # native test programs (mock-JVM test of the JNI bridge)
+    bin_dir = ROOT / "build" / "bin"
+    bin_dir.mkdir(parents=True, exist_ok=True)
+    for src in sorted((ROOT / "tests" / "native").glob("*.cc")):
+        exe = bin_dir / src.stem
+        if cc_objs:
+            _run([CXX, *CXX_FLAGS, str(src), "-o", str(exe), f"-L{LIB_DIR}", "-luda", f"-Wl,-rpath,{LIB_DIR}", "-ldl"])
+            out[src.stem] = exe
     if verbose:
         for o in cu_objs:
             log = o.with_suffix(".log")
