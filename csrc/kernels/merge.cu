@@ -20,6 +20,7 @@
 // Output order is (key, run, index-in-run): stable by run, one of the orders the reference heap can
 // produce. The sorted entries drive the record gather in gather.cu.
 #include "common.cuh"
+#include "merge_tree.cuh"
 #include "../../include/uda_b200.h"
 
 namespace uda {
@@ -267,87 +268,6 @@ struct MergeSmem {
     uint32_t* offB;  // [k+1]
 };
 
-__device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_t* total_out) {
-    __shared__ uint32_t ws[MG_THREADS / 32];
-    __shared__ uint32_t tot;
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    uint32_t x = v;
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-        if (lane >= o) x += y;
-    }
-    __syncthreads();  // protect ws/tot from the previous call
-    if (lane == 31) ws[w] = x;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t acc = 0;
-        for (int i = 0; i < MG_THREADS / 32; ++i) { uint32_t t = ws[i]; ws[i] = acc; acc += t; }
-        tot = acc;
-    }
-    __syncthreads();
-    *total_out = tot;
-    return ws[w] + x - v;
-}
-
-// one level of the in-shared-memory merge tree: lists (soff, L) in src -> pairs merged into dst
-__device__ __forceinline__ void merge_level(const Entry* __restrict__ src, const uint32_t* __restrict__ soff, int L,
-                                            Entry* __restrict__ dst, uint32_t* __restrict__ doff, uint32_t total) {
-    const int Lp = (L + 1) >> 1;
-    for (int p = threadIdx.x; p <= Lp; p += MG_THREADS) doff[p] = p < Lp ? soff[2 * p] : total;
-    const uint32_t o = threadIdx.x * MG_VT;
-    if (o < total) {
-        // pair containing output position o: largest p with soff[2p] <= o
-        int plo = 0, phi = Lp - 1;
-        while (plo < phi) {
-            int mid = (plo + phi + 1) >> 1;
-            if (soff[2 * mid] <= o) plo = mid; else phi = mid - 1;
-        }
-        int p = plo;
-        uint32_t a0 = soff[2 * p];
-        uint32_t a1 = soff[min(2 * p + 1, L)];
-        uint32_t b1 = soff[min(2 * p + 2, L)];
-        // merge path on diagonal d
-        uint32_t d = o - a0, la = a1 - a0, lb = b1 - a1;
-        uint32_t lo = d > lb ? d - lb : 0u, hi = d < la ? d : la;
-        while (lo < hi) {
-            uint32_t mid = (lo + hi) >> 1;
-            Entry ea = src[a0 + mid], eb = src[a1 + (d - 1 - mid)];
-            if (!entry_less(eb, ea)) lo = mid + 1; else hi = mid;  // A[mid] <= B[d-1-mid]
-        }
-        uint32_t ia = a0 + lo, ib = a1 + (d - lo);
-        uint32_t ea_end = a1, eb_end = b1;
-        bool ha = ia < ea_end, hb = ib < eb_end;
-        Entry ea, eb;
-        if (ha) ea = src[ia];
-        if (hb) eb = src[ib];
-#pragma unroll
-        for (int t = 0; t < MG_VT; ++t) {
-            uint32_t pos = o + t;
-            if (pos >= total) break;
-            if (!ha && !hb) {  // pair exhausted: the next non-empty pair starts exactly at pos
-                do { ++p; } while (soff[min(2 * p + 2, L)] <= pos);
-                ia = soff[2 * p];
-                ea_end = soff[min(2 * p + 1, L)];
-                ib = ea_end;
-                eb_end = soff[min(2 * p + 2, L)];
-                ha = ia < ea_end; hb = ib < eb_end;
-                if (ha) ea = src[ia];
-                if (hb) eb = src[ib];
-            }
-            bool takeA = ha && (!hb || !entry_less(eb, ea));
-            if (takeA) {
-                dst[pos] = ea;
-                ++ia; ha = ia < ea_end;
-                if (ha) ea = src[ia];
-            } else {
-                dst[pos] = eb;
-                ++ib; hb = ib < eb_end;
-                if (hb) eb = src[ib];
-            }
-        }
-    }
-}
-
 // load slices [lo[r],hi[r]) of every run with TMA, merge them, write `total` sorted entries to out
 __device__ __forceinline__ void merge_one_tile(const Entry* __restrict__ E, const MergeSmem& sm, int k, uint32_t total,
                                                Entry* __restrict__ out, uint64_t* mbar, uint32_t& phase) {
@@ -356,7 +276,7 @@ __device__ __forceinline__ void merge_one_tile(const Entry* __restrict__ E, cons
     uint32_t mine = 0;
     for (int r = r0; r < r1; ++r) mine += sm.hi[r] - sm.lo[r];
     uint32_t tot;
-    uint32_t base = block_exclusive_scan_256(mine, &tot);
+    uint32_t base = block_exclusive_scan<MG_THREADS>(mine, &tot);
     for (int r = r0; r < r1; ++r) { sm.offA[r] = base; base += sm.hi[r] - sm.lo[r]; }
     if (threadIdx.x == 0) {
         sm.offA[k] = total;
@@ -375,7 +295,7 @@ __device__ __forceinline__ void merge_one_tile(const Entry* __restrict__ E, cons
     uint32_t* soff = sm.offA; uint32_t* doff = sm.offB;
     int L = k;
     while (L > 1) {
-        merge_level(src, soff, L, dst, doff, total);
+        merge_level<MG_THREADS, MG_VT>(src, soff, L, dst, doff, total);
         __syncthreads();
         Entry* t = src; src = dst; dst = t;
         uint32_t* u = soff; soff = doff; doff = u;

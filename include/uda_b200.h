@@ -78,6 +78,16 @@ int uda_kway_merge_entries(const void* entries, const long long* run_off_dev, in
 int uda_merge_runs_fixed(const UdaRunDesc* runs_dev, const long long* run_off_dev, int nruns, long long n,
                          long long max_nrec, int stride, int key_off, int key_len, void* entries_tmp,
                          void* sorted_out, void* scratch, cudaStream_t stream);
+/* Fused fixed-stride merge that reads and writes every record exactly once (sampled k-way merge-path
+ * partition, TMA-staged record tiles, in-shared-memory merge tree, records stored straight to their merged
+ * position). out: n*stride bytes (+2 for the EOF marker). align2 = 1 when stride, key_off, every run base
+ * and `out` are even (TeraSort). Runs need 32 readable bytes after their last record. */
+long long uda_merge_records_scratch_bytes(long long n, int nruns);
+int uda_merge_records_supported(int nruns, long long n, int stride, int key_len);
+int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, long long n, long long max_nrec, int stride,
+                            int key_off, int key_len, int align2, void* out, int write_eof, void* scratch,
+                            cudaStream_t stream);
+int uda_merge_records_stats(const void* scratch, unsigned long long* out2_host, cudaStream_t stream);
 /* synchronises the stream; out2_host = {oversize buckets, bisection iterations} of the last merge */
 int uda_merge_stats(const void* scratch, unsigned long long* out2_host, cudaStream_t stream);
 

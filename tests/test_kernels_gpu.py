@@ -223,6 +223,40 @@ def test_kway_merge_and_gather(K, sizes, key_bits):
     assert bytes(host[n * 102: n * 102 + 2]) == b"\xff\xff"
 
 
+@pytest.mark.parametrize("sizes,key_bits,odd", [
+    ([1000], 0, False), ([0, 5, 0], 0, False), ([3000, 1, 2500, 0, 4000], 0, False), ([20000] * 24, 0, False), ([700] * 100, 0, False),
+    ([6000, 7000, 5000], 3, False),   # 8 distinct keys: oversize buckets -> (key, run, index) bisection
+    ([4000] * 9, 10, False), ([5000, 3000, 4000], 0, True),  # odd base addresses: byte-granular path
+])
+def test_fused_record_merge(K, sizes, key_bits, odd):
+    dev = _dev()
+    bufs, host_runs = _make_runs(K, sizes, seed=23, key_bits=key_bits)
+    k, n = len(sizes), sum(sizes)
+    shift = 1 if odd else 0
+    if odd:  # shift every run by one byte
+        nb = []
+        for b in bufs:
+            c = torch.zeros(b.numel() + 16, dtype=torch.uint8, device=dev)
+            c[1:1 + b.numel()] = b
+            nb.append(c)
+        bufs = nb
+    assert K.merge_records_supported(k, n, 102, 10)
+    desc, run_off = K.make_run_descs([b.data_ptr() + K.GATHER_SLACK + shift for b in bufs], sizes)
+    out = torch.zeros(n * 102 + 2 + 64, dtype=torch.uint8, device=dev)
+    scratch = torch.empty(K.merge_records_scratch_bytes(n, k), dtype=torch.uint8, device=dev)
+    K.merge_records_fixed(K.to_device_struct(desc, dev), k, n, max(sizes), 102, 2, 10, out, scratch, write_eof=True, align2=not odd)
+    fb, iters = K.merge_records_stats(scratch)
+    w0 = np.concatenate([_entries_np(h, run=r)[0] for r, h in enumerate(host_runs)]) if n else np.zeros(0, np.uint64)
+    w1 = np.concatenate([_entries_np(h, run=r)[1] for r, h in enumerate(host_runs)]) if n else np.zeros(0, np.uint64)
+    order = _sort_order(w0, w1)
+    allrec = np.concatenate(host_runs) if n else np.zeros((0, 102), np.uint8)
+    host = out.cpu().numpy()
+    assert (host[: n * 102].reshape(n, 102) == allrec[order]).all()
+    assert bytes(host[n * 102: n * 102 + 2]) == b"\xff\xff"
+    if key_bits == 3:
+        assert fb > 0 and iters > 0
+
+
 @pytest.mark.parametrize("stride", [16, 30, 100, 102, 257])
 def test_gather_generic_strides(K, stride):
     dev = _dev()

@@ -121,6 +121,27 @@ def merge_runs_fixed(run_descs_dev: torch.Tensor, run_off_dev: torch.Tensor, nru
           "uda_merge_runs_fixed")
 
 
+def merge_records_supported(nruns: int, n: int, stride: int, key_len: int) -> bool:
+    return bool(kernels().uda_merge_records_supported(nruns, n, stride, key_len))
+
+
+def merge_records_scratch_bytes(n: int, nruns: int) -> int:
+    return int(kernels().uda_merge_records_scratch_bytes(n, nruns))
+
+
+def merge_records_fixed(run_descs_dev: torch.Tensor, nruns: int, n: int, max_nrec: int, stride: int, key_off: int, key_len: int,
+                        out: torch.Tensor, scratch: torch.Tensor, write_eof: bool = True, align2: bool = True) -> None:
+    """Fused fixed-stride k-way merge: every record is read once and written once."""
+    check(kernels().uda_merge_records_fixed(run_descs_dev.data_ptr(), nruns, n, max_nrec, stride, key_off, key_len, int(align2),
+                                            out.data_ptr(), int(write_eof), scratch.data_ptr(), _stream()), "uda_merge_records_fixed")
+
+
+def merge_records_stats(scratch: torch.Tensor) -> Tuple[int, int]:
+    out = (C.c_ulonglong * 2)()
+    check(kernels().uda_merge_records_stats(scratch.data_ptr(), out, _stream()), "uda_merge_records_stats")
+    return int(out[0]), int(out[1])
+
+
 def merge_stats(scratch: torch.Tensor) -> Tuple[int, int]:
     out = (C.c_ulonglong * 2)()
     check(kernels().uda_merge_stats(scratch.data_ptr(), out, _stream()), "uda_merge_stats")

@@ -19,11 +19,18 @@ from . import kernels as K
 
 
 class DeviceMerger:
-    def __init__(self, max_records: int, max_runs: int, stride: int, device, out_bytes: Optional[int] = None):
+    def __init__(self, max_records: int, max_runs: int, stride: int, device, out_bytes: Optional[int] = None,
+                 fused: Optional[bool] = None, key_len: int = 10):
         self.device, self.stride, self.max_records, self.max_runs = device, stride, max_records, max_runs
-        self.entries = torch.empty((max(max_records, 1), 2), dtype=torch.int64, device=device)
-        self.sorted = torch.empty_like(self.entries)
-        self.scratch = torch.empty(K.merge_scratch_bytes(max_records, max_runs), dtype=torch.uint8, device=device)
+        # fused record merge (one read + one write per record) when the shape allows it, else the
+        # entry pipeline (key normalise -> entry merge -> gather)
+        self.fused = K.merge_records_supported(max_runs, max_records, stride, key_len) if fused is None else fused
+        if self.fused:
+            self.scratch = torch.empty(K.merge_records_scratch_bytes(max_records, max_runs), dtype=torch.uint8, device=device)
+        else:
+            self.entries = torch.empty((max(max_records, 1), 2), dtype=torch.int64, device=device)
+            self.sorted = torch.empty_like(self.entries)
+            self.scratch = torch.empty(K.merge_scratch_bytes(max_records, max_runs), dtype=torch.uint8, device=device)
         ob = (max_records * stride + 2 if out_bytes is None else out_bytes)
         self.out = torch.empty(ob + 64, dtype=torch.uint8, device=device)
         self.n = 0
@@ -38,6 +45,7 @@ class DeviceMerger:
         self.run_descs_dev = K.to_device_struct(run_descs, self.device)
         self.run_off_dev = torch.from_numpy(run_off.astype(np.int64)).to(self.device)
         self.run_base_dev = torch.from_numpy(run_base.astype(np.uint64).view(np.int64)).to(self.device)
+        self.align2 = bool(self.stride % 2 == 0 and not (np.asarray(run_base, dtype=np.uint64) & np.uint64(1)).any())
 
     def merge_fixed(self, key_off: int = 2, key_len: int = 10, write_eof: bool = True,
                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -45,11 +53,15 @@ class DeviceMerger:
         ``self.out``)."""
         n = self.n
         out = self.out if out is None else out
+        if self.fused:
+            K.merge_records_fixed(self.run_descs_dev, self.nruns, n, self.max_nrec, self.stride, key_off, key_len, out,
+                                  self.scratch, write_eof=write_eof, align2=self.align2)
+            return out[: n * self.stride + (2 if write_eof else 0)]
         if n:
             K.merge_runs_fixed(self.run_descs_dev, self.run_off_dev, self.nruns, n, self.max_nrec, self.stride, key_off, key_len,
                                self.entries, self.sorted, self.scratch)
         K.gather_fixed(self.sorted, n, self.run_base_dev, self.stride, out, write_eof)
         return out[: n * self.stride + (2 if write_eof else 0)]
 
-    #: kernels launched by one merge_fixed() call (range, extract+hist, 3 scan, partition, tiles, gather, eof)
-    LAUNCHES_PER_MERGE = 9
+    #: kernels launched by one fused merge_fixed() call (range, sample-hist, 3 scan, partition, sizes, 3 scan, merge, eof)
+    LAUNCHES_PER_MERGE = 12
