@@ -28,10 +28,23 @@
 
 namespace uda {
 
+// Tuning (measured on B200, 125 M records, k = 8; ms per TeraSort step incl. the 4.4 ms push):
+//   VT=3 / 2 CTAs per SM 13.95   VT=2 / 3 CTAs 13.53   VT=4 / 1 CTA 17.76   VT=2 / 3 CTAs, 128 merge threads 13.91
+#ifndef UDA_FR_VT
+#define UDA_FR_VT 2
+#endif
+#ifndef UDA_FR_MERGE_THREADS
+#define UDA_FR_MERGE_THREADS 256
+#endif
+#ifndef UDA_FR_CTAS
+#define UDA_FR_CTAS 3
+#endif
 constexpr int FR_THREADS = 256;
-constexpr int FR_VT = 3;
-constexpr int FR_TILE = FR_THREADS * FR_VT;  // 768 record slots per tile
-constexpr int FR_TARGET = 576;               // target bucket size: leaves 192 slots for sampling error
+constexpr int FR_VT = UDA_FR_VT;
+constexpr int FR_TILE = FR_THREADS * FR_VT;  // record slots per tile (512 by default)
+constexpr int FR_MERGE_THREADS = UDA_FR_MERGE_THREADS;   // threads that run the merge tree (fewer = more items per thread)
+constexpr int FR_MERGE_VT = FR_TILE / FR_MERGE_THREADS;
+constexpr int FR_TARGET = FR_TILE * 3 / 4;   // target bucket size: a quarter of the tile absorbs the sampling error
 constexpr int FR_SAMPLE = 8;
 constexpr int FR_NB_LOG = 22;
 constexpr int FR_NB = 1 << FR_NB_LOG;
@@ -187,10 +200,11 @@ __device__ __forceinline__ void mbar_expect_tx_only(uint64_t* bar, uint32_t byte
     asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 
-template <bool ALIGN2>
-__device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ runs, const FrSmem& sm, int k, int stride,
+template <bool ALIGN2, int STRIDE>
+__device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ runs, const FrSmem& sm, int k, int stride_rt,
                                                 int key_off, int key_len, uint32_t total, uint8_t* __restrict__ out,
                                                 uint64_t* mbar, uint32_t& phase) {
+    const int stride = STRIDE > 0 ? STRIDE : stride_rt;
     const int tid = threadIdx.x;
     const int rpt = (k + FR_THREADS - 1) / FR_THREADS;
     const int r0 = tid * rpt, r1 = min(k, r0 + rpt);
@@ -254,7 +268,7 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
     uint32_t* soff = sm.soff; uint32_t* doff = sm.doff;
     int L = k;
     while (L > 1) {
-        merge_level<FR_THREADS, FR_VT>(src, soff, L, dst, doff, total);
+        if (tid < FR_MERGE_THREADS) merge_level<FR_MERGE_THREADS, FR_MERGE_VT>(src, soff, L, dst, doff, total);
         __syncthreads();
         Entry* te = src; src = dst; dst = te;
         uint32_t* tu = soff; soff = doff; doff = tu;
@@ -288,6 +302,7 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
     const uint32_t span = total * (uint32_t)stride;
     const uint32_t head = (uint32_t)((16u - ((uintptr_t)out & 15u)) & 15u) < span ? (uint32_t)((16u - ((uintptr_t)out & 15u)) & 15u) : span;
     const uint32_t nfull = (span - head) >> 4;
+#pragma unroll 2
     for (uint32_t w = tid; w < nfull; w += FR_THREADS) {
         const uint32_t rel = head + (w << 4);
         const uint32_t p = rel / (uint32_t)stride;
@@ -296,8 +311,10 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
         uint4 v = lds16(slot_addr(p) + o);
         if (len0 < 16u) {  // the word straddles two records (stride >= 16: never three)
             const uint4 u = lds16(slot_addr(p + 1) - len0);
-            auto mask = [](int nb) -> uint32_t { return nb >= 4 ? 0xFFFFFFFFu : (nb <= 0 ? 0u : ((1u << (8 * nb)) - 1u)); };
-            const uint32_t m0 = mask((int)len0), m1 = mask((int)len0 - 4), m2 = mask((int)len0 - 8), m3 = mask((int)len0 - 12);
+            // byte k of the word comes from v for k < len0, from u otherwise: one 128-bit mask, 4 LOP3 selects
+            const unsigned long long mlo = len0 >= 8u ? ~0ull : ((1ull << (8u * len0)) - 1ull);
+            const unsigned long long mhi = len0 <= 8u ? 0ull : ((1ull << (8u * (len0 - 8u))) - 1ull);
+            const uint32_t m0 = (uint32_t)mlo, m1 = (uint32_t)(mlo >> 32), m2 = (uint32_t)mhi, m3 = (uint32_t)(mhi >> 32);
             v.x = (v.x & m0) | (u.x & ~m0); v.y = (v.y & m1) | (u.y & ~m1);
             v.z = (v.z & m2) | (u.z & ~m2); v.w = (v.w & m3) | (u.w & ~m3);
         }
@@ -318,11 +335,12 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
     __syncthreads();  // buffers are reused by the next tile
 }
 
-template <bool ALIGN2>
-__global__ void __launch_bounds__(FR_THREADS, 2)
-fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride, int key_off, int key_len,
+template <bool ALIGN2, int STRIDE>
+__global__ void __launch_bounds__(FR_THREADS, UDA_FR_CTAS)
+fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride_rt, int key_off, int key_len,
                 const uint32_t* __restrict__ P, const uint32_t* __restrict__ outoff, FrParams* __restrict__ prm,
                 uint8_t* __restrict__ out) {
+    const int stride = STRIDE > 0 ? STRIDE : stride_rt;
     extern __shared__ __align__(128) uint8_t fr_smem_raw[];
     __shared__ __align__(8) uint64_t mbar;
     __shared__ uint32_t s_cnt;
@@ -353,7 +371,7 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride, i
         }
         __syncthreads();
         if (total <= (uint32_t)FR_TILE) {
-            fr_process_tile<ALIGN2>(runs, sm, k, stride, key_off, key_len, total, out + (unsigned long long)obase * stride, &mbar, phase);
+            fr_process_tile<ALIGN2, STRIDE>(runs, sm, k, stride, key_off, key_len, total, out + (unsigned long long)obase * stride, &mbar, phase);
             continue;
         }
         // ---- oversize bucket: split by bisection over the 128-bit value (key80 | run | index)
@@ -406,7 +424,7 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride, i
                 vlo = best;
                 __syncthreads();
             }
-            if (cnt) fr_process_tile<ALIGN2>(runs, sm, k, stride, key_off, key_len, cnt, out + (unsigned long long)(obase + done) * stride, &mbar, phase);
+            if (cnt) fr_process_tile<ALIGN2, STRIDE>(runs, sm, k, stride, key_off, key_len, cnt, out + (unsigned long long)(obase + done) * stride, &mbar, phase);
             done += cnt;
             remaining -= cnt;
             for (int r = threadIdx.x; r < k; r += FR_THREADS) sm.lo[r] = sm.hi[r];
@@ -496,11 +514,16 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
         if (rc) return rc;
         {
             const size_t smem = fr_smem_bytes(nruns, stride);
-            auto kern = align2 ? fr_merge_kernel<true> : fr_merge_kernel<false>;
-            static size_t configured[2] = {0, 0};
-            if (smem > configured[align2 ? 1 : 0]) {
+            void (*kern)(const UdaRunDesc*, int, int, int, int, int, const uint32_t*, const uint32_t*, FrParams*, uint8_t*);
+            int slot;
+            if (align2 && stride == 102) { kern = fr_merge_kernel<true, 102>; slot = 0; }
+            else if (align2 && stride == 100) { kern = fr_merge_kernel<true, 100>; slot = 1; }
+            else if (align2) { kern = fr_merge_kernel<true, 0>; slot = 2; }
+            else { kern = fr_merge_kernel<false, 0>; slot = 3; }
+            static size_t configured[4] = {0, 0, 0, 0};
+            if (smem > configured[slot]) {
                 UDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                configured[align2 ? 1 : 0] = smem;
+                configured[slot] = smem;
             }
             int per_sm = 0;
             UDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FR_THREADS, smem));
