@@ -99,10 +99,20 @@ class ClockSampler:
 
 def main():
     a = parse_args()
+    # Rank 0 must print exactly one line on stdout. Libraries print banners there (NCCL's version line comes
+    # from C code, so redirecting sys.stdout is not enough): park the real stdout and point fd 1 at stderr.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(obj) + "\n").encode())
+
     if a.impl == "reference":
-        print(json.dumps({"impl": "reference", "unavailable":
-                          "chaoyang223/UDA is a Hadoop JNI plugin on libibverbs/librdmacm/libaio: not pip-installable "
-                          "(no setup.py/pyproject) and its verbs, rdmacm, libaio, JDK and autotools dependencies are absent from this image"}))
+        emit({"impl": "reference", "unavailable":
+              "chaoyang223/UDA is a Hadoop JNI plugin on libibverbs/librdmacm/libaio: not pip-installable "
+              "(no setup.py/pyproject) and its verbs, rdmacm, libaio, JDK and autotools dependencies are absent from this image"})
         return 0
 
     import torch
@@ -203,8 +213,7 @@ def main():
             "gpu_launches": int(getattr(job, "launches_per_step", 0)) * a.steps,
             "validated": None if check is None else check["ok"],
         }
-        sys.stdout.flush()
-        print(json.dumps(out), flush=True)
+        emit(out)
     job.close()
     if world > 1:
         dist.destroy_process_group()

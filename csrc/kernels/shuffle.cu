@@ -81,10 +81,16 @@ __device__ __forceinline__ void copy_chunk(const uint8_t* __restrict__ src, uint
     if (tail0 + tid < bytes) dst[tail0 + tid] = src[tail0 + tid];
 }
 
+// nway > 1 interleaves the chunk order nway-fold: with peer-major descriptors of similar size per peer,
+// consecutive CTAs then work on different destinations at the same time, so the HBM-bound local copy and the
+// NVLink-bound remote pushes overlap instead of running one peer after the other.
 __global__ void __launch_bounds__(PUSH_THREADS) push_kernel(const UdaPushDesc* __restrict__ d, int nseg,
-                                                            const unsigned* __restrict__ chunk_prefix) {
+                                                            const unsigned* __restrict__ chunk_prefix, unsigned nway) {
     const unsigned total = chunk_prefix[nseg];
-    for (unsigned c = blockIdx.x; c < total; c += gridDim.x) {
+    const unsigned per = (total + nway - 1) / nway;
+    for (unsigned ci = blockIdx.x; ci < per * nway; ci += gridDim.x) {
+        const unsigned c = (ci % nway) * per + ci / nway;
+        if (c >= total) continue;
         int lo = 0, hi = nseg - 1;  // last segment with chunk_prefix[j] <= c
         while (lo < hi) {
             int mid = (lo + hi + 1) >> 1;
@@ -130,6 +136,14 @@ __global__ void barrier_kernel(unsigned long long* const* __restrict__ pads /* [
 
 }  // namespace uda
 
+// process-wide interleave factor for uda_shuffle_push (set once per job to the number of destination ranks)
+static int g_push_nway = 1;
+extern "C" int uda_shuffle_push_set_interleave(int nway) {
+    if (nway < 1 || nway > 4096) return UDA_E_INVALID;
+    g_push_nway = nway;
+    return 0;
+}
+
 extern "C" long long uda_push_scratch_bytes(int nseg) { return ((long long)nseg + 1) * (long long)sizeof(unsigned); }
 
 extern "C" int uda_shuffle_push(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, cudaStream_t stream) {
@@ -138,7 +152,7 @@ extern "C" int uda_shuffle_push(const UdaPushDesc* descs_dev, int nseg, void* sc
     unsigned* prefix = (unsigned*)scratch;
     push_plan_kernel<<<1, 1024, 0, stream>>>(descs_dev, nseg, prefix);
     int grid = max_ctas > 0 ? max_ctas : kNumSMs * 8;
-    push_kernel<<<grid, PUSH_THREADS, 0, stream>>>(descs_dev, nseg, prefix);
+    push_kernel<<<grid, PUSH_THREADS, 0, stream>>>(descs_dev, nseg, prefix, g_push_nway > 0 ? (unsigned)g_push_nway : 1u);
     UDA_CHECK_LAUNCH();
     return 0;
 }
@@ -219,7 +233,7 @@ extern "C" int uda_shuffle_push_static(const UdaPushDesc* descs_dev, int nseg, i
     }
     push_plan_kernel<<<1, 1024, 0, stream>>>(descs_dev, nseg, prefix);
     int grid = max_ctas > 0 ? max_ctas : kNumSMs * 8;
-    push_kernel<<<grid, PUSH_THREADS, 0, stream>>>(descs_dev, nseg, prefix);
+    push_kernel<<<grid, PUSH_THREADS, 0, stream>>>(descs_dev, nseg, prefix, 1u);
     UDA_CHECK_LAUNCH();
     return 0;
 }

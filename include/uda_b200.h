@@ -107,6 +107,8 @@ int uda_gather_var(const void* sorted_entries, long long n, const unsigned long 
  *      :44-136 credits) --------------------------------------------------------------------------- */
 long long uda_push_scratch_bytes(int nseg);
 int uda_shuffle_push(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, cudaStream_t stream);
+/* chunk-order interleave factor of uda_shuffle_push (number of destination ranks; 1 = sequential) */
+int uda_shuffle_push_set_interleave(int nway);
 /* No counterpart in the reference (it has no device code and nothing that must avoid allocation).
  * Same push as uda_shuffle_push, but the chunk-prefix scratch is a fixed array inside the library,
  * so the call never allocates: for providers embedded in a process that does not own the GPU's free

@@ -52,6 +52,7 @@ _PROTOS = {
     "uda_gather_var": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "uda_push_scratch_bytes": (c_ll, [c_int]),
     "uda_shuffle_push": (c_int, [c_vp, c_int, c_vp, c_int, c_vp]),
+    "uda_shuffle_push_set_interleave": (c_int, [c_int]),
     "uda_wait_flags": (c_int, [c_vp, c_vp, c_int, c_ull, c_vp, c_vp]),
     "uda_barrier_all": (c_int, [c_vp, c_int, c_int, c_ull, c_ull, c_vp, c_vp]),
     "uda_crc32": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp, c_vp]),

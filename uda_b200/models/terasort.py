@@ -105,6 +105,7 @@ class TeraSortJob:
         self.nseg = len(descs)
         self.push_descs_dev = K.to_device_struct(descs, dev)
         self.push_scratch = torch.empty(K.push_scratch_bytes(self.nseg), dtype=torch.uint8, device=dev)
+        K.shuffle_push_set_interleave(P)  # local copy and the P-1 remote pushes run concurrently
         rd, run_off, run_base, run_bytes = self.plan.run_descs(self.rank, self.arena.peer_data_ptr(self.rank))
         self.n_out = int(run_off[-1])
         self.expect_step = torch.from_numpy(run_bytes.astype(np.int64)).to(dev)

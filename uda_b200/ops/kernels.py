@@ -174,6 +174,10 @@ def shuffle_push(descs_dev: torch.Tensor, nseg: int, scratch: torch.Tensor, max_
     check(kernels().uda_shuffle_push(descs_dev.data_ptr(), nseg, scratch.data_ptr(), max_ctas, _stream()), "uda_shuffle_push")
 
 
+def shuffle_push_set_interleave(nway: int) -> None:
+    check(kernels().uda_shuffle_push_set_interleave(nway), "uda_shuffle_push_set_interleave")
+
+
 def wait_flags(flags: torch.Tensor, expect: torch.Tensor, n: int, status: torch.Tensor, max_spins: int = 50_000_000) -> None:
     check(kernels().uda_wait_flags(flags.data_ptr(), expect.data_ptr(), n, max_spins, status.data_ptr(), _stream()),
           "uda_wait_flags")
