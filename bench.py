@@ -173,6 +173,11 @@ def main():
     ms_per_step = ms / a.steps
     value = total_bytes / (ms_per_step * 1e-3) / 1e9
 
+    phases = None
+    if hasattr(job, "step_phases"):
+        ph = [job.step_phases() for _ in range(3)][-1]
+        phases = {k: max_over_ranks(v) for k, v in ph.items()}
+
     check = None
     if not a.no_check:
         check = job.check()
@@ -209,7 +214,7 @@ def main():
                 "l2_policy": "inputs (12.75 GB/GPU) larger than the 126 MB L2; no flush needed",
                 "timed_region": "shuffle push + flag acquire + key normalise + k-way merge + record gather (map-side sort is set-up)",
             },
-            "clocks": clocks, "e2e": e2e,
+            "clocks": clocks, "e2e": e2e, "phases_ms_max_over_ranks": phases,
             "gpu_launches": int(getattr(job, "launches_per_step", 0)) * a.steps,
             "validated": None if check is None else check["ok"],
         }

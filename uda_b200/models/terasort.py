@@ -131,6 +131,23 @@ class TeraSortJob:
         K.wait_flags(self.arena.flags(), self.expect, self.plan.nruns, self.arena.status)
         return self.merger.merge_fixed(out=out)
 
+    def step_phases(self) -> dict:
+        """One step with CUDA events between the phases (diagnostics; not used for the headline number)."""
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        if self.world > 1:
+            self.arena.barrier()
+        ev[0].record()
+        K.shuffle_push(self.push_descs_dev, self.nseg, self.push_scratch, self.push_ctas)
+        ev[1].record()
+        self.expect.add_(self.expect_step)
+        K.wait_flags(self.arena.flags(), self.expect, self.plan.nruns, self.arena.status)
+        ev[2].record()
+        self.merger.merge_fixed()
+        ev[3].record()
+        torch.cuda.synchronize(self.device)
+        self.steps_run += 1
+        return {"push_ms": ev[0].elapsed_time(ev[1]), "wait_ms": ev[1].elapsed_time(ev[2]), "merge_ms": ev[2].elapsed_time(ev[3])}
+
     # ------------------------------------------------------------------------------------ end to end
     def e2e_setup(self) -> None:
         """End-to-end path: map outputs start in pinned host memory (what a provider that just read

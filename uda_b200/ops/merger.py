@@ -63,5 +63,5 @@ class DeviceMerger:
         K.gather_fixed(self.sorted, n, self.run_base_dev, self.stride, out, write_eof)
         return out[: n * self.stride + (2 if write_eof else 0)]
 
-    #: kernels launched by one fused merge_fixed() call (range, sample-hist, 3 scan, partition, sizes, 3 scan, merge, eof)
-    LAUNCHES_PER_MERGE = 12
+    #: kernels launched by one fused merge_fixed() call (range, sample-hist, 3 scan, bkeys, partition, sizes, 3 scan, merge, eof)
+    LAUNCHES_PER_MERGE = 13
