@@ -42,6 +42,11 @@ def parse_args():
     ap.add_argument("--impl", default="uda_b200", choices=["uda_b200", "reference", "nccl_sort"])
     ap.add_argument("--records-per-gpu", type=int, default=125_000_000)
     ap.add_argument("--maps-per-gpu", type=int, default=8)
+    ap.add_argument("--subparts", type=int, default=0,
+                    help="sub-partitions per reducer pushed/merged as a pipeline (0 = auto: 1 on one GPU, 4 on several)")
+    ap.add_argument("--push-ctas", type=int, default=-1,
+                    help="grid of the push kernel (0 = 8 CTAs per SM; -1 = auto: 0 on one GPU, 296 when pipelined)")
+    ap.add_argument("--merge-ctas-per-sm", type=int, default=0, help="cap on resident merge CTAs per SM (0 = occupancy limit)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-check", action="store_true")
     return ap.parse_args()
@@ -148,7 +153,17 @@ def main():
     else:
         from uda_b200.models.terasort import TeraSortJob as Job
 
-    job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev).setup()
+    # measured on 8xB200 (profiles/pipeline_sweep.md): pipelining 4 sub-partitions with a 2-CTA/SM push grid
+    # takes the 8-GPU step from 33.6 to 29.6 ms; on one GPU (no NVLink wait to hide) it does not pay
+    if a.subparts <= 0:
+        a.subparts = 4 if world > 1 else 1
+    if a.push_ctas < 0:
+        a.push_ctas = 296 if a.subparts > 1 else 0
+    if a.impl == "nccl_sort":
+        job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev).setup()
+    else:
+        job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev, subparts=a.subparts, push_ctas=a.push_ctas,
+                  merge_ctas_per_sm=a.merge_ctas_per_sm).setup()
     total_bytes = float(a.records_per_gpu) * RECORD_BYTES * world
 
     def timed(fn, steps, warmup, sample_clocks):
@@ -210,6 +225,7 @@ def main():
                 "model": "TeraSort 100 GB/8 GPUs (12.5 GB per GPU), 100-byte teragen records, IFile-framed sorted MOFs in HBM",
                 "global_batch": a.records_per_gpu * world, "seq_len": RECORD_BYTES,
                 "records_per_gpu": a.records_per_gpu, "maps_per_gpu": a.maps_per_gpu, "runs_per_reducer": a.maps_per_gpu * world,
+                "subparts": a.subparts, "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
                 "parallelism": f"partition-parallel a2a x{world} (one reducer per GPU)",
                 "l2_policy": "inputs (12.75 GB/GPU) larger than the 126 MB L2; no flush needed",
                 "timed_region": "shuffle push + flag acquire + key normalise + k-way merge + record gather (map-side sort is set-up)",

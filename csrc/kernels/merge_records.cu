@@ -531,6 +531,15 @@ static FrScratch fr_layout(void* base, long long n, int k) {
 
 }  // namespace uda
 
+// cap on resident merge CTAs per SM (0 = as many as fit): lowered when the merge shares the GPU with a
+// concurrently running push kernel, so that the push CTAs find registers and thread slots
+static int g_fr_ctas_per_sm = 0;
+extern "C" int uda_merge_records_set_ctas_per_sm(int n) {
+    if (n < 0 || n > 32) return UDA_E_INVALID;
+    g_fr_ctas_per_sm = n;
+    return 0;
+}
+
 extern "C" long long uda_merge_records_scratch_bytes(long long n, int nruns) {
     if (n < 0 || nruns < 1) return UDA_E_INVALID;
     return (long long)uda::fr_layout(nullptr, n, nruns).bytes;
@@ -610,6 +619,7 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
             int per_sm = 0;
             UDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FR_THREADS, smem));
             if (per_sm < 1) return UDA_E_TOO_LARGE;
+            if (g_fr_ctas_per_sm > 0 && per_sm > g_fr_ctas_per_sm) per_sm = g_fr_ctas_per_sm;
             int grid = kNumSMs * per_sm;
             if (grid > G) grid = G;
             kern<<<grid, FR_THREADS, smem, stream>>>(runs_dev, nruns, G, stride, key_off, key_len, s.P, s.sizes, s.prm, o);

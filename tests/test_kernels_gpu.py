@@ -227,6 +227,7 @@ def test_kway_merge_and_gather(K, sizes, key_bits):
     ([1000], 0, False), ([0, 5, 0], 0, False), ([3000, 1, 2500, 0, 4000], 0, False), ([20000] * 24, 0, False), ([700] * 100, 0, False),
     ([6000, 7000, 5000], 3, False),   # 8 distinct keys: oversize buckets -> (key, run, index) bisection
     ([4000] * 9, 10, False), ([5000, 3000, 4000], 0, True),  # odd base addresses: byte-granular path
+    ([3] * 20 + [5000] * 4, 0, False),                       # k > 16: streaming partition, tiny runs take the search path
 ])
 def test_fused_record_merge(K, sizes, key_bits, odd):
     dev = _dev()
@@ -307,12 +308,13 @@ def test_shuffle_push_loopback(K):
 
 
 # ------------------------------------------------------------------------------------------- end to end
-@pytest.mark.parametrize("n,maps,key_bits", [(50_000, 4, 0), (200_000, 7, 0), (30_000, 3, 5), (6_000_000, 2, 0)])
-def test_terasort_job_single_gpu(built, n, maps, key_bits):
+@pytest.mark.parametrize("n,maps,key_bits,subparts", [(50_000, 4, 0, 1), (200_000, 7, 0, 1), (30_000, 3, 5, 1), (6_000_000, 2, 0, 1),
+                                                       (300_000, 5, 0, 4), (40_000, 3, 4, 3)])
+def test_terasort_job_single_gpu(built, n, maps, key_bits, subparts):
     from uda_b200.models.terasort import TeraSortJob
     from uda_b200.utils import ifile as _if
 
-    job = TeraSortJob(n, maps, device=_dev(), key_bits=key_bits).setup()
+    job = TeraSortJob(n, maps, device=_dev(), key_bits=key_bits, subparts=subparts).setup()
     try:
         # every MOF is a valid Hadoop file.out + index with correct CRCs
         mof = job.mofs[0]

@@ -53,7 +53,7 @@ class TeraSortJob:
     E2E_RING_BYTES = 256 << 20
 
     def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 1234,
-                 key_bits: int = 0, group=None, push_ctas: int = 0):
+                 key_bits: int = 0, group=None, push_ctas: int = 0, subparts: int = 1, merge_ctas_per_sm: int = 0):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -62,6 +62,11 @@ class TeraSortJob:
         self.maps = maps_per_rank
         self.seed, self.key_bits = seed, key_bits
         self.push_ctas = push_ctas
+        #: every reducer's key range is cut into `subparts` consecutive sub-partitions that are pushed in order on a
+        #: side stream while the merge of the previous sub-partition runs: the NVLink-bound (or, on one GPU,
+        #: HBM-bound) push overlaps the issue-bound merge. 1 = push everything, then merge.
+        self.subparts = max(1, subparts)
+        self.merge_ctas_per_sm = merge_ctas_per_sm
         self.mofs: List[DeviceMOF] = []
         self.input_fingerprint = 0
         self.steps_run = 0
@@ -70,8 +75,9 @@ class TeraSortJob:
     def setup(self) -> "TeraSortJob":
         dev, P = self.device, self.world
         per_map = [self.n_local // self.maps + (1 if i < self.n_local % self.maps else 0) for i in range(self.maps)]
-        splitters = uniform_splitters_w0(P)
-        task = MapTask(max(per_map), P, dev)
+        C = self.subparts
+        splitters = uniform_splitters_w0(P * C)
+        task = MapTask(max(per_map), P * C, dev)
         row0 = self.rank * self.n_local
         fp = 0
         for m, nm in enumerate(per_map):
@@ -95,23 +101,35 @@ class TeraSortJob:
             index = allt.cpu().numpy()
         else:
             index = local_idx[None]
-        self.plan = ShufflePlan(index, record_stride=TERA_STRIDE)
+        self.plan = ShufflePlan(index, record_stride=TERA_STRIDE, subparts=C)
+        nruns = self.plan.nruns
 
-        # ---- arena + tables
-        self.arena = SymmetricArena(self.plan.max_arena_bytes(), self.plan.nruns, dev, self.group)
-        descs = self.plan.push_descs(self.rank, [m.data.data_ptr() for m in self.mofs],
-                                     [self.arena.peer_data_ptr(p) for p in range(P)],
-                                     [self.arena.peer_flag_ptr(p, 0) for p in range(P)])
-        self.nseg = len(descs)
-        self.push_descs_dev = K.to_device_struct(descs, dev)
-        self.push_scratch = torch.empty(K.push_scratch_bytes(self.nseg), dtype=torch.uint8, device=dev)
+        # ---- arena + tables (one push table and one run table per sub-partition)
+        self.arena = SymmetricArena(self.plan.max_arena_bytes(), nruns * C, dev, self.group)
+        self.push_descs_dev = self._push_tables([m.data.data_ptr() for m in self.mofs])
+        self.nseg = self.maps * P
+        self.push_scratch = [torch.empty(K.push_scratch_bytes(self.nseg), dtype=torch.uint8, device=dev) for _ in range(C)]
         K.shuffle_push_set_interleave(P)  # local copy and the P-1 remote pushes run concurrently
-        rd, run_off, run_base, run_bytes = self.plan.run_descs(self.rank, self.arena.peer_data_ptr(self.rank))
-        self.n_out = int(run_off[-1])
-        self.expect_step = torch.from_numpy(run_bytes.astype(np.int64)).to(dev)
+        K.merge_records_set_ctas_per_sm(self.merge_ctas_per_sm)
+        self.sub_runs, self.sub_n, expect = [], [], []
+        max_sub = 1
+        for j in range(C):
+            rd, run_off, run_base, run_bytes = self.plan.run_descs(self.rank, self.arena.peer_data_ptr(self.rank), j)
+            self.sub_n.append(int(run_off[-1]))
+            max_sub = max(max_sub, self.sub_n[-1])
+            expect.append(run_bytes.astype(np.int64))
+            self.sub_runs.append((rd, run_off, run_base))
+        self.n_out = sum(self.sub_n)
+        self.expect_step = torch.from_numpy(np.concatenate(expect)).to(dev)
         self.expect = torch.zeros_like(self.expect_step)
-        self.merger = DeviceMerger(max(self.n_out, 1), self.plan.nruns, TERA_STRIDE, dev)
-        self.merger.set_runs(rd, run_off, run_base)
+        self.merger = DeviceMerger(max_sub, nruns, TERA_STRIDE, dev, out_bytes=self.n_out * TERA_STRIDE + 2)
+        snaps = []
+        for rd, run_off, run_base in self.sub_runs:
+            self.merger.set_runs(rd, run_off, run_base)
+            snaps.append(self.merger.snapshot_runs())
+        self.sub_runs = snaps
+        self.push_stream = torch.cuda.Stream(dev) if C > 1 else None
+        self.ev_go, self.ev_pushed = torch.cuda.Event(), torch.cuda.Event()
         self.bytes_in = int(sum(int(m.index[:, 2].sum()) for m in self.mofs))
         self.record_bytes_local = self.n_local * 100
         torch.cuda.synchronize(dev)
@@ -120,29 +138,62 @@ class TeraSortJob:
         return self
 
     # ------------------------------------------------------------------------------------ step
-    def step(self, descs: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def _push_tables(self, mof_ptrs) -> List[torch.Tensor]:
+        P = self.world
+        return [K.to_device_struct(self.plan.push_descs(self.rank, mof_ptrs, [self.arena.peer_data_ptr(p) for p in range(P)],
+                                                        [self.arena.peer_flag_ptr(p, 0) for p in range(P)], j), self.device)
+                for j in range(self.subparts)]
+
+    def _merge_sub(self, j: int, out: torch.Tensor) -> None:
+        C, nruns = self.subparts, self.plan.nruns
+        K.wait_flags(self.arena.flags()[j * nruns:(j + 1) * nruns], self.expect[j * nruns:(j + 1) * nruns], nruns, self.arena.status)
+        self.merger.use_runs(self.sub_runs[j])
+        off = sum(self.sub_n[:j]) * TERA_STRIDE
+        self.merger.merge_fixed(out=out[off:], write_eof=(j == C - 1))
+
+    def step(self, descs: Optional[List[torch.Tensor]] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One shuffle + merge. Flags are cumulative counters, so step ``i`` waits for ``i * bytes``; the
-        all-rank barrier at the top keeps a fast rank from overwriting an arena that is still being merged."""
+        all-rank barrier at the top keeps a fast rank from overwriting an arena that is still being merged.
+        With ``subparts > 1`` the pushes of all sub-partitions are queued on a side stream and the merge of
+        sub-partition j starts as soon as its runs have landed, i.e. while sub-partition j+1 is still in flight."""
         self.steps_run += 1
+        descs = self.push_descs_dev if descs is None else descs
+        out = self.merger.out if out is None else out
+        C = self.subparts
+        cur = torch.cuda.current_stream(self.device)
         if self.world > 1:
             self.arena.barrier()
-        K.shuffle_push(self.push_descs_dev if descs is None else descs, self.nseg, self.push_scratch, self.push_ctas)
         self.expect.add_(self.expect_step)
-        K.wait_flags(self.arena.flags(), self.expect, self.plan.nruns, self.arena.status)
-        return self.merger.merge_fixed(out=out)
+        if C == 1:
+            K.shuffle_push(descs[0], self.nseg, self.push_scratch[0], self.push_ctas)
+            self._merge_sub(0, out)
+        else:
+            self.ev_go.record(cur)
+            with torch.cuda.stream(self.push_stream):
+                self.push_stream.wait_event(self.ev_go)
+                for j in range(C):
+                    K.shuffle_push(descs[j], self.nseg, self.push_scratch[j], self.push_ctas)
+                self.ev_pushed.record(self.push_stream)
+            for j in range(C):
+                self._merge_sub(j, out)
+            cur.wait_event(self.ev_pushed)  # the step is over only when this rank's own pushes have retired
+        return out[: self.n_out * TERA_STRIDE + 2]
 
     def step_phases(self) -> dict:
         """One step with CUDA events between the phases (diagnostics; not used for the headline number)."""
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
         if self.world > 1:
             self.arena.barrier()
-        ev[0].record()
-        K.shuffle_push(self.push_descs_dev, self.nseg, self.push_scratch, self.push_ctas)
-        ev[1].record()
         self.expect.add_(self.expect_step)
-        K.wait_flags(self.arena.flags(), self.expect, self.plan.nruns, self.arena.status)
+        ev[0].record()
+        for j in range(self.subparts):  # phases are measured un-overlapped, one sub-partition after the other
+            K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas)
+        ev[1].record()
+        nr = self.plan.nruns * self.subparts
+        K.wait_flags(self.arena.flags(), self.expect, nr, self.arena.status)
         ev[2].record()
-        self.merger.merge_fixed()
+        for j in range(self.subparts):
+            self._merge_sub(j, self.merger.out)
         ev[3].record()
         torch.cuda.synchronize(self.device)
         self.steps_run += 1
@@ -175,10 +226,7 @@ class TeraSortJob:
         self.h_ring = [torch.empty(self.E2E_RING_BYTES, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
         # second device buffer set
         self.d_mofs = [[m.data for m in self.mofs], [torch.empty_like(m.data) for m in self.mofs]]
-        descs2 = self.plan.push_descs(self.rank, [t.data_ptr() for t in self.d_mofs[1]],
-                                      [self.arena.peer_data_ptr(p) for p in range(self.world)],
-                                      [self.arena.peer_flag_ptr(p, 0) for p in range(self.world)])
-        self.d_descs = [self.push_descs_dev, K.to_device_struct(descs2, dev)]
+        self.d_descs = [self.push_descs_dev, self._push_tables([t.data_ptr() for t in self.d_mofs[1]])]
         self.d_out = [self.merger.out, torch.empty_like(self.merger.out)]
         self.s_h2d, self.s_d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
         self.ev_h2d = [torch.cuda.Event(), torch.cuda.Event()]
@@ -223,10 +271,10 @@ class TeraSortJob:
         last_ok = bool(torch.equal(self.h_ring[(nblk - 1) % 2][: nb - off], out[off:nb].cpu()))
         return bool(self.check(out)["ok"]) and last_ok
 
-    #: kernel launches of this library inside one step (barrier, plan, push, add_, wait, merge chain)
+    #: kernel launches of this library inside one step (barrier, then per sub-partition: plan, push, wait, merge chain)
     @property
     def launches_per_step(self) -> int:
-        return (1 if self.world > 1 else 0) + 2 + 1 + DeviceMerger.LAUNCHES_PER_MERGE
+        return (1 if self.world > 1 else 0) + self.subparts * (2 + 1 + DeviceMerger.LAUNCHES_PER_MERGE)
 
     # ------------------------------------------------------------------------------------ check
     def check(self, out: Optional[torch.Tensor] = None) -> dict:

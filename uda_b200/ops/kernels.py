@@ -136,6 +136,10 @@ def merge_records_fixed(run_descs_dev: torch.Tensor, nruns: int, n: int, max_nre
                                             out.data_ptr(), int(write_eof), scratch.data_ptr(), _stream()), "uda_merge_records_fixed")
 
 
+def merge_records_set_ctas_per_sm(n: int) -> None:
+    check(kernels().uda_merge_records_set_ctas_per_sm(n), "uda_merge_records_set_ctas_per_sm")
+
+
 def merge_records_stats(scratch: torch.Tensor) -> Tuple[int, int]:
     out = (C.c_ulonglong * 2)()
     check(kernels().uda_merge_records_stats(scratch.data_ptr(), out, _stream()), "uda_merge_records_stats")

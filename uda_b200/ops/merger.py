@@ -35,6 +35,14 @@ class DeviceMerger:
         self.out = torch.empty(ob + 64, dtype=torch.uint8, device=device)
         self.n = 0
 
+    def snapshot_runs(self) -> dict:
+        """The currently installed run tables (device tensors), for jobs that alternate between several."""
+        return {k: getattr(self, k) for k in ("nruns", "n", "max_nrec", "run_descs_dev", "run_off_dev", "run_base_dev", "align2")}
+
+    def use_runs(self, snap: dict) -> None:
+        for k, v in snap.items():
+            setattr(self, k, v)
+
     def set_runs(self, run_descs: np.ndarray, run_off: np.ndarray, run_base: np.ndarray) -> None:
         """Upload the (static for the job) run tables."""
         self.nruns = len(run_descs)

@@ -46,27 +46,41 @@ class ShufflePlan:
     """``index[s][m][p] = (startOffset, rawLength, partLength)`` for every rank ``s``, local map ``m``,
     partition ``p``; all ranks hold the same array. ``record_stride`` > 0 marks a fixed-stride job."""
 
-    def __init__(self, index: np.ndarray, record_stride: int = 0):
+    def __init__(self, index: np.ndarray, record_stride: int = 0, subparts: int = 1):
         index = np.asarray(index, dtype=np.int64)
-        assert index.ndim == 4 and index.shape[3] == 3, "index must be [world, maps, P, 3]"
+        assert index.ndim == 4 and index.shape[3] == 3, "index must be [world, maps, P*subparts, 3]"
         self.index = index
-        self.world, self.maps, self.P = index.shape[:3]
-        assert self.P == self.world, "one reducer per rank (reference: src/Merger/reducer.h:137)"
+        self.world, self.maps = index.shape[:2]
+        self.subparts = subparts
+        self.P = index.shape[2] // subparts
+        assert self.P == self.world and self.P * subparts == index.shape[2], "one reducer per rank (reference: src/Merger/reducer.h:137)"
         self.stride = record_stride
         self.nruns = self.world * self.maps
-        self.layouts: List[ReducerLayout] = [self._layout(r) for r in range(self.P)]
+        #: flat list over (reducer r, sub-partition j): self.layouts[r * subparts + j]; sub-partitions of one
+        #: reducer share one arena and are laid out one after the other
+        self.layouts: List[ReducerLayout] = []
+        self.arena_bytes: List[int] = []
+        for r in range(self.P):
+            cur = _align(GATHER_SLACK)
+            for j in range(subparts):
+                lay, cur = self._layout(r, j, cur)
+                self.layouts.append(lay)
+            self.arena_bytes.append(_align(cur + GATHER_SLACK))
 
     def run_id(self, src_rank: int, m: int) -> int:
         return src_rank * self.maps + m
 
-    def _layout(self, r: int) -> ReducerLayout:
+    def layout(self, r: int, j: int = 0) -> ReducerLayout:
+        return self.layouts[r * self.subparts + j]
+
+    def _layout(self, r: int, j: int, cur: int):
         offs = np.zeros(self.nruns, dtype=np.int64)
         nbytes = np.zeros(self.nruns, dtype=np.int64)
         nrec = np.full(self.nruns, -1, dtype=np.int64)
-        cur = _align(GATHER_SLACK)
+        lp = r * self.subparts + j  # logical partition
         for s in range(self.world):
             for m in range(self.maps):
-                start, raw, part = (int(x) for x in self.index[s, m, r])
+                start, raw, part = (int(x) for x in self.index[s, m, lp])
                 rid = self.run_id(s, m)
                 # keep the source's 16-byte phase so the copy is vectorised end to end
                 cur = _align(cur) + (start % ALIGN)
@@ -77,32 +91,36 @@ class ShufflePlan:
                     assert body % self.stride == 0, "fixed-stride job with a ragged segment"
                     nrec[rid] = body // self.stride
                 cur += part
-        return ReducerLayout(offs, nbytes, nrec, _align(cur + GATHER_SLACK))
+        cur = _align(cur + GATHER_SLACK)
+        return ReducerLayout(offs, nbytes, nrec, cur), cur
 
     def max_arena_bytes(self) -> int:
-        return max(l.total_bytes for l in self.layouts)
+        return max(self.arena_bytes)
 
     # ---- sender side ------------------------------------------------------------------------
     def push_descs(self, rank: int, mof_ptrs: Sequence[int], peer_data_ptrs: Sequence[int],
-                   peer_flag_base: Sequence[int]) -> np.ndarray:
-        """Descriptor table for ``rank``: ``mof_ptrs[m]`` = device address of local map ``m``'s file.out bytes;
-        ``peer_data_ptrs[p]`` / ``peer_flag_base[p]`` = rank ``p``'s arena data / flag region as mapped here."""
+                   peer_flag_base: Sequence[int], sub: int = 0) -> np.ndarray:
+        """Descriptor table of sub-partition ``sub`` for ``rank``: ``mof_ptrs[m]`` = device address of local map
+        ``m``'s file.out bytes; ``peer_data_ptrs[p]`` / ``peer_flag_base[p]`` = rank ``p``'s arena data / flag
+        region as mapped here. Flag slot of (sub, run) is ``sub * nruns + run``."""
         d = np.zeros(self.maps * self.P, dtype=PUSH_DESC_DTYPE)
         i = 0
         for step in range(self.P):
             p = (rank + 1 + step) % self.P
-            lay = self.layouts[p]
+            lay = self.layout(p, sub)
             for m in range(self.maps):
-                start, _raw, part = (int(x) for x in self.index[rank, m, p])
+                start, _raw, part = (int(x) for x in self.index[rank, m, p * self.subparts + sub])
                 rid = self.run_id(rank, m)
-                d[i] = (mof_ptrs[m] + start, peer_data_ptrs[p] + int(lay.run_offsets[rid]), part, peer_flag_base[p] + 8 * rid)
+                d[i] = (mof_ptrs[m] + start, peer_data_ptrs[p] + int(lay.run_offsets[rid]), part,
+                        peer_flag_base[p] + 8 * (sub * self.nruns + rid))
                 i += 1
         return d
 
     # ---- receiver side ----------------------------------------------------------------------
-    def run_descs(self, rank: int, arena_data_ptr: int):
-        """``(UdaRunDesc table, run_off[nruns+1], run_base[nruns], expected_flag_bytes[nruns])`` for reducer ``rank``."""
-        lay = self.layouts[rank]
+    def run_descs(self, rank: int, arena_data_ptr: int, sub: int = 0):
+        """``(UdaRunDesc table, run_off[nruns+1], run_base[nruns], expected_flag_bytes[nruns])`` for sub-partition
+        ``sub`` of reducer ``rank``."""
+        lay = self.layout(rank, sub)
         d = np.zeros(self.nruns, dtype=RUN_DESC_DTYPE)
         base = arena_data_ptr + lay.run_offsets
         d["base"] = base.astype(np.uint64)
