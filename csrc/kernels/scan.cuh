@@ -33,7 +33,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* ws /* 
     return ws[w] + x - v;
 }
 
-__global__ void __launch_bounds__(THREADS) sums_kernel(const uint32_t* __restrict__ v, int m, uint32_t* __restrict__ sums) {
+static __global__ void __launch_bounds__(THREADS) sums_kernel(const uint32_t* __restrict__ v, int m, uint32_t* __restrict__ sums) {
     __shared__ uint32_t ws[32];
     __shared__ uint32_t tot;
     const int base = blockIdx.x * PER_BLOCK + threadIdx.x * ITEMS;
@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(THREADS) sums_kernel(const uint32_t* __restric
     if (threadIdx.x == 0) sums[blockIdx.x] = tot;
 }
 
-__global__ void __launch_bounds__(THREADS) scan_sums_kernel(uint32_t* __restrict__ sums, int nb) {
+static __global__ void __launch_bounds__(THREADS) scan_sums_kernel(uint32_t* __restrict__ sums, int nb) {
     __shared__ uint32_t ws[32];
     uint32_t s = (int)threadIdx.x < nb ? sums[threadIdx.x] : 0u;
     uint32_t e = block_excl_scan(s, ws, nullptr);
@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(THREADS) scan_sums_kernel(uint32_t* __restrict
 }
 
 // out[i] = exclusive prefix (out may alias v); out[m] = grand total
-__global__ void __launch_bounds__(THREADS) apply_kernel(const uint32_t* __restrict__ v, int m, const uint32_t* __restrict__ sums,
+static __global__ void __launch_bounds__(THREADS) apply_kernel(const uint32_t* __restrict__ v, int m, const uint32_t* __restrict__ sums,
                                                         uint32_t* __restrict__ out) {
     __shared__ uint32_t ws[32];
     const int base = blockIdx.x * PER_BLOCK + threadIdx.x * ITEMS;
@@ -76,6 +76,25 @@ static inline int exclusive(const uint32_t* v, int m, uint32_t* out, uint32_t* s
     sums_kernel<<<nb, THREADS, 0, stream>>>(v, m, sums);
     scan_sums_kernel<<<1, THREADS, 0, stream>>>(sums, nb);
     apply_kernel<<<nb, THREADS, 0, stream>>>(v, m, sums, out);
+    return 0;
+}
+
+// Any length: the block sums are scanned recursively. scratch must hold scratch_elems(m) u32.
+static inline long long scratch_elems(long long m) {
+    long long tot = 0;
+    while (m > PER_BLOCK) { m = (m + PER_BLOCK - 1) / PER_BLOCK; tot += m + 1; }
+    return tot + THREADS + 1;
+}
+static inline int exclusive_any(const uint32_t* v, long long m, uint32_t* out, uint32_t* scratch, cudaStream_t stream) {
+    if (m <= 0) return 0;
+    if (m > (1LL << 31) - 1) return -2;
+    if (m <= MAX_ELEMS) return exclusive(v, (int)m, out, scratch, stream);
+    const long long nb = (m + PER_BLOCK - 1) / PER_BLOCK;
+    uint32_t* sums = scratch;                 // nb + 1 entries, then the next level's scratch
+    sums_kernel<<<(unsigned)nb, THREADS, 0, stream>>>(v, (int)m, sums);
+    int rc = exclusive_any(sums, nb, sums, sums + nb + 1, stream);
+    if (rc) return rc;
+    apply_kernel<<<(unsigned)nb, THREADS, 0, stream>>>(v, (int)m, sums, out);
     return 0;
 }
 

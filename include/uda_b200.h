@@ -160,6 +160,26 @@ int uda_host_free_pinned(void* ptr);
 /* text for a return code of this library (negative: UDA_E_*, positive: cudaError_t) */
 const char* uda_error_string(int rc);
 
+/* ---- K1 second mode: fused key partition + record scatter for map outputs not yet grouped by reducer
+ *      (no reference counterpart: Hadoop's MapTask partitions; the transfer it fuses with replaces
+ *      src/DataNet/RDMAServer.cc:537-631). mode 0 = Hadoop HashPartitioner over key[key_skip..key_len),
+ *      mode 1 = total-order range over P-1 big-endian 8-byte splitters. stride even, <= 104; P <= 256. ---- */
+int uda_partition_count(const void* recs, long long n, int stride, int key_off, int key_len, int key_skip, int mode,
+                        int P, const unsigned long long* splitters_dev, unsigned long long* counts_dev,
+                        cudaStream_t stream);
+int uda_partition_scatter(const void* recs, long long n, int stride, int key_off, int key_len, int key_skip, int mode,
+                          int P, const unsigned long long* splitters_dev, const unsigned long long* dst_dev,
+                          unsigned long long* cursor_dev, cudaStream_t stream);
+/* ---- combiner (WordCount-style sum of 4-byte big-endian values over equal adjacent keys of a sorted
+ *      fixed-stride stream; the reference leaves combining to Hadoop's reducer) ---------------------- */
+int uda_combine_heads(const void* recs, long long n, int stride, int key_off, int key_len, unsigned* head_dev,
+                      cudaStream_t stream);
+int uda_combine_emit(const void* recs, long long n, long long groups, int stride, int key_off, int key_len, int val_off,
+                     const unsigned* gid_dev, void* out, unsigned long long* sums_dev, cudaStream_t stream);
+/* device-wide exclusive scan of m < 2^31 u32 values (out may alias v; out[m] = total) */
+long long uda_scan_u32_scratch_bytes(long long m);
+int uda_scan_u32(const unsigned* v, long long m, unsigned* out, unsigned* sums_scratch, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -328,3 +328,59 @@ def test_terasort_job_single_gpu(built, n, maps, key_bits, subparts):
         assert out.numel() == n * 102 + 2
     finally:
         job.close()
+
+
+# ------------------------------------------------------------------------------------------- partition / combine / wordcount
+@pytest.mark.parametrize("mode,P,stride", [(0, 7, 16), (1, 5, 16), (0, 3, 102), (1, 8, 102)])
+def test_partition_count_and_scatter(K, mode, P, stride):
+    from uda_b200.oracle.partition import java_hash_bytes
+
+    dev = _dev()
+    n = 30_011
+    rng = np.random.RandomState(mode * 10 + P)
+    recs = rng.randint(0, 256, size=(n, stride), dtype=np.uint8)
+    key_off, key_len, skip = 2, 10, (1 if mode == 0 else 0)
+    d = torch.from_numpy(recs.reshape(-1)).to(dev)
+    spl_host = np.array([((1 << 64) * i) // P for i in range(1, P)], dtype=np.uint64)
+    spl = torch.from_numpy(spl_host.view(np.int64)).to(dev) if mode == 1 else None
+    counts = K.partition_count(d, n, stride, key_off, key_len, skip, mode, P, spl).cpu().numpy()
+    if mode == 0:
+        dest = np.array([(java_hash_bytes(bytes(r[key_off + skip:key_off + key_len])) & 0x7FFFFFFF) % P for r in recs])
+    else:
+        w0 = np.array([int.from_bytes(bytes(r[key_off:key_off + 8]), "big") for r in recs], dtype=np.uint64)
+        dest = np.searchsorted(spl_host, w0, side="right")
+    assert (counts == np.bincount(dest, minlength=P)).all()
+    bufs = [torch.zeros(int(c) * stride + 16, dtype=torch.uint8, device=dev) for c in counts]
+    dst = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device=dev)
+    cursor = torch.zeros(P, dtype=torch.int64, device=dev)
+    K.partition_scatter(d, n, stride, key_off, key_len, skip, mode, P, dst, cursor, spl)
+    assert (cursor.cpu().numpy() == counts).all()
+    for p in range(P):
+        got = bufs[p][: int(counts[p]) * stride].cpu().numpy().reshape(-1, stride)
+        want = recs[dest == p]
+        assert sorted(map(bytes, got)) == sorted(map(bytes, want))
+
+
+def test_scan_u32_large(K):
+    dev = _dev()
+    for m in (1, 4097, 5_000_000):
+        v = torch.randint(0, 5, (m,), dtype=torch.int32, device=dev)
+        out = K.scan_u32(v)
+        want = torch.cumsum(v.to(torch.int64), 0)
+        assert int(out[m].item()) == int(want[-1].item())
+        assert torch.equal(out[1:m + 1].to(torch.int64), want)
+        assert int(out[0].item()) == 0
+
+
+@pytest.mark.parametrize("n,vocab", [(50_000, 1000), (400_000, 50_000)])
+def test_wordcount_job_single_gpu(built, n, vocab):
+    from uda_b200.models.wordcount import WordCountJob
+
+    job = WordCountJob(n, vocab=vocab, device=_dev()).setup()
+    try:
+        job.step()
+        job.step()
+        res = job.check()
+        assert res["ok"], res
+    finally:
+        job.close()

@@ -56,6 +56,12 @@ _PROTOS = {
     "uda_shuffle_push_set_interleave": (c_int, [c_int]),
     "uda_wait_flags": (c_int, [c_vp, c_vp, c_int, c_ull, c_vp, c_vp]),
     "uda_barrier_all": (c_int, [c_vp, c_int, c_int, c_ull, c_ull, c_vp, c_vp]),
+    "uda_partition_count": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp]),
+    "uda_partition_scatter": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "uda_combine_heads": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_vp, c_vp]),
+    "uda_combine_emit": (c_int, [c_vp, c_ll, c_ll, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "uda_scan_u32_scratch_bytes": (c_ll, [c_ll]),
+    "uda_scan_u32": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp]),
     "uda_crc32": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp, c_vp]),
     "uda_ifile_frame_fixed": (c_int, [c_vp, c_ll, c_int, c_int, c_vp, c_vp]),
     "uda_ifile_unframe_fixed": (c_int, [c_vp, c_ll, c_int, c_int, c_vp, c_vp]),

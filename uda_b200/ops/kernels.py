@@ -236,3 +236,45 @@ def ifile_encode_var(keys: torch.Tensor, key_off: torch.Tensor, klen: torch.Tens
                                          val_off.data_ptr(), vlen.data_ptr(), n, off.data_ptr(), out.data_ptr(), _stream()),
           "uda_ifile_encode_var")
     return out[: total + 2]
+
+
+# ------------------------------------------------------------------------------------------------ partition / combine
+def scan_u32(v: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Exclusive scan of an int32 tensor; returns ``m+1`` entries (``out[m]`` = total). No sync."""
+    m = v.numel()
+    if out is None:
+        out = torch.empty(m + 1, dtype=torch.int32, device=v.device)
+    scratch = torch.empty(int(kernels().uda_scan_u32_scratch_bytes(m)), dtype=torch.uint8, device=v.device)
+    check(kernels().uda_scan_u32(v.data_ptr(), m, out.data_ptr(), scratch.data_ptr(), _stream()), "uda_scan_u32")
+    return out
+
+
+def partition_count(recs: torch.Tensor, n: int, stride: int, key_off: int, key_len: int, key_skip: int, mode: int, P: int,
+                    splitters: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Records per destination (int64[P] device tensor, no sync). mode 0 = Hadoop hash, 1 = range."""
+    counts = torch.empty(P, dtype=torch.int64, device=recs.device)
+    check(kernels().uda_partition_count(recs.data_ptr(), n, stride, key_off, key_len, key_skip, mode, P, _p(splitters),
+                                        counts.data_ptr(), _stream()), "uda_partition_count")
+    return counts
+
+
+def partition_scatter(recs: torch.Tensor, n: int, stride: int, key_off: int, key_len: int, key_skip: int, mode: int, P: int,
+                      dst_ptrs: torch.Tensor, cursor: torch.Tensor, splitters: Optional[torch.Tensor] = None) -> None:
+    check(kernels().uda_partition_scatter(recs.data_ptr(), n, stride, key_off, key_len, key_skip, mode, P, _p(splitters),
+                                          dst_ptrs.data_ptr(), cursor.data_ptr(), _stream()), "uda_partition_scatter")
+
+
+def combine_sum_fixed(recs: torch.Tensor, n: int, stride: int, key_off: int, key_len: int, val_off: int) -> Tuple[torch.Tensor, int]:
+    """WordCount combiner over a key-sorted fixed-stride stream. Returns ``(combined records, groups)``; one sync
+    (the number of distinct keys sizes the output)."""
+    dev = recs.device
+    head = torch.empty(n + 1, dtype=torch.int32, device=dev)
+    check(kernels().uda_combine_heads(recs.data_ptr(), n, stride, key_off, key_len, head.data_ptr(), _stream()), "uda_combine_heads")
+    gid = scan_u32(head[:n], out=head)
+    groups = int(gid[n].item()) if n else 0
+    out = torch.empty(max(groups, 1) * stride + 16, dtype=torch.uint8, device=dev)
+    sums = torch.empty(max(groups, 1), dtype=torch.int64, device=dev)
+    if n:
+        check(kernels().uda_combine_emit(recs.data_ptr(), n, groups, stride, key_off, key_len, val_off, gid.data_ptr(), out.data_ptr(),
+                                         sums.data_ptr(), _stream()), "uda_combine_emit")
+    return out[: groups * stride], groups
