@@ -636,3 +636,41 @@ extern "C" int uda_merge_records_stats(const void* scratch, unsigned long long* 
     UDA_CUDA(cudaStreamSynchronize(stream));
     return 0;
 }
+
+// Positions of nkeys probe keys (8-byte big-endian prefixes, tail 0) in one sorted fixed-stride run:
+// pos_out[i] = first record whose key is >= keys[i]. Used by the spill path to cut merged runs into key ranges.
+namespace uda {
+__global__ void fr_lower_bound_kernel(const uint8_t* __restrict__ base, long long n, int stride, int key_off, int key_len,
+                                      const unsigned long long* __restrict__ keys, int nkeys, long long* __restrict__ pos_out) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nkeys; i += gridDim.x * blockDim.x)
+        pos_out[i] = (long long)lb_records(base, stride, key_off, key_len, 0u, (uint32_t)n, keys[i], 0u);
+}
+__global__ void fr_sample_keys_kernel(const uint8_t* __restrict__ base, long long n, int stride, int key_off, int key_len,
+                                      int nkeys, unsigned long long* __restrict__ keys_out) {
+    // keys_out[i] = key prefix of record (i+1)*n/(nkeys+1): nkeys equi-depth splitters of this run
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nkeys; i += gridDim.x * blockDim.x) {
+        unsigned long long w0;
+        uint32_t t;
+        load_key80(base + ((long long)(i + 1) * n / (nkeys + 1)) * stride + key_off, key_len, &w0, &t);
+        keys_out[i] = w0;
+    }
+}
+}  // namespace uda
+
+extern "C" int uda_lower_bound_records(const void* base, long long n, int stride, int key_off, int key_len,
+                                       const unsigned long long* keys_dev, int nkeys, long long* pos_out_dev, cudaStream_t stream) {
+    if (nkeys <= 0) return 0;
+    if (n >= (1LL << 32)) return UDA_E_INVALID;
+    uda::fr_lower_bound_kernel<<<(nkeys + 127) / 128, 128, 0, stream>>>((const uint8_t*)base, n, stride, key_off, key_len, keys_dev, nkeys,
+                                                                        pos_out_dev);
+    UDA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int uda_sample_splitters(const void* base, long long n, int stride, int key_off, int key_len, int nkeys,
+                                    unsigned long long* keys_out_dev, cudaStream_t stream) {
+    if (nkeys <= 0 || n <= 0) return 0;
+    uda::fr_sample_keys_kernel<<<(nkeys + 127) / 128, 128, 0, stream>>>((const uint8_t*)base, n, stride, key_off, key_len, nkeys, keys_out_dev);
+    UDA_CHECK_LAUNCH();
+    return 0;
+}

@@ -87,6 +87,11 @@ int uda_merge_records_supported(int nruns, long long n, int stride, int key_len)
 int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, long long n, long long max_nrec, int stride,
                             int key_off, int key_len, int align2, void* out, int write_eof, void* scratch,
                             cudaStream_t stream);
+/* key-range cuts of a sorted fixed-stride run (spill path): equi-depth splitters, and positions of splitters */
+int uda_sample_splitters(const void* base, long long n, int stride, int key_off, int key_len, int nkeys,
+                         unsigned long long* keys_out_dev, cudaStream_t stream);
+int uda_lower_bound_records(const void* base, long long n, int stride, int key_off, int key_len,
+                            const unsigned long long* keys_dev, int nkeys, long long* pos_out_dev, cudaStream_t stream);
 /* cap on resident merge CTAs per SM (0 = occupancy limit); use < max when a push kernel runs concurrently */
 int uda_merge_records_set_ctas_per_sm(int n);
 int uda_merge_records_stats(const void* scratch, unsigned long long* out2_host, cudaStream_t stream);

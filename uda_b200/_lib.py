@@ -45,6 +45,8 @@ _PROTOS = {
     "uda_merge_records_scratch_bytes": (c_ll, [c_ll, c_int]),
     "uda_merge_records_supported": (c_int, [c_int, c_ll, c_int, c_int]),
     "uda_merge_records_fixed": (c_int, [c_vp, c_int, c_ll, c_ll, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp, c_vp]),
+    "uda_sample_splitters": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_int, c_vp, c_vp]),
+    "uda_lower_bound_records": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_vp, c_int, c_vp, c_vp]),
     "uda_merge_records_set_ctas_per_sm": (c_int, [c_int]),
     "uda_merge_records_stats": (c_int, [c_vp, C.POINTER(c_ull), c_vp]),
     "uda_merge_stats": (c_int, [c_vp, C.POINTER(c_ull), c_vp]),

@@ -278,3 +278,18 @@ def combine_sum_fixed(recs: torch.Tensor, n: int, stride: int, key_off: int, key
         check(kernels().uda_combine_emit(recs.data_ptr(), n, groups, stride, key_off, key_len, val_off, gid.data_ptr(), out.data_ptr(),
                                          sums.data_ptr(), _stream()), "uda_combine_emit")
     return out[: groups * stride], groups
+
+
+def sample_splitters(run: torch.Tensor, n: int, stride: int, key_off: int, key_len: int, nkeys: int) -> torch.Tensor:
+    """``nkeys`` equi-depth key prefixes (int64 view of uint64) of a sorted fixed-stride run."""
+    out = torch.empty(max(nkeys, 1), dtype=torch.int64, device=run.device)
+    check(kernels().uda_sample_splitters(run.data_ptr(), n, stride, key_off, key_len, nkeys, out.data_ptr(), _stream()), "uda_sample_splitters")
+    return out[:nkeys]
+
+
+def lower_bound_records(run: torch.Tensor, n: int, stride: int, key_off: int, key_len: int, keys: torch.Tensor) -> torch.Tensor:
+    """First record index with key >= each probe key (int64 device tensor, no sync)."""
+    out = torch.empty(max(keys.numel(), 1), dtype=torch.int64, device=run.device)
+    check(kernels().uda_lower_bound_records(run.data_ptr(), n, stride, key_off, key_len, keys.data_ptr(), keys.numel(), out.data_ptr(),
+                                            _stream()), "uda_lower_bound_records")
+    return out[: keys.numel()]
