@@ -185,6 +185,12 @@ int uda_combine_emit(const void* recs, long long n, long long groups, int stride
 long long uda_scan_u32_scratch_bytes(long long m);
 int uda_scan_u32(const unsigned* v, long long m, unsigned* out, unsigned* sums_scratch, cudaStream_t stream);
 
+/* ---- K10 broadcast of side tables: NVLS multicast store (multimem.st) or unicast peer stores
+ *      (no reference counterpart: Hadoop distributes such tables as files) ------------------------ */
+int uda_multicast_store(const void* src, unsigned long long multicast_ptr, long long bytes, cudaStream_t stream);
+int uda_unicast_store(const void* src, const unsigned long long* peer_ptrs_dev, int world, long long bytes,
+                      cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

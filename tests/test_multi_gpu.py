@@ -39,3 +39,13 @@ def test_wordcount_multi_rank(built, world):
     text = p.stdout + "\n" + p.stderr
     assert p.returncode == 0, text[-6000:]
     assert text.count("MPRESULT") == world and text.count('"ok": true') == world, text[-6000:]
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_side_table_broadcast(built, world):
+    if _ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    p = _torchrun(world, "mp_bcast.py")
+    text = p.stdout + "\n" + p.stderr
+    assert p.returncode == 0, text[-6000:]
+    assert text.count('"ok": true') == world, text[-6000:]

@@ -64,6 +64,8 @@ _PROTOS = {
     "uda_combine_emit": (c_int, [c_vp, c_ll, c_ll, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp, c_vp]),
     "uda_scan_u32_scratch_bytes": (c_ll, [c_ll]),
     "uda_scan_u32": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp]),
+    "uda_multicast_store": (c_int, [c_vp, c_ull, c_ll, c_vp]),
+    "uda_unicast_store": (c_int, [c_vp, c_vp, c_int, c_ll, c_vp]),
     "uda_crc32": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp, c_vp]),
     "uda_ifile_frame_fixed": (c_int, [c_vp, c_ll, c_int, c_int, c_vp, c_vp]),
     "uda_ifile_unframe_fixed": (c_int, [c_vp, c_ll, c_int, c_int, c_vp, c_vp]),
