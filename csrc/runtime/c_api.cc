@@ -5,11 +5,14 @@
 // The reference exposes this surface only through JNI (src/UdaBridge.cc:187-330: startNative,
 // doCommandNative, reduceExitMsgNative, setLogLevelNative) with one role per process held in globals;
 // here a role is a handle, which lets one test process run a provider and several consumers.
+#include <set>
+#include <list>
 #include <cstring>
 #include <memory>
 #include <string>
 #include <vector>
 
+#include "threads.h"
 #include "../../include/uda_rt_api.h"
 #include "consumer.h"
 #include "provider.h"
@@ -28,6 +31,7 @@ struct Role {
     std::unique_ptr<Provider> provider;
     std::unique_ptr<Consumer> consumer;
     std::thread provider_thread;
+    FailureLatch latch;
     std::string last_error;
     bool failed = false;
 };
@@ -101,7 +105,7 @@ uda_role_t uda_rt_start(int is_net_merger, int argc, const char* const* argv, in
             r->provider = std::make_unique<Provider>(r->opt, &r->host);
             r->provider->start();
             Provider* p = r->provider.get();
-            r->provider_thread = std::thread([p] { p->run(); });  // MOFSupplierRun
+            r->provider_thread = spawn_guarded("MOFSupplierRun", &r->host, &r->latch, [p] { p->run(); });
         }
         UDA_LOG(lsINFO, "main initialization finished ret=0");
     });
@@ -309,4 +313,42 @@ int uda_rt_selftest_queues(void) {
 
 const char* uda_rt_version(void) { return VERSION_UDA; }
 
+
+// Exercises spawn_guarded / FailureLatch and the shuffle helpers; returns 0 when all invariants held.
+// perm_out (n ints, may be null) receives vector_shuffle(0..n-1) for `seed` so that the order can be pinned.
+int uda_rt_selftest_threads(unsigned long long seed, int n, int* perm_out) {
+    static std::atomic<int> fails{0};
+    fails = 0;
+    HostCallbacks cb;
+    cb.failure_in_uda = [](void*) { ++fails; };
+    FailureLatch latch;
+    std::thread a = spawn_guarded("selftest-a", &cb, &latch, [] { throw UdaError("boom"); });
+    a.join();
+    std::thread b = spawn_guarded("selftest-b", &cb, &latch, [] { throw std::runtime_error("again"); });
+    b.join();
+    std::thread c = spawn_guarded("selftest-c", &cb, &latch, [] {});
+    c.join();
+    if (fails != 1 || !latch.failed()) return 1;  // exactly one up-call for two failing threads
+    ShuffleRng rng(seed);
+    std::vector<int> v(n);
+    for (int i = 0; i < n; ++i) v[i] = i;
+    vector_shuffle(v, rng);
+    std::vector<char> seen(n, 0);
+    for (int x : v) { if (x < 0 || x >= n || seen[x]) return 2; seen[x] = 1; }
+    if (perm_out) for (int i = 0; i < n; ++i) perm_out[i] = v[i];
+    std::list<int> l;
+    for (int i = 0; i < n; ++i) l.push_back(i);
+    auto lv = list_shuffle_in_vector(l, rng);
+    if (!l.empty() || (int)lv.size() != n) return 3;
+    // 3 hosts with 4, 2 and 1 entries: no host repeats back to back while another still has work
+    std::vector<std::pair<std::string, int>> work;
+    for (int i = 0; i < 4; ++i) work.push_back({"h0", i});
+    for (int i = 0; i < 2; ++i) work.push_back({"h1", i});
+    work.push_back({"h2", 0});
+    auto out = shuffle_interleave_hosts(work, rng, [](const std::pair<std::string, int>& x) { return x.first; });
+    if (out.size() != work.size()) return 4;
+    std::set<std::string> first3{out[0].first, out[1].first, out[2].first};
+    if (first3.size() != 3) return 5;
+    return 0;
+}
 }  // extern "C"

@@ -1,4 +1,5 @@
 #include "consumer.h"
+#include "threads.h"
 
 #include <dlfcn.h>
 #include <unistd.h>
@@ -576,7 +577,7 @@ std::unique_ptr<ByteSource> Consumer::make_source(const FetchOrder& o) {
 
 void Consumer::fetching_phase(MergeHeap* heap, int count, int* progress) {
     int got = 0;
-    std::mt19937 rng(12345u + (unsigned)segment_seq_);
+    ShuffleRng rng(12345u + (uint64_t)segment_seq_);
     while (got < count) {
         std::vector<FetchOrder> batch;
         {
@@ -588,7 +589,8 @@ void Consumer::fetching_phase(MergeHeap* heap, int count, int* progress) {
                 fetch_list_.pop_front();
             }
         }
-        std::shuffle(batch.begin(), batch.end(), rng);  // spread the first requests over the providers
+        // random order, interleaved by host: the first requests of all reducers must not pile up on one provider
+        batch = shuffle_interleave_hosts(std::move(batch), rng, [](const FetchOrder& o) { return o.host; });
         std::vector<std::pair<std::unique_ptr<ByteSource>, FetchSource*>> started;
         for (auto& o : batch) {
             auto src = make_source(o);

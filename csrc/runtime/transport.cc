@@ -1,4 +1,5 @@
 #include "transport.h"
+#include "threads.h"
 
 #include <arpa/inet.h>
 #include <errno.h>
@@ -97,7 +98,7 @@ void ShuffleServer::start() {
     socklen_t sl = sizeof(sa);
     if (getsockname(listen_fd_, (sockaddr*)&sa, &sl) == 0) port_ = ntohs(sa.sin_port);
     running_ = true;
-    accept_thread_ = std::thread([this] { accept_loop(); });
+    accept_thread_ = spawn_guarded("accept", nullptr, nullptr, [this] { accept_loop(); });
     UDA_LOG(lsINFO, "shuffle server listening on port %d", port_);
 }
 
@@ -185,7 +186,7 @@ std::shared_ptr<TcpInputClient::Peer> TcpInputClient::peer_for(const std::string
     auto p = std::make_shared<Peer>();
     p->conn = std::make_shared<Connection>(fd);
     p->credits = wqes_ - 1;
-    p->reader = std::thread([this, p] { read_loop(p); });
+    p->reader = spawn_guarded("client-read", nullptr, nullptr, [this, p] { read_loop(p); });
     if (it != peers_.end()) { if (it->second->reader.joinable()) it->second->reader.detach(); }
     peers_[host] = p;
     return p;

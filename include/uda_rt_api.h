@@ -56,6 +56,8 @@ long long uda_rt_snappy_store(const unsigned char* in, long long n, unsigned cha
 int uda_rt_plan_memory(int num_maps, long long max_buf, long long min_buf, long long shuffle_mem, int compressed,
                        double ratio, long long* out4);
 int uda_rt_selftest_queues(void);
+/* thread wrapper (exception -> one failure up-call) and Fisher-Yates fetch-order helpers; 0 = all invariants held */
+int uda_rt_selftest_threads(unsigned long long seed, int n, int* perm_out);
 
 #ifdef __cplusplus
 }

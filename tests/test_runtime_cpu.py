@@ -108,6 +108,19 @@ def test_queues_selftest(L):
     assert L.uda_rt_selftest_queues() == 0
 
 
+def test_thread_wrapper_and_shuffles(L):
+    """N4: a throwing native thread raises exactly one failure up-call; the shuffles are permutations and
+    deterministic for a seed (src/CommUtils/UdaUtil.cc:39-94; vector_shuffle / list_shuffle_in_vector)."""
+    import ctypes as C
+    n = 97
+    a, b = (C.c_int * n)(), (C.c_int * n)()
+    assert L.uda_rt_selftest_threads(C.c_ulonglong(42), n, a) == 0
+    assert L.uda_rt_selftest_threads(C.c_ulonglong(42), n, b) == 0
+    assert list(a) == list(b) and sorted(a) == list(range(n)) and list(a) != list(range(n))
+    assert L.uda_rt_selftest_threads(C.c_ulonglong(43), n, b) == 0
+    assert list(a) != list(b)
+
+
 def test_memory_plan(L):
     out = (C.c_longlong * 4)()
     MiB = 1 << 20
