@@ -109,6 +109,24 @@ int uda_gather_var(const void* sorted_entries, long long n, const unsigned long 
                    const unsigned long long* run_recoff_dev, const unsigned long long* dst_off_dev, void* dst,
                    cudaStream_t stream);
 
+/* ---- general (variable-length) reduce path: exact comparator tie-break + 64-bit stream offsets
+ *      (reference: src/Merger/CompareFunc.cc:70-91 called from the segment heap, src/Merger/StreamRW.h:163) ---- */
+/* Re-orders, inside `sorted_entries`, every group of entries that share the 80-bit key prefix but are not in the
+ * order of the exact comparator (key_kind 0 raw bytes, 1 Text, 2 BytesWritable; equal keys keep (run, index)
+ * order). run_base_dev[run] / run_recoff_dev[run] locate record idx of a run as base + recoff[idx].
+ * tmp_entries: n entries of scratch (the merge's input array is free at this point). n < 2^31-1. */
+long long uda_tiebreak_scratch_bytes(long long n);
+int uda_tiebreak_var(void* sorted_entries, long long n, const unsigned long long* run_base_dev,
+                     const unsigned long long* run_recoff_dev, int key_kind, void* tmp_entries, void* scratch,
+                     cudaStream_t stream);
+/* out3_host: {groups re-ordered, largest such group, entries moved}; synchronises the stream */
+int uda_tiebreak_stats(const void* scratch, long long n, unsigned long long* out3_host, cudaStream_t stream);
+/* out[i] = sum of v[0..i) as 64-bit, out[m] = total (record lengths -> byte offsets of the merged stream) */
+long long uda_scan_u32_to_u64_scratch_bytes(long long m);
+int uda_scan_u32_to_u64(const unsigned* v, long long m, unsigned long long* out, void* scratch, cudaStream_t stream);
+/* writes the IFile EOF marker (VInt -1, VInt -1) at dst + *total_dev (dst + 0 when total_dev is null) */
+int uda_write_eof_at(void* dst, const unsigned long long* total_dev, cudaStream_t stream);
+
 /* ---- K1 fused shuffle push over peer memory (reference: src/DataNet/RDMAClient.cc:559-600 request,
  *      src/MOFServer/IndexInfo.cc:237-335 chunk read, src/DataNet/RDMAServer.cc:537-631 write+ack,
  *      :44-136 credits) --------------------------------------------------------------------------- */

@@ -429,3 +429,148 @@ def test_spill_merger(K, sizes, budget):
     assert bytes(host[total * 102: total * 102 + 2]) == b"\xff\xff"
     if budget < (1 << 30):
         assert sm.stats["groups"] > 1 and sm.stats["ranges"] > 1 and sm.stats["spilled_bytes"] == total * 102
+
+
+# ------------------------------------------------------------------------------------------- general (var-length) path
+@pytest.mark.parametrize("m,hi", [(0, 10), (1, 10), (4097, 1000), (3_000_000, 1 << 31)])
+def test_scan_u32_to_u64(K, m, hi):
+    g = np.random.default_rng(m + 1)
+    v = g.integers(0, hi, size=m, dtype=np.int64).astype(np.uint32)
+    out = K.scan_u32_to_u64(torch.from_numpy(v.view(np.int32).copy()).to(_dev()), m)
+    want = np.concatenate([[0], np.cumsum(v.astype(np.uint64))]).astype(np.uint64)
+    assert np.array_equal(out.cpu().numpy().view(np.uint64), want)
+    if m == 3_000_000:
+        assert int(want[-1]) > (1 << 32)  # the case a 32-bit scan cannot represent
+
+
+def _tie_records(seed, n, kind):
+    """Keys that share 10-byte prefixes, incl. shorter keys that tie through zero padding and exact duplicates."""
+    rng = random.Random(seed)
+    pre = [bytes(rng.randrange(256) for _ in range(10)) for _ in range(3)] + [b"ab", b"ab\0", b"ab\0\0", b""]
+    recs = []
+    for i in range(n):
+        body = rng.choice(pre)
+        if len(body) == 10 and rng.random() < 0.8:
+            body += bytes(rng.randrange(256) for _ in range(rng.randint(0, 12)))
+        elif rng.random() < 0.3:
+            body = bytes(rng.randrange(256) for _ in range(rng.randint(0, 30)))
+        key = (len(body).to_bytes(4, "big") + body) if kind == 2 else (vint.encode_vlong(len(body)) + body) if kind == 1 else body
+        recs.append((key, i.to_bytes(4, "big")))
+    return recs
+
+
+def _cmp_body(kind):
+    if kind == 2:
+        return lambda kv: kv[0][4:]
+    if kind == 1:
+        return lambda kv: kv[0][vint.decode_vint_size(kv[0][0]):]
+    return lambda kv: kv[0]
+
+
+@pytest.mark.parametrize("kind", [0, 1, 2])
+@pytest.mark.parametrize("sizes", [[700], [300, 1, 0, 450, 200], [2500, 2500, 2500]])
+def test_var_merger_with_prefix_ties(K, kind, sizes):
+    """VarMerger == stable CPU sort with the exact comparator, on sorted runs full of prefix ties."""
+    from uda_b200.ops.varlen import VarMerger
+    dev = _dev()
+    body = _cmp_body(kind)
+    runs, segs, keep = [], [], []
+    for r, n in enumerate(sizes):
+        recs = sorted(_tie_records(100 * r + n + kind, n, kind), key=body)
+        runs.append(recs)
+        raw = ifile.encode_segment(recs, with_crc=False)
+        t = torch.from_numpy(np.frombuffer(raw + b"\0" * 16, dtype=np.uint8).copy()).to(dev)
+        keep.append(t)
+        segs.append((t, len(raw), n))
+    total = sum(sizes)
+    vm = VarMerger(dev, kind, total, len(sizes), sum(s[1] for s in segs))
+    for exact in (True, False):
+        use = segs if exact else [(t, l, n + 5) for t, l, n in segs]
+        out, nbytes = vm.merge(use, exact_counts=exact)
+        want = ifile.encode_segment(sorted([kv for run in runs for kv in run], key=body), with_crc=False)
+        assert nbytes == len(want)
+        assert bytes(out.cpu().numpy()) == want
+    groups, largest, moved = vm.tiebreak_stats()
+    if len(sizes) > 1:
+        assert groups > 0 and largest > 1 and moved >= largest  # the tie-break really ran
+
+
+@pytest.mark.parametrize("kind,n,maps", [(2, 30_000, 3), (1, 20_000, 2)])
+def test_sort_job_single_gpu(built, kind, n, maps):
+    from uda_b200.models.sortjob import SortJob
+    job = SortJob(n, maps, device=_dev(), key_kind=kind, key_len=(0, 60), val_len=(0, 150), tie_fraction=0.05).setup()
+    job.step()
+    out = job.step()
+    res = job.check(out)
+    assert res["ok"] and res["records"] == n and res["tiebreak_groups"] > 0, res
+    # every map output is a valid MOF: CRC of every segment, sortedness inside every partition
+    body = _cmp_body(kind)
+    for mof in job.mofs:
+        fb = mof.file_bytes()
+        for rec in mof.index_records():
+            part = ifile.read_partition(fb, rec, verify_crc=True)
+            assert part == sorted(part, key=body)
+    job.close()
+
+
+# ------------------------------------------------------------------------------------------- fault injection
+def test_fault_lost_push_times_out_and_falls_back(built):
+    """A push that sends fewer bytes than planned trips the wait kernel's watchdog; the controller raises the
+    failure up-call once and later phases are skipped."""
+    from uda_b200.models.terasort import TeraSortJob
+    from uda_b200.runtime.failure import FallbackController, ShuffleTimeout
+    from uda_b200.utils.faults import drop_push_segment
+    job = TeraSortJob(60_000, 3, device=_dev()).setup()
+    job.step()
+    job.raise_on_failure()                                   # healthy step: no time-out recorded
+    job.wait_max_spins = 20_000
+    bad = [drop_push_segment(job.push_descs_dev[0], 1, keep_bytes=16)]
+    calls = []
+    fc = FallbackController(on_failure=calls.append)
+    with fc.guard("shuffle"):
+        job.step(descs=bad)
+        job.raise_on_failure()
+    assert fc.failed and len(calls) == 1 and isinstance(calls[0], ShuffleTimeout)
+    with fc.guard("merge") as active:
+        assert active is False
+    job.close()
+
+
+def test_fault_corrupt_segment_detected_by_crc(built):
+    from uda_b200.models.terasort import TeraSortJob
+    from uda_b200.runtime.failure import ChecksumMismatch
+    from uda_b200.utils.faults import corrupt_segment
+    job = TeraSortJob(50_000, 2, device=_dev()).setup()
+    job.step()
+    job.verify_crc()                                         # clean data passes
+    corrupt_segment(job.mofs[1], 0)
+    job.step()
+    with pytest.raises(ChecksumMismatch):
+        job.verify_crc()
+    job.close()
+
+
+def test_fault_arena_oom_is_a_fallback_reason(built):
+    from uda_b200.models.terasort import TeraSortJob
+    from uda_b200.runtime.failure import ArenaAllocationFailed, FallbackController
+    from uda_b200.utils.faults import arena_oom
+    calls = []
+    fc = FallbackController(on_failure=calls.append)
+    with arena_oom(), fc.guard("init"):
+        TeraSortJob(10_000, 2, device=_dev()).setup()
+    assert fc.failed and isinstance(calls[0], ArenaAllocationFailed)
+
+
+def test_phase_timer_and_metrics(built, tmp_path):
+    from uda_b200.models.terasort import TeraSortJob
+    from uda_b200.utils.trace import PhaseTimer, write_metrics
+    job = TeraSortJob(100_000, 2, device=_dev()).setup()
+    t = PhaseTimer(_dev())
+    for _ in range(2):
+        with t.phase("step", bytes_moved=job.record_bytes_local, hbm_bytes=4 * job.bytes_in):
+            job.step()
+    s = t.summary()
+    assert s["step"]["calls"] == 2 and s["step"]["ms"] > 0 and s["step"]["gbs"] > 0 and 0 < s["step"]["hbm_roofline_frac"] < 1.5
+    p = write_metrics("unit_phase_timer", {"phases": s}, directory=str(tmp_path))
+    assert p.exists() and "hbm_roofline_frac" in p.read_text()
+    job.close()

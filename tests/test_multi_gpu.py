@@ -49,3 +49,14 @@ def test_side_table_broadcast(built, world):
     text = p.stdout + "\n" + p.stderr
     assert p.returncode == 0, text[-6000:]
     assert text.count('"ok": true') == world, text[-6000:]
+
+
+@pytest.mark.parametrize("world,kind", [(2, 2), (2, 1), (8, 2)])
+def test_sort_job_multi_rank(built, world, kind):
+    """Variable-length records, BytesWritable (2) / Text (1) keys, 5 % of the keys tie on the sort prefix."""
+    if _ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    p = _torchrun(world, "mp_sort.py", 40_000, kind)
+    text = p.stdout + "\n" + p.stderr
+    assert p.returncode == 0, text[-6000:]
+    assert text.count("MPRESULT") == world and text.count('"ok": true') == world, text[-6000:]

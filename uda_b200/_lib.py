@@ -53,6 +53,12 @@ _PROTOS = {
     "uda_gather_fixed": (c_int, [c_vp, c_ll, c_vp, c_int, c_vp, c_int, c_vp]),
     "uda_gather_var_lengths": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp]),
     "uda_gather_var": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "uda_tiebreak_scratch_bytes": (c_ll, [c_ll]),
+    "uda_tiebreak_var": (c_int, [c_vp, c_ll, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]),
+    "uda_tiebreak_stats": (c_int, [c_vp, c_ll, C.POINTER(c_ull), c_vp]),
+    "uda_scan_u32_to_u64_scratch_bytes": (c_ll, [c_ll]),
+    "uda_scan_u32_to_u64": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp]),
+    "uda_write_eof_at": (c_int, [c_vp, c_vp, c_vp]),
     "uda_push_scratch_bytes": (c_ll, [c_int]),
     "uda_shuffle_push": (c_int, [c_vp, c_int, c_vp, c_int, c_vp]),
     "uda_shuffle_push_set_interleave": (c_int, [c_int]),

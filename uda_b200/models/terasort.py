@@ -67,6 +67,9 @@ class TeraSortJob:
         #: HBM-bound) push overlaps the issue-bound merge. 1 = push everything, then merge.
         self.subparts = max(1, subparts)
         self.merge_ctas_per_sm = merge_ctas_per_sm
+        #: polls of the landed-byte counters before the wait kernel gives up and records a time-out in the arena's
+        #: status word (the watchdog that turns a lost push into a failure up-call instead of a hang)
+        self.wait_max_spins = 50_000_000
         self.mofs: List[DeviceMOF] = []
         self.input_fingerprint = 0
         self.steps_run = 0
@@ -146,7 +149,8 @@ class TeraSortJob:
 
     def _merge_sub(self, j: int, out: torch.Tensor) -> None:
         C, nruns = self.subparts, self.plan.nruns
-        K.wait_flags(self.arena.flags()[j * nruns:(j + 1) * nruns], self.expect[j * nruns:(j + 1) * nruns], nruns, self.arena.status)
+        K.wait_flags(self.arena.flags()[j * nruns:(j + 1) * nruns], self.expect[j * nruns:(j + 1) * nruns], nruns, self.arena.status,
+                     self.wait_max_spins)
         self.merger.use_runs(self.sub_runs[j])
         off = sum(self.sub_n[:j]) * TERA_STRIDE
         self.merger.merge_fixed(out=out[off:], write_eof=(j == C - 1))
@@ -303,6 +307,32 @@ class TeraSortJob:
         }
         res["ok"] = bad == 0 and eof_ok and range_ok and status == 0 and res["count_match"] and res["fingerprint_match"]
         return res
+
+    # ------------------------------------------------------------------------------------ failure detection
+    def raise_on_failure(self) -> None:
+        """Synchronises and raises :class:`~uda_b200.runtime.failure.ShuffleTimeout` when a wait or barrier kernel
+        of an earlier step gave up (lost or short push, dead peer)."""
+        from ..runtime.failure import check_wait_status
+
+        torch.cuda.synchronize(self.device)
+        check_wait_status(self.arena.status, f"terasort rank {self.rank}")
+
+    def landed_segments(self):
+        """``(tensor at segment start, rawLength)`` of every run of every sub-partition landed in this rank's arena."""
+        data, segs = self.arena.data(), []
+        for j in range(self.subparts):
+            lay = self.plan.layout(self.rank, j)
+            for s in range(self.world):
+                for m in range(self.maps):
+                    rid = self.plan.run_id(s, m)
+                    segs.append((data[int(lay.run_offsets[rid]):], int(self.plan.index[s, m, self.rank * self.subparts + j, 1])))
+        return segs
+
+    def verify_crc(self) -> None:
+        """Recomputes the IFile CRC32 of every landed segment on the device; raises ChecksumMismatch."""
+        from ..utils.faults import verify_landed_crc
+
+        verify_landed_crc(self.landed_segments())
 
     def close(self) -> None:
         if hasattr(self, "arena"):

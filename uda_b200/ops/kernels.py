@@ -169,6 +169,38 @@ def gather_var(sorted_entries: torch.Tensor, n: int, run_base_dev: torch.Tensor,
                                    dst_off_dev.data_ptr(), dst.data_ptr(), _stream()), "uda_gather_var")
 
 
+def tiebreak_scratch_bytes(n: int) -> int:
+    return int(kernels().uda_tiebreak_scratch_bytes(n))
+
+
+def tiebreak_var(sorted_entries: torch.Tensor, n: int, run_base_dev: torch.Tensor, run_recoff_dev: torch.Tensor, key_kind: int,
+                 tmp_entries: torch.Tensor, scratch: torch.Tensor) -> None:
+    """Exact-comparator re-ordering of equal-prefix groups (in place). No sync."""
+    check(kernels().uda_tiebreak_var(sorted_entries.data_ptr(), n, run_base_dev.data_ptr(), run_recoff_dev.data_ptr(), key_kind,
+                                     tmp_entries.data_ptr(), scratch.data_ptr(), _stream()), "uda_tiebreak_var")
+
+
+def tiebreak_stats(scratch: torch.Tensor, n: int) -> Tuple[int, int, int]:
+    """(groups re-ordered, largest such group, entries moved) of the last :func:`tiebreak_var`. Synchronises."""
+    out = (C.c_ulonglong * 3)()
+    check(kernels().uda_tiebreak_stats(scratch.data_ptr(), n, out, _stream()), "uda_tiebreak_stats")
+    return int(out[0]), int(out[1]), int(out[2])
+
+
+def scan_u32_to_u64(v: torch.Tensor, m: Optional[int] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Exclusive 64-bit prefix of an int32/uint32 tensor: ``m+1`` int64 entries, ``out[m]`` = total. No sync."""
+    m = v.numel() if m is None else m
+    if out is None:
+        out = torch.empty(m + 1, dtype=torch.int64, device=v.device)
+    scratch = torch.empty(int(kernels().uda_scan_u32_to_u64_scratch_bytes(m)), dtype=torch.uint8, device=v.device)
+    check(kernels().uda_scan_u32_to_u64(v.data_ptr(), m, out.data_ptr(), scratch.data_ptr(), _stream()), "uda_scan_u32_to_u64")
+    return out
+
+
+def write_eof_at(dst: torch.Tensor, total_dev: Optional[torch.Tensor]) -> None:
+    check(kernels().uda_write_eof_at(dst.data_ptr(), _p(total_dev), _stream()), "uda_write_eof_at")
+
+
 # ------------------------------------------------------------------------------------------------ shuffle
 def push_scratch_bytes(nseg: int) -> int:
     return int(kernels().uda_push_scratch_bytes(nseg))
@@ -228,8 +260,7 @@ def ifile_encode_var(keys: torch.Tensor, key_off: torch.Tensor, klen: torch.Tens
     sizes = torch.empty(n, dtype=torch.int32, device=keys.device)
     check(kernels().uda_ifile_encoded_sizes(klen.data_ptr(), vlen.data_ptr(), n, sizes.data_ptr(), _stream()),
           "uda_ifile_encoded_sizes")
-    off = torch.zeros(n + 1, dtype=torch.int64, device=keys.device)
-    torch.cumsum(sizes.to(torch.int64), 0, out=off[1:])
+    off = scan_u32_to_u64(sizes, n)
     total = int(off[-1].item())
     out = torch.empty(total + 2 + 16, dtype=torch.uint8, device=keys.device)
     check(kernels().uda_ifile_encode_var(keys.data_ptr(), key_off.data_ptr(), klen.data_ptr(), vals.data_ptr(),

@@ -53,8 +53,14 @@ class RawDeviceBuffer:
 
 
 def dev_malloc(nbytes: int) -> RawDeviceBuffer:
+    """cudaMalloc outside the torch allocator. A failure is an :class:`ArenaAllocationFailed` (the counterpart of
+    the reference's MR registration failure, src/DataNet/RDMAComm.cc:67-154), which the host answers with fallback."""
+    from ..runtime.failure import ArenaAllocationFailed
+
     p = C.c_void_p()
-    check(kernels().uda_dev_malloc(C.byref(p), nbytes), "uda_dev_malloc")
+    rc = kernels().uda_dev_malloc(C.byref(p), nbytes)
+    if rc != 0 or not p.value:
+        raise ArenaAllocationFailed(f"uda_dev_malloc({nbytes} bytes) failed: CUDA error {rc}")
     return RawDeviceBuffer(p.value, nbytes, owner=True)
 
 
