@@ -43,9 +43,13 @@ def parse_args():
     ap.add_argument("--records-per-gpu", type=int, default=125_000_000)
     ap.add_argument("--maps-per-gpu", type=int, default=8)
     ap.add_argument("--subparts", type=int, default=0,
-                    help="sub-partitions per reducer pushed/merged as a pipeline (0 = auto: 1 on one GPU, 4 on several)")
+                    help="sub-partitions per reducer pushed/merged as a pipeline (0 = auto: 1 on one GPU, 8 on several)")
     ap.add_argument("--push-ctas", type=int, default=-1,
-                    help="grid of the push kernel (0 = 8 CTAs per SM; -1 = auto: 0 on one GPU, 296 when pipelined)")
+                    help="grid of the push kernel (-1 = auto: all SMs on one GPU; pipelined: 32 SMs for tma, 296 CTAs for lsu)")
+    ap.add_argument("--push-mode", default="auto", choices=["auto", "lsu", "tma"],
+                    help="lsu: load/store push kernel on all SMs; tma: copy-engine push on --push-ctas SMs of its own (one launch "
+                         "for all sub-partitions); auto: lsu on one GPU, tma on several")
+    ap.add_argument("--tma-flush", type=int, default=0, help="tma push: chunks between landed-counter advances (0 = library default)")
     ap.add_argument("--merge-ctas-per-sm", type=int, default=0, help="cap on resident merge CTAs per SM (0 = occupancy limit)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-check", action="store_true")
@@ -153,17 +157,24 @@ def main():
     else:
         from uda_b200.models.terasort import TeraSortJob as Job
 
-    # measured on 8xB200 (profiles/pipeline_sweep.md): pipelining 4 sub-partitions with a 2-CTA/SM push grid
-    # takes the 8-GPU step from 33.6 to 29.6 ms; on one GPU (no NVLink wait to hide) it does not pay
+    # measured on 8xB200 (profiles/pipeline_sweep.md): 8 sub-partitions pushed by the copy-engine kernel on 32 SMs
+    # of its own while the merge keeps the other 116 take the 8-GPU step from 33.6 ms (push, then merge) and 29.6 ms
+    # (4 sub-partitions, load/store push sharing all SMs with the merge) to 25.5 ms; on one GPU (no NVLink wait to
+    # hide) pipelining does not pay
+    if a.push_mode == "auto":
+        a.push_mode = "tma" if world > 1 else "lsu"
     if a.subparts <= 0:
-        a.subparts = 4 if world > 1 else 1
+        a.subparts = 8 if world > 1 else 1
     if a.push_ctas < 0:
-        a.push_ctas = 296 if a.subparts > 1 else 0
+        a.push_ctas = (32 if a.push_mode == "tma" else 296) if a.subparts > 1 else 0
+    if a.tma_flush > 0:
+        from uda_b200._lib import check, kernels
+        check(kernels().uda_shuffle_push_tma_set_flush(a.tma_flush), "uda_shuffle_push_tma_set_flush")
     if a.impl == "nccl_sort":
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev).setup()
     else:
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev, subparts=a.subparts, push_ctas=a.push_ctas,
-                  merge_ctas_per_sm=a.merge_ctas_per_sm).setup()
+                  merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode).setup()
     total_bytes = float(a.records_per_gpu) * RECORD_BYTES * world
 
     def timed(fn, steps, warmup, sample_clocks):
@@ -192,6 +203,9 @@ def main():
     if hasattr(job, "step_phases"):
         ph = [job.step_phases() for _ in range(3)][-1]
         phases = {k: max_over_ranks(v) for k, v in ph.items()}
+        if hasattr(job, "step_timeline") and getattr(job, "subparts", 1) > 1:
+            tl = [job.step_timeline() for _ in range(3)][-1]
+            phases["timeline_rank0_ms"] = {k: [round(x, 2) for x in v] for k, v in tl.items()}
 
     check = None
     if not a.no_check:
@@ -225,7 +239,7 @@ def main():
                 "model": "TeraSort 100 GB/8 GPUs (12.5 GB per GPU), 100-byte teragen records, IFile-framed sorted MOFs in HBM",
                 "global_batch": a.records_per_gpu * world, "seq_len": RECORD_BYTES,
                 "records_per_gpu": a.records_per_gpu, "maps_per_gpu": a.maps_per_gpu, "runs_per_reducer": a.maps_per_gpu * world,
-                "subparts": a.subparts, "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
+                "subparts": a.subparts, "push_mode": a.push_mode, "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
                 "parallelism": f"partition-parallel a2a x{world} (one reducer per GPU)",
                 "l2_policy": "inputs (12.75 GB/GPU) larger than the 126 MB L2; no flush needed",
                 "timed_region": "shuffle push + flag acquire + key normalise + k-way merge + record gather (map-side sort is set-up)",

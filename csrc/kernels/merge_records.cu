@@ -55,6 +55,7 @@ struct FrParams {
     unsigned long long kmin, kmax;
     int shift, pad;
     unsigned long long fallback_buckets, fallback_iters;
+    unsigned int next_bucket, pad2;   // dynamic bucket scheduler of fr_merge_kernel (reset by fr_range_kernel)
 };
 
 __device__ __forceinline__ void load_key80(const uint8_t* p, int key_len, unsigned long long* w0, uint32_t* t) {
@@ -115,6 +116,7 @@ __global__ void fr_range_kernel(const UdaRunDesc* __restrict__ runs, int k, int 
         while (shift < 64 && (range >> shift) >= (unsigned long long)FR_NB) ++shift;
         prm->kmin = lo; prm->kmax = hi; prm->shift = shift;
         prm->fallback_buckets = 0; prm->fallback_iters = 0;
+        prm->next_bucket = 0;
     }
 }
 
@@ -425,7 +427,15 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride_rt
     __syncthreads();
     uint32_t phase = 0;
 
-    for (int q = blockIdx.x; q < G; q += gridDim.x) {
+    // Buckets are handed out through a counter, not by blockIdx stride: when part of the SMs is held by a
+    // concurrently running push kernel, the CTAs that do get an SM still share the work evenly.
+    __shared__ int s_q;
+    for (;;) {
+        if (threadIdx.x == 0) s_q = (int)atomicAdd(&prm->next_bucket, 1u);
+        __syncthreads();
+        const int q = s_q;
+        __syncthreads();
+        if (q >= G) break;
         const uint32_t obase = outoff[q];
         const uint32_t total = outoff[q + 1] - obase;
         if (total == 0) continue;

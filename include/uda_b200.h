@@ -132,6 +132,17 @@ int uda_write_eof_at(void* dst, const unsigned long long* total_dev, cudaStream_
  *      :44-136 credits) --------------------------------------------------------------------------- */
 long long uda_push_scratch_bytes(int nseg);
 int uda_shuffle_push(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, cudaStream_t stream);
+/* Copy-engine variant of the push: `nsub` descriptor tables of nseg/nsub entries each, concatenated in the order
+ * they must land (sub-partition 0 first). `num_ctas` single-warp CTAs (default 32) each claim one SM through a
+ * 192 KiB shared-memory ring and move 32 KiB chunks with cp.async.bulk in both directions; the landed-byte counters
+ * are advanced per chunk exactly as by uda_shuffle_push. `nway` interleaves the chunk order inside a sub-partition
+ * over the peer-major descriptor order. scratch: uda_push_tma_scratch_bytes(nseg). */
+long long uda_push_tma_scratch_bytes(int nseg);
+int uda_shuffle_push_tma(const UdaPushDesc* descs_dev, int nseg, int nsub, int nway, void* scratch, int num_ctas,
+                         cudaStream_t stream);
+/* chunks (16 KiB each) a copy warp completes between two advances of the landed-byte counters (1..64, default 8):
+ * each advance costs one system-scope fence */
+int uda_shuffle_push_tma_set_flush(int chunks);
 /* chunk-order interleave factor of uda_shuffle_push (number of destination ranks; 1 = sequential) */
 int uda_shuffle_push_set_interleave(int nway);
 /* No counterpart in the reference (it has no device code and nothing that must avoid allocation).

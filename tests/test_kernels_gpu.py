@@ -308,24 +308,27 @@ def test_shuffle_push_loopback(K):
 
 
 # ------------------------------------------------------------------------------------------- end to end
-@pytest.mark.parametrize("n,maps,key_bits,subparts", [(50_000, 4, 0, 1), (200_000, 7, 0, 1), (30_000, 3, 5, 1), (6_000_000, 2, 0, 1),
-                                                       (300_000, 5, 0, 4), (40_000, 3, 4, 3)])
-def test_terasort_job_single_gpu(built, n, maps, key_bits, subparts):
+@pytest.mark.parametrize("n,maps,key_bits,subparts,mode", [(50_000, 4, 0, 1, "lsu"), (200_000, 7, 0, 1, "lsu"), (30_000, 3, 5, 1, "lsu"),
+                                                            (6_000_000, 2, 0, 1, "lsu"), (300_000, 5, 0, 4, "lsu"), (40_000, 3, 4, 3, "lsu"),
+                                                            (50_000, 4, 0, 1, "tma"), (3_000_000, 5, 0, 4, "tma"), (40_000, 3, 4, 3, "tma"),
+                                                            (7, 2, 0, 2, "tma")])
+def test_terasort_job_single_gpu(built, n, maps, key_bits, subparts, mode):
     from uda_b200.models.terasort import TeraSortJob
     from uda_b200.utils import ifile as _if
 
-    job = TeraSortJob(n, maps, device=_dev(), key_bits=key_bits, subparts=subparts).setup()
+    job = TeraSortJob(n, maps, device=_dev(), key_bits=key_bits, subparts=subparts, push_mode=mode, push_ctas=8 if mode == "tma" else 0).setup()
     try:
         # every MOF is a valid Hadoop file.out + index with correct CRCs
         mof = job.mofs[0]
         recs = _if.read_partition(mof.file_bytes(), mof.index_records()[0], verify_crc=True)
         assert len(recs) == int(mof.nrec[0]) and all(len(k) == 10 and len(v) == 90 for k, v in recs[:10])
         assert [k for k, _ in recs] == sorted(k for k, _ in recs)
-        for _ in range(2):  # second step checks the cumulative flag protocol
+        for _ in range(3 if mode == "tma" else 2):  # later steps check the cumulative flag protocol
             out = job.step()
         res = job.check(out)
         assert res["ok"], res
         assert out.numel() == n * 102 + 2
+        job.verify_crc()  # every landed segment is byte-identical to what the map wrote
     finally:
         job.close()
 

@@ -21,11 +21,12 @@ def _torchrun(n, script, *args, timeout=600):
     return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
 
 
-@pytest.mark.parametrize("world,subparts", [(2, 1), (2, 3), (4, 1), (8, 1), (8, 4)])
-def test_terasort_multi_rank(built, world, subparts):
+@pytest.mark.parametrize("world,subparts,mode", [(2, 1, "lsu"), (2, 3, "lsu"), (4, 1, "lsu"), (8, 1, "lsu"), (8, 4, "lsu"),
+                                                 (2, 1, "tma"), (2, 4, "tma"), (8, 4, "tma")])
+def test_terasort_multi_rank(built, world, subparts, mode):
     if _ngpu() < world:
         pytest.skip(f"needs {world} GPUs")
-    p = _torchrun(world, "mp_terasort.py", 300_000, 3, 2, subparts)
+    p = _torchrun(world, "mp_terasort.py", 300_000 if mode == "lsu" else 2_000_000, 3, 3, subparts, mode)
     text = p.stdout + "\n" + p.stderr
     assert p.returncode == 0, text[-6000:]
     assert text.count("MPRESULT") == world and text.count('"ok": true') == world, text[-6000:]

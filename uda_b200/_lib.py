@@ -62,6 +62,9 @@ _PROTOS = {
     "uda_push_scratch_bytes": (c_ll, [c_int]),
     "uda_shuffle_push": (c_int, [c_vp, c_int, c_vp, c_int, c_vp]),
     "uda_shuffle_push_set_interleave": (c_int, [c_int]),
+    "uda_push_tma_scratch_bytes": (c_ll, [c_int]),
+    "uda_shuffle_push_tma_set_flush": (c_int, [c_int]),
+    "uda_shuffle_push_tma": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_int, c_vp]),
     "uda_wait_flags": (c_int, [c_vp, c_vp, c_int, c_ull, c_vp, c_vp]),
     "uda_barrier_all": (c_int, [c_vp, c_int, c_int, c_ull, c_ull, c_vp, c_vp]),
     "uda_partition_count": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp]),

@@ -53,7 +53,8 @@ class TeraSortJob:
     E2E_RING_BYTES = 256 << 20
 
     def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 1234,
-                 key_bits: int = 0, group=None, push_ctas: int = 0, subparts: int = 1, merge_ctas_per_sm: int = 0):
+                 key_bits: int = 0, group=None, push_ctas: int = 0, subparts: int = 1, merge_ctas_per_sm: int = 0,
+                 push_mode: str = "lsu"):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -67,6 +68,10 @@ class TeraSortJob:
         #: HBM-bound) push overlaps the issue-bound merge. 1 = push everything, then merge.
         self.subparts = max(1, subparts)
         self.merge_ctas_per_sm = merge_ctas_per_sm
+        #: "lsu": load/store push kernel on every SM (one launch per sub-partition); "tma": copy-engine push, ONE
+        #: launch for all sub-partitions on `push_ctas` SMs of its own, the merge keeps the remaining SMs
+        assert push_mode in ("lsu", "tma")
+        self.push_mode = push_mode
         #: polls of the landed-byte counters before the wait kernel gives up and records a time-out in the arena's
         #: status word (the watchdog that turns a lost push into a failure up-call instead of a hang)
         self.wait_max_spins = 50_000_000
@@ -112,6 +117,8 @@ class TeraSortJob:
         self.push_descs_dev = self._push_tables([m.data.data_ptr() for m in self.mofs])
         self.nseg = self.maps * P
         self.push_scratch = [torch.empty(K.push_scratch_bytes(self.nseg), dtype=torch.uint8, device=dev) for _ in range(C)]
+        self.push_descs_all = torch.cat(self.push_descs_dev).contiguous()
+        self.push_tma_scratch = torch.empty(K.push_tma_scratch_bytes(self.nseg * C), dtype=torch.uint8, device=dev)
         K.shuffle_push_set_interleave(P)  # local copy and the P-1 remote pushes run concurrently
         K.merge_records_set_ctas_per_sm(self.merge_ctas_per_sm)
         self.sub_runs, self.sub_n, expect = [], [], []
@@ -168,20 +175,68 @@ class TeraSortJob:
         if self.world > 1:
             self.arena.barrier()
         self.expect.add_(self.expect_step)
+        tma = self.push_mode == "tma"
+        if tma:
+            all_descs = self.push_descs_all if descs is self.push_descs_dev else torch.cat(descs).contiguous()
         if C == 1:
-            K.shuffle_push(descs[0], self.nseg, self.push_scratch[0], self.push_ctas)
+            if tma:
+                K.shuffle_push_tma(all_descs, self.nseg, 1, self.world, self.push_tma_scratch, self.push_ctas)
+            else:
+                K.shuffle_push(descs[0], self.nseg, self.push_scratch[0], self.push_ctas)
             self._merge_sub(0, out)
         else:
             self.ev_go.record(cur)
             with torch.cuda.stream(self.push_stream):
                 self.push_stream.wait_event(self.ev_go)
-                for j in range(C):
-                    K.shuffle_push(descs[j], self.nseg, self.push_scratch[j], self.push_ctas)
+                if tma:
+                    K.shuffle_push_tma(all_descs, self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas)
+                else:
+                    for j in range(C):
+                        K.shuffle_push(descs[j], self.nseg, self.push_scratch[j], self.push_ctas)
                 self.ev_pushed.record(self.push_stream)
             for j in range(C):
                 self._merge_sub(j, out)
             cur.wait_event(self.ev_pushed)  # the step is over only when this rank's own pushes have retired
         return out[: self.n_out * TERA_STRIDE + 2]
+
+    def step_timeline(self) -> dict:
+        """One pipelined step with an event after every push (side stream) and around every sub-partition merge
+        (main stream); times in ms since the start of the step (diagnostics for the overlap)."""
+        C = self.subparts
+        if C == 1:
+            return {}
+        cur = torch.cuda.current_stream(self.device)
+        mk = lambda: torch.cuda.Event(enable_timing=True)
+        t0, pushed, m0, m1 = mk(), [mk() for _ in range(C)], [mk() for _ in range(C)], [mk() for _ in range(C)]
+        if self.world > 1:
+            self.arena.barrier()
+        self.expect.add_(self.expect_step)
+        t0.record(cur)
+        self.ev_go.record(cur)
+        with torch.cuda.stream(self.push_stream):
+            self.push_stream.wait_event(self.ev_go)
+            if self.push_mode == "tma":
+                K.shuffle_push_tma(self.push_descs_all, self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas)
+                for j in range(C):
+                    pushed[j].record(self.push_stream)
+            else:
+                for j in range(C):
+                    K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas)
+                    pushed[j].record(self.push_stream)
+            self.ev_pushed.record(self.push_stream)
+        nruns = self.plan.nruns
+        for j in range(C):
+            K.wait_flags(self.arena.flags()[j * nruns:(j + 1) * nruns], self.expect[j * nruns:(j + 1) * nruns], nruns, self.arena.status,
+                         self.wait_max_spins)
+            m0[j].record(cur)
+            self.merger.use_runs(self.sub_runs[j])
+            self.merger.merge_fixed(out=self.merger.out[sum(self.sub_n[:j]) * TERA_STRIDE:], write_eof=(j == C - 1))
+            m1[j].record(cur)
+        cur.wait_event(self.ev_pushed)
+        torch.cuda.synchronize(self.device)
+        self.steps_run += 1
+        return {"pushed_ms": [t0.elapsed_time(e) for e in pushed], "merge_start_ms": [t0.elapsed_time(e) for e in m0],
+                "merge_end_ms": [t0.elapsed_time(e) for e in m1]}
 
     def step_phases(self) -> dict:
         """One step with CUDA events between the phases (diagnostics; not used for the headline number)."""
@@ -190,8 +245,12 @@ class TeraSortJob:
             self.arena.barrier()
         self.expect.add_(self.expect_step)
         ev[0].record()
-        for j in range(self.subparts):  # phases are measured un-overlapped, one sub-partition after the other
-            K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas)
+        if self.push_mode == "tma":
+            K.shuffle_push_tma(self.push_descs_all, self.nseg * self.subparts, self.subparts, self.world, self.push_tma_scratch,
+                               self.push_ctas)
+        else:
+            for j in range(self.subparts):  # phases are measured un-overlapped, one sub-partition after the other
+                K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas)
         ev[1].record()
         nr = self.plan.nruns * self.subparts
         K.wait_flags(self.arena.flags(), self.expect, nr, self.arena.status)

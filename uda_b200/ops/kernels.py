@@ -210,6 +210,17 @@ def shuffle_push(descs_dev: torch.Tensor, nseg: int, scratch: torch.Tensor, max_
     check(kernels().uda_shuffle_push(descs_dev.data_ptr(), nseg, scratch.data_ptr(), max_ctas, _stream()), "uda_shuffle_push")
 
 
+def push_tma_scratch_bytes(nseg: int) -> int:
+    return int(kernels().uda_push_tma_scratch_bytes(nseg))
+
+
+def shuffle_push_tma(descs_dev: torch.Tensor, nseg: int, nsub: int, nway: int, scratch: torch.Tensor, num_ctas: int = 0) -> None:
+    """Copy-engine push: ``nsub`` equally long descriptor tables, concatenated, pushed in order by ``num_ctas``
+    single-warp CTAs that each own an SM (TMA bulk load -> shared-memory ring -> TMA bulk store to the peer)."""
+    check(kernels().uda_shuffle_push_tma(descs_dev.data_ptr(), nseg, nsub, nway, scratch.data_ptr(), num_ctas, _stream()),
+          "uda_shuffle_push_tma")
+
+
 def shuffle_push_set_interleave(nway: int) -> None:
     check(kernels().uda_shuffle_push_set_interleave(nway), "uda_shuffle_push_set_interleave")
 
