@@ -249,8 +249,11 @@ void FetchSource::send(int slot, const FetchRequest& r) {
                     // prefetch the next chunk into the other buffer
                     if (state_[other] == EMPTY && fetched_ < part_len_ && ack.sent > 0) { next = prepare(other); more = true; }
                 }
+                // notify under the lock: the destructor waits on cv_ for "no fetch in flight" and frees this object as
+                // soon as it can re-acquire mu_, so nothing of *this may be touched after the unlock unless a new fetch
+                // (more == true, state FETCHING) keeps the object alive
+                cv_.notify_all();
             }
-            cv_.notify_all();
             if (more) send(other, next);
         });
     } catch (const UdaError& e) {
@@ -259,8 +262,8 @@ void FetchSource::send(int slot, const FetchRequest& r) {
             std::lock_guard<std::mutex> lk(mu_);
             failed_ = true;
             state_[slot] = EMPTY;
+            cv_.notify_all();  // under the lock, see above
         }
-        cv_.notify_all();
     }
 }
 

@@ -139,8 +139,12 @@ bool ShuffleServer::reply(const std::shared_ptr<Connection>& c, uint64_t src_req
 
 void ShuffleServer::stop() {
     if (!running_.exchange(false)) return;
-    if (listen_fd_ >= 0) { ::shutdown(listen_fd_, SHUT_RDWR); ::close(listen_fd_); listen_fd_ = -1; }
+    // wake accept() with shutdown(), join, and only then close: closing first would let the descriptor number be
+    // reused while the accept thread may still be about to call accept() on it
+    const int lfd = listen_fd_.load();
+    if (lfd >= 0) ::shutdown(lfd, SHUT_RDWR);
     if (accept_thread_.joinable()) accept_thread_.join();
+    if (lfd >= 0) { ::close(lfd); listen_fd_ = -1; }
     std::vector<std::thread> ts;
     {
         std::lock_guard<std::mutex> lk(mu_);

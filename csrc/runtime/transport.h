@@ -58,7 +58,8 @@ public:
 private:
     void accept_loop();
     void serve(std::shared_ptr<Connection> c);
-    int port_, listen_fd_ = -1;
+    int port_;
+    std::atomic<int> listen_fd_{-1};  // read by the accept thread, closed by stop()
     RequestHandler on_request_;
     std::atomic<bool> running_{false};
     std::thread accept_thread_;

@@ -1,0 +1,17 @@
+#!/usr/bin/env bash
+# Host runtime under ASAN / TSAN / UBSAN: builds build/<kind>/libuda.so + the native tests and runs
+#   * the mock-JVM test of the JNI bridge (threads attach/detach, up-calls, failure latch)
+#   * the plumbing self-tests through the C API (queues, thread wrapper)
+# usage: scripts/ci/host_sanitizers.sh address|thread|undefined
+set -euo pipefail
+kind="${1:-address}"
+root="$(cd "$(dirname "$0")/../.." && pwd)"
+cd "$root"
+python tools/build.py --sanitize "$kind"
+# leak detection is off: the mock JVM of the test never frees its fake jobjects (a real JVM collects local references)
+export ASAN_OPTIONS="detect_leaks=0:abort_on_error=1" TSAN_OPTIONS="halt_on_error=1 second_deadlock_stack=1" UBSAN_OPTIONS="halt_on_error=1"
+tmp="$(mktemp -d)"
+trap 'rm -rf "$tmp"' EXIT
+# the test program dlopens the library it is given: the sanitizer runtime must come first in the process
+"build/$kind/test_jni_mock" "build/$kind/libuda.so" "$tmp"
+echo "host sanitizer run ($kind): ok"

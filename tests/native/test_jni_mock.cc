@@ -290,10 +290,18 @@ int main(int argc, char** argv) {
         }
     }
     CHECK(port > 0);
-    struct Sink { std::string data; std::atomic<int> over{0}, fail{0}; } sink;
+    struct Sink {
+        std::mutex mu;
+        std::string data;
+        std::atomic<int> over{0}, fail{0};
+        size_t size() { std::lock_guard<std::mutex> lk(mu); return data.size(); }
+    } sink;
     uda_host_callbacks_t cb{};
     cb.user = &sink;
-    cb.data_from_uda = [](void* u, const void* b, int n) { ((Sink*)u)->data.append((const char*)b, (size_t)n); };
+    cb.data_from_uda = [](void* u, const void* b, int n) {
+        std::lock_guard<std::mutex> lk(((Sink*)u)->mu);
+        ((Sink*)u)->data.append((const char*)b, (size_t)n);
+    };
     cb.fetch_over_message = [](void* u) { ++((Sink*)u)->over; };
     cb.failure_in_uda = [](void* u) { ++((Sink*)u)->fail; };
     std::string ports = std::to_string(port);
@@ -303,8 +311,8 @@ int main(int argc, char** argv) {
     CHECK(uda_rt_do_command(cons, "12:7:2:job_1:attempt_r_0:0:16384:4096:org.apache.hadoop.io.LongWritable:null:0:67108864:0") == 0);
     CHECK(uda_rt_do_command(cons, "5:4:127.0.0.1:job_1:attempt_m_0:0") == 0);
     CHECK(uda_rt_do_command(cons, "5:4:127.0.0.1:job_1:attempt_m_1:0") == 0);
-    for (int i = 0; i < 3000 && sink.data.size() < expect.size() && !sink.fail; ++i) std::this_thread::sleep_for(std::chrono::milliseconds(10));
-    CHECK(sink.fail == 0 && sink.data == expect && sink.over >= 1);
+    for (int i = 0; i < 3000 && sink.size() < expect.size() && !sink.fail; ++i) std::this_thread::sleep_for(std::chrono::milliseconds(10));
+    { std::lock_guard<std::mutex> lk(sink.mu); CHECK(sink.fail == 0 && sink.data == expect && sink.over >= 1); }
     CHECK(has_call("getPathUda job_1 attempt_m_0 0") && has_call("getPathUda job_1 attempt_m_1 0"));
     CHECK(has_call("GetFieldID startOffset J") && has_call("GetFieldID rawLength J") && has_call("GetFieldID partLength J") &&
           has_call("GetFieldID pathMOF Ljava/lang/String;"));

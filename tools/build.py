@@ -114,7 +114,31 @@ def build(verbose: bool = False) -> dict:
     return out
 
 
+def build_host_sanitized(kind: str) -> dict:
+    """Host runtime + native tests under ``-fsanitize=<kind>`` (address | thread | undefined) in build/<kind>/.
+    The reference has no sanitizer targets; its known latent races are exactly what TSAN is for."""
+    assert kind in ("address", "thread", "undefined")
+    out_dir = ROOT / "build" / kind
+    out_dir.mkdir(parents=True, exist_ok=True)
+    cc = sorted((ROOT / "csrc" / "runtime").glob("*.cc")) + sorted((ROOT / "csrc" / "jni").glob("*.cc"))
+    flags = [f for f in CXX_FLAGS if f != "-O2"] + ["-O1", "-fno-omit-frame-pointer", f"-fsanitize={kind}", f'-DVERSION_UDA="{uda_version()}"']
+    rlib = out_dir / "libuda.so"
+    # the sanitizer runtimes ship with the distribution compiler, not necessarily with $CXX
+    cxx = os.environ.get("SAN_CXX", "/usr/bin/g++" if Path("/usr/bin/g++").exists() else CXX)
+    _run([cxx, *flags, "-shared", "-o", str(rlib), *map(str, cc), "-ldl"])
+    out = {"runtime": rlib}
+    for src in sorted((ROOT / "tests" / "native").glob("*.cc")):
+        exe = out_dir / src.stem
+        _run([cxx, *flags, str(src), "-o", str(exe), f"-L{out_dir}", "-luda", f"-Wl,-rpath,{out_dir}", "-ldl"])
+        out[src.stem] = exe
+    return out
+
+
 if __name__ == "__main__":
+    if "--sanitize" in sys.argv:
+        for k, v in build_host_sanitized(sys.argv[sys.argv.index("--sanitize") + 1]).items():
+            print(f"built {k}: {v}")
+        sys.exit(0)
     res = build(verbose="-v" in sys.argv)
     for k, v in res.items():
         print(f"built {k}: {v}")
