@@ -324,3 +324,24 @@ def test_log_line_contract(built, tmp_path):
                    for _, m in cons.logs)
     finally:
         cons.close(); prov.close()
+
+
+def test_reader_bench_selftest(built):
+    """N19: the native reader benchmark (counterpart of src/tests/AIOHandler_test.cc) agrees between back-ends."""
+    import subprocess
+    p = subprocess.run([str(built["reader_bench"])], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert p.stdout.count("BW:") == 3 and "checksums agree" in p.stdout
+
+
+def test_regression_driver_parses_matrix(tmp_path):
+    """The single-node regression driver reads its matrix and produces a report without executing anything."""
+    import json, subprocess, sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    p = subprocess.run([sys.executable, str(root / "scripts" / "regression" / "auto_tester.py"), "--out", str(tmp_path),
+                        "--phases", "input,control,configure,analyze,view,exit"], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stdout + p.stderr
+    rep = json.loads((tmp_path / "report.json").read_text())
+    names = [t["name"] for t in rep["tests"]]
+    assert "terasort-8gpu" in names and "plumbing-online" in names and len(names) >= 10
