@@ -263,6 +263,14 @@ long long uda_rt_snappy_store(const unsigned char* in, long long n, unsigned cha
     return (long long)v.size();
 }
 
+long long uda_rt_snappy_compress(const unsigned char* in, long long n, unsigned char* out, long long cap) {
+    std::vector<uint8_t> v;
+    snappy_compress(in, (size_t)n, &v);
+    if ((long long)v.size() > cap) return -1;
+    memcpy(out, v.data(), v.size());
+    return (long long)v.size();
+}
+
 // out4 = {buffer_size, pairs, pair0, pair1}; returns 0, or 1/2 for the two sizing failures
 int uda_rt_plan_memory(int num_maps, long long max_buf, long long min_buf, long long shuffle_mem, int compressed, double ratio,
                        long long* out4) {

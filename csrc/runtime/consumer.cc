@@ -115,6 +115,68 @@ bool snappy_uncompress_builtin(const uint8_t* in, size_t n, uint8_t* out, size_t
     return op == out_len;
 }
 
+// Greedy single-pass Snappy compressor (hash of 4 bytes -> last position, copies with 2-byte offsets). The
+// reference only decompresses (the map side compresses inside Hadoop); this exists so that tests and benchmarks can
+// produce real compressed segments without a libsnappy on the box.
+namespace {
+inline uint32_t load32(const uint8_t* p) { uint32_t v; memcpy(&v, p, 4); return v; }
+void emit_literal(const uint8_t* p, size_t len, std::vector<uint8_t>* out) {
+    while (len) {
+        const size_t l = std::min<size_t>(len, 65536);
+        if (l <= 60) out->push_back((uint8_t)((l - 1) << 2));
+        else if (l <= 256) { out->push_back(60 << 2); out->push_back((uint8_t)(l - 1)); }
+        else { out->push_back(61 << 2); out->push_back((uint8_t)((l - 1) & 0xFF)); out->push_back((uint8_t)((l - 1) >> 8)); }
+        out->insert(out->end(), p, p + l);
+        p += l; len -= l;
+    }
+}
+void emit_copy(size_t off, size_t len, std::vector<uint8_t>* out) {
+    while (len) {
+        size_t l = std::min<size_t>(len, 64);
+        if (len - l > 0 && len - l < 4) l = len - 4;             // never leave a tail shorter than a copy may be
+        if (l >= 4 && l <= 11 && off < 2048) {                    // 1-byte-offset form
+            out->push_back((uint8_t)(1 | ((l - 4) << 2) | ((off >> 8) << 5)));
+            out->push_back((uint8_t)(off & 0xFF));
+        } else {
+            out->push_back((uint8_t)(2 | ((l - 1) << 2)));
+            out->push_back((uint8_t)(off & 0xFF));
+            out->push_back((uint8_t)(off >> 8));
+        }
+        len -= l;
+    }
+}
+}  // namespace
+
+size_t snappy_compress(const uint8_t* in, size_t n, std::vector<uint8_t>* out) {
+    out->clear();
+    uint64_t v = n;
+    do {
+        uint8_t b = v & 0x7F;
+        v >>= 7;
+        out->push_back(b | (v ? 0x80 : 0));
+    } while (v);
+    constexpr int kBits = 14;
+    std::vector<uint32_t> table(1u << kBits, 0xFFFFFFFFu);
+    size_t ip = 0, lit = 0;
+    while (ip + 4 <= n) {
+        const uint32_t h = (load32(in + ip) * 0x1E35A7BDu) >> (32 - kBits);
+        const uint32_t cand = table[h];
+        table[h] = (uint32_t)ip;
+        if (cand != 0xFFFFFFFFu && ip - cand <= 65535 && load32(in + cand) == load32(in + ip)) {
+            size_t len = 4;
+            while (ip + len < n && in[cand + len] == in[ip + len]) ++len;
+            emit_literal(in + lit, ip - lit, out);
+            emit_copy(ip - cand, len, out);
+            ip += len;
+            lit = ip;
+        } else {
+            ++ip;
+        }
+    }
+    emit_literal(in + lit, n - lit, out);
+    return out->size();
+}
+
 size_t snappy_compress_literal(const uint8_t* in, size_t n, std::vector<uint8_t>* out) {
     out->clear();
     uint64_t v = n;

@@ -80,6 +80,7 @@ enum class Codec { NONE, SNAPPY, LZO };
 bool codec_decompress(Codec c, const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len, const HostCallbacks* host);
 Codec codec_for_class(const std::string& java_class);  // "null" -> NONE; unknown -> throws (fallback contract)
 bool snappy_uncompress_builtin(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len);
+size_t snappy_compress(const uint8_t* in, size_t n, std::vector<uint8_t>* out);            // greedy LZ77 matcher, real copies
 size_t snappy_compress_literal(const uint8_t* in, size_t n, std::vector<uint8_t>* out);  // test helper: valid, uncompressed stream
 
 // One map output partition being fetched chunk by chunk into a borrowed buffer pair.

@@ -179,6 +179,17 @@ int uda_ifile_encode_var(const void* keys, const long long* key_off, const int* 
                          const long long* val_off, const int* vlen, long long n, const unsigned long long* out_off_dev,
                          void* out, cudaStream_t stream);
 
+/* ---- K9 block decompression on the device (reference: decompress thread + dlopen'ed codecs,
+ *      src/Merger/DecompressorWrapper.cc:168-197, src/Merger/SnappyDecompressor.cc:89-105). A compressed segment is
+ *      Hadoop block framing: [u32 BE rawLen][u32 BE compLen][compLen bytes of raw Snappy] repeated. -------------- */
+long long uda_snappy_table_bytes(int max_blocks);
+/* out2_dev = {blocks found, total plain bytes}; status_dev: 0 ok, 1 more than max_blocks, 2 corrupt block header */
+int uda_snappy_scan_blocks(const void* seg, long long seg_len, int max_blocks, void* table, unsigned long long* out2_dev,
+                           unsigned* status_dev, cudaStream_t stream);
+/* one warp per block; `out` holds the total plain bytes; status_dev becomes 3 when a block is corrupt */
+int uda_snappy_decode_blocks(const void* seg, const void* table, const unsigned long long* nblocks_dev, int max_blocks, void* out,
+                             unsigned* status_dev, cudaStream_t stream);
+
 /* ---- symmetric receive arena plumbing (reference: registered MR + rkey exchange,
  *      src/DataNet/RDMAComm.cc:67-154,178-218, src/DataNet/RDMAComm.h:35-39). These allocate. ---- */
 int uda_dev_malloc(void** ptr, long long bytes);

@@ -53,6 +53,8 @@ int uda_rt_compare_keys(int kind, const unsigned char* a, int la, const unsigned
 int uda_rt_key_kind(const char* java_class);
 int uda_rt_snappy_uncompress(const unsigned char* in, long long n, unsigned char* out, long long out_len);
 long long uda_rt_snappy_store(const unsigned char* in, long long n, unsigned char* out, long long cap);
+/* greedy Snappy compressor with real copy elements (tests / benchmarks; cap >= 32 + n + n/6 is always enough) */
+long long uda_rt_snappy_compress(const unsigned char* in, long long n, unsigned char* out, long long cap);
 int uda_rt_plan_memory(int num_maps, long long max_buf, long long min_buf, long long shuffle_mem, int compressed,
                        double ratio, long long* out4);
 int uda_rt_selftest_queues(void);

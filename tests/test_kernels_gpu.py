@@ -577,3 +577,73 @@ def test_phase_timer_and_metrics(built, tmp_path):
     p = write_metrics("unit_phase_timer", {"phases": s}, directory=str(tmp_path))
     assert p.exists() and "hbm_roofline_frac" in p.read_text()
     job.close()
+
+
+# ------------------------------------------------------------------------------------------- K9 decompression
+@pytest.mark.parametrize("kind,n,block", [("random", 300_000, 65536), ("text", 1_000_000, 262144), ("runs", 500_000, 4096),
+                                          ("tiny", 5, 65536), ("empty", 0, 65536)])
+def test_snappy_decode_blocks(built, kind, n, block):
+    from uda_b200.ops.compress import SnappyDecoder, frame_compress_segment
+    rng = random.Random(n)
+    if kind == "random":
+        plain = bytes(rng.randrange(256) for _ in range(n))
+    elif kind == "text":
+        words = [bytes(rng.choice(b"etaoinshr") for _ in range(rng.randint(1, 9))) for _ in range(200)]
+        plain = b" ".join(rng.choice(words) for _ in range(n // 5))[:n]
+    elif kind == "runs":
+        plain = b"".join(bytes([rng.randrange(256)]) * rng.randint(1, 300) for _ in range(n // 100))[:n]   # self-overlapping matches
+    else:
+        plain = b"abcde"[:n]
+    comp = frame_compress_segment(plain, block)
+    if kind in ("text", "runs"):
+        assert len(comp) < 0.7 * len(plain)       # the test really contains copy elements
+    dev = _dev()
+    seg = torch.from_numpy(np.frombuffer(comp + b"\0" * 16, dtype=np.uint8).copy()).to(dev)
+    dec = SnappyDecoder(dev, max(1, -(-len(plain) // block)))
+    out, raw = dec.decode(seg, len(comp))
+    dec.check(expect_raw=len(plain))
+    assert raw == len(plain) and bytes(out.cpu().numpy()) == plain
+    out2, _ = dec.decode(seg, len(comp), raw_len=len(plain))    # sync-free form
+    assert bytes(out2.cpu().numpy()) == plain
+
+
+def test_snappy_decode_detects_corruption(built):
+    from uda_b200.ops.compress import SnappyDecoder, frame_compress_segment
+    from uda_b200.runtime.failure import UdaFailure
+    plain = b"the quick brown fox jumps over the lazy dog " * 2000
+    comp = bytearray(frame_compress_segment(plain, 16384))
+    comp[8] ^= 0x55                                  # varint length of the first block
+    dev = _dev()
+    seg = torch.from_numpy(np.frombuffer(bytes(comp) + b"\0" * 16, dtype=np.uint8).copy()).to(dev)
+    dec = SnappyDecoder(dev, 16)
+    dec.decode(seg, len(comp), raw_len=len(plain))
+    with pytest.raises(UdaFailure):
+        dec.check()
+    dec2 = SnappyDecoder(dev, 2)                     # table too small for 6 blocks
+    dec2.decode(seg, len(comp), raw_len=len(plain))
+    with pytest.raises(UdaFailure):
+        dec2.check()
+
+
+def test_compressed_segments_through_var_merger(built):
+    """Compressed sorted runs -> device Snappy decode -> VarMerger == CPU oracle."""
+    from uda_b200.ops.compress import SnappyDecoder, frame_compress_segment
+    from uda_b200.ops.varlen import VarMerger
+    dev = _dev()
+    body = _cmp_body(1)
+    runs, segs, keep = [], [], []
+    dec = SnappyDecoder(dev, 64)
+    for r, n in enumerate([800, 1200, 500]):
+        recs = sorted(_tie_records(7 * r + 1, n, 1), key=body)
+        runs.append(recs)
+        plain = ifile.encode_segment(recs, with_crc=False)
+        comp = frame_compress_segment(plain, 8192)
+        t = torch.from_numpy(np.frombuffer(comp + b"\0" * 16, dtype=np.uint8).copy()).to(dev)
+        out, raw = dec.decode(t, len(comp), raw_len=len(plain))
+        dec.check(expect_raw=len(plain))
+        keep.append(out)
+        segs.append((out, raw, n))
+    vm = VarMerger(dev, 1, sum(s[2] for s in segs), len(segs), sum(s[1] for s in segs))
+    out, nbytes = vm.merge(segs)
+    want = ifile.encode_segment(sorted([kv for run in runs for kv in run], key=body), with_crc=False)
+    assert bytes(out.cpu().numpy()) == want

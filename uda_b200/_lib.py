@@ -59,6 +59,9 @@ _PROTOS = {
     "uda_scan_u32_to_u64_scratch_bytes": (c_ll, [c_ll]),
     "uda_scan_u32_to_u64": (c_int, [c_vp, c_ll, c_vp, c_vp, c_vp]),
     "uda_write_eof_at": (c_int, [c_vp, c_vp, c_vp]),
+    "uda_snappy_table_bytes": (c_ll, [c_int]),
+    "uda_snappy_scan_blocks": (c_int, [c_vp, c_ll, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "uda_snappy_decode_blocks": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]),
     "uda_push_scratch_bytes": (c_ll, [c_int]),
     "uda_shuffle_push": (c_int, [c_vp, c_int, c_vp, c_int, c_vp]),
     "uda_shuffle_push_set_interleave": (c_int, [c_int]),
