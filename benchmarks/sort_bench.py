@@ -22,9 +22,10 @@ def main() -> int:
     ap.add_argument("--key-kind", type=int, default=2, help="1 Text, 2 BytesWritable")
     ap.add_argument("--key-len", default="10,100")
     ap.add_argument("--val-len", default="0,200")
-    ap.add_argument("--tie-fraction", type=float, default=0.01)
+    ap.add_argument("--tie-fraction", type=float, default=0.001)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--no-side-index", action="store_true", help="do not ship record offsets: the reducer rediscovers the boundaries (K5)")
     ap.add_argument("--check", action="store_true", help="byte-exact CPU oracle (small inputs only)")
     a = ap.parse_args()
     lr = int(os.environ.get("LOCAL_RANK", "0"))
@@ -37,7 +38,7 @@ def main() -> int:
 
     kl = tuple(int(x) for x in a.key_len.split(","))
     vl = tuple(int(x) for x in a.val_len.split(","))
-    job = SortJob(a.records, a.maps, device=dev, key_kind=a.key_kind, key_len=kl, val_len=vl, tie_fraction=a.tie_fraction).setup()
+    job = SortJob(a.records, a.maps, device=dev, key_kind=a.key_kind, key_len=kl, val_len=vl, tie_fraction=a.tie_fraction, side_index=not a.no_side_index).setup()
     for _ in range(a.warmup):
         out = job.step()
     if world > 1:
@@ -62,7 +63,7 @@ def main() -> int:
            "ms_per_step": ms, "n_gpus": world, "records": total_rec, "bytes": int(total_bytes), "tiebreak_groups": groups,
            "tiebreak_largest_group": largest, "gpu_launches": job.launches_per_step * a.steps,
            "config": {"records_per_gpu": a.records, "maps_per_gpu": a.maps, "key_kind": a.key_kind, "key_len": kl, "val_len": vl,
-                      "tie_fraction": a.tie_fraction}}
+                      "tie_fraction": a.tie_fraction, "side_index": not a.no_side_index}}
     if a.check:
         c = job.check(out)
         res["ok"] = res["validated"] = bool(c["ok_all"])

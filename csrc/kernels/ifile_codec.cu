@@ -51,24 +51,37 @@ constexpr int DC_CHUNK = 4096;           // bytes per chunk (one CTA)
 constexpr int DC_THREADS = 256;
 constexpr unsigned DC_EXIT = 0x80000000u;  // high bit: the chain left the chunk; low bits = overshoot
 
-// "next record start" if a record header began at absolute position p; returns p for EOF / invalid
-__device__ __forceinline__ long long next_from(const uint8_t* __restrict__ seg, long long len, long long p, bool* eof) {
+// "next record start" if a record header began at absolute position p; returns p for EOF / invalid.
+// `byte_at(q)` returns the segment byte at absolute offset q (global memory, or a shared-memory copy of the chunk).
+template <class ByteAt>
+__device__ __forceinline__ long long vint_at(ByteAt byte_at, long long p, int n) {
+    // n = total encoded size (2..9) of a multi-byte VInt whose first byte is at p
+    const int8_t b = (int8_t)byte_at(p);
+    const bool neg = b < -120;
+    unsigned long long t = 0;
+    for (int i = 1; i < n; ++i) t = (t << 8) | byte_at(p + i);
+    return neg ? (long long)~t : (long long)t;
+}
+template <class ByteAt>
+__device__ __forceinline__ long long next_from_rd(ByteAt byte_at, long long len, long long p, bool* eof) {
     *eof = false;
     if (p >= len) { *eof = true; return p; }
-    long long klen, vlen;
-    int8_t b0 = (int8_t)seg[p];
-    int n1 = vint_size_from_first(b0);
+    const int8_t b0 = (int8_t)byte_at(p);
+    const int n1 = vint_size_from_first(b0);
     if (p + n1 >= len) { *eof = true; return p; }
-    vint_decode(seg + p, &klen);
-    int8_t b1 = (int8_t)seg[p + n1];
-    int n2 = vint_size_from_first(b1);
+    const long long klen = n1 == 1 ? (long long)b0 : vint_at(byte_at, p, n1);
+    const int8_t b1 = (int8_t)byte_at(p + n1);
+    const int n2 = vint_size_from_first(b1);
     if (p + n1 + n2 > len) { *eof = true; return p; }
-    vint_decode(seg + p + n1, &vlen);
+    const long long vlen = n2 == 1 ? (long long)b1 : vint_at(byte_at, p + n1, n2);
     // EOF marker, or garbage on a speculative path (bounded so the sum below cannot overflow)
     if (klen < 0 || vlen < 0 || klen > len || vlen > len) { *eof = true; return p; }
-    long long nx = p + n1 + n2 + klen + vlen;
+    const long long nx = p + n1 + n2 + klen + vlen;
     if (nx > len) { *eof = true; return p; }
     return nx;
+}
+__device__ __forceinline__ long long next_from(const uint8_t* __restrict__ seg, long long len, long long p, bool* eof) {
+    return next_from_rd([seg](long long q) { return (unsigned)seg[q]; }, len, p, eof);
 }
 
 // Phase 1+2: per chunk, for every byte offset e in the chunk: exit[e] = where the chain started at e
@@ -79,28 +92,34 @@ __global__ void __launch_bounds__(DC_THREADS) decode_chunk_maps_kernel(const uin
                                                                       unsigned* __restrict__ cnt_map) {
     __shared__ unsigned nxt[DC_CHUNK];  // in-chunk target, or DC_EXIT|overshoot, or 0xFFFFFFFF for EOF
     __shared__ unsigned cnt[DC_CHUNK];
+    __shared__ __align__(16) uint8_t sb[DC_CHUNK + 32];  // the chunk + the longest header that can start in it (2 x 9 bytes)
     const long long base = (chunk0 + blockIdx.x) * DC_CHUNK;
     const long long wbase = (long long)blockIdx.x * DC_CHUNK;  // position inside the scratch window
+    for (int i = threadIdx.x; i < DC_CHUNK + 32; i += DC_THREADS) sb[i] = base + i < len ? seg[base + i] : (uint8_t)0;
+    __syncthreads();
+    auto byte_at = [&](long long q) { return (unsigned)sb[q - base]; };
     for (int e = threadIdx.x; e < DC_CHUNK; e += DC_THREADS) {
         long long p = base + e;
         bool eof;
-        long long nx = next_from(seg, len, p, &eof);
+        long long nx = next_from_rd(byte_at, len, p, &eof);
         if (eof) { nxt[e] = 0xFFFFFFFFu; cnt[e] = 0; }
         else if (nx - base >= DC_CHUNK) { nxt[e] = DC_EXIT | (unsigned)(nx - base - DC_CHUNK); cnt[e] = 1; }
         else { nxt[e] = (unsigned)(nx - base); cnt[e] = 1; }
     }
     __syncthreads();
-    // pointer doubling: a record is >= 2 bytes so at most DC_CHUNK/2 hops; log2 rounds
+    // pointer doubling: a record is >= 2 bytes so at most DC_CHUNK/2 hops = 12 rounds; stop as soon as every chain
+    // has left the chunk (records of ~100 bytes need 6 rounds)
     for (int round = 0; round < 12; ++round) {
         unsigned nn[DC_CHUNK / DC_THREADS], cc[DC_CHUNK / DC_THREADS];
+        bool all_out = true;
 #pragma unroll
         for (int i = 0; i < DC_CHUNK / DC_THREADS; ++i) {
             int e = threadIdx.x + i * DC_THREADS;
             unsigned t = nxt[e];
             if (t & DC_EXIT) { nn[i] = t; cc[i] = cnt[e]; }
-            else { nn[i] = nxt[t]; cc[i] = cnt[e] + cnt[t]; }
+            else { nn[i] = nxt[t]; cc[i] = cnt[e] + cnt[t]; all_out = false; }
         }
-        __syncthreads();
+        if (__syncthreads_and(all_out)) break;
 #pragma unroll
         for (int i = 0; i < DC_CHUNK / DC_THREADS; ++i) {
             int e = threadIdx.x + i * DC_THREADS;
@@ -114,32 +133,86 @@ __global__ void __launch_bounds__(DC_THREADS) decode_chunk_maps_kernel(const uin
     }
 }
 
-// Phase 3: thread the true entry offset through the chunks of one scratch window (serial over chunks,
-// one thread; the carry {entry offset, records so far, finished} lives in device memory so successive
-// windows chain without a host round trip).
+// Phase 3: thread the true entry offset through the chunks of one scratch window. The chain
+//     entry(c+1) = exit_map[c][entry(c)]
+// is serial in c, and one dependent load per 4 KiB chunk is what a first version paid (7.5 GB/s). It is done in two
+// levels instead: groups of DC_GROUP chunks get their own entry -> exit table, built speculatively for all 4096
+// possible entry offsets in parallel (chains that start at different offsets fall into step after a few records,
+// so the loads of a group's threads coalesce); one thread then hops from group to group, and one thread per group
+// fills in the per-chunk entries.
 // entry[c] = offset inside chunk c where the first record header of that chunk begins (0xFFFFFFFE: chunk
 // lies inside a long record, 0xFFFFFFFF: the chain ended earlier), first[c] = index of that record.
+constexpr int DC_GROUP = 64;
 struct DecodeCarry { unsigned long long entry; unsigned long long total; unsigned long long done; };
-__global__ void decode_thread_chunks_kernel(const unsigned* __restrict__ exit_map, const unsigned* __restrict__ cnt_map,
-                                            long long chunk0, long long nwin, unsigned* __restrict__ entry,
-                                            unsigned long long* __restrict__ first, DecodeCarry* __restrict__ carry,
-                                            unsigned long long* __restrict__ nrec_out) {
-    unsigned long long e = carry->entry, total = carry->total;
-    bool done = carry->done != 0;
-    for (long long w = 0; w < nwin; ++w) {
-        const long long c = chunk0 + w;
-        first[c] = total;
-        if (done) { entry[c] = 0xFFFFFFFFu; continue; }
-        // a record may span whole chunks: overshoot >= DC_CHUNK skips them
-        if (e >= (unsigned long long)DC_CHUNK) { entry[c] = 0xFFFFFFFEu; e -= DC_CHUNK; continue; }
-        entry[c] = (unsigned)e;
-        unsigned x = exit_map[w * DC_CHUNK + e];
+
+// walks chunks [w0, w1) of the window starting with overshoot/entry e; optionally records entry[]/first[]
+__device__ __forceinline__ void walk_chunks(const unsigned* __restrict__ exit_map, const unsigned* __restrict__ cnt_map, long long w0,
+                                            long long w1, long long chunk0, unsigned long long& e, unsigned long long& total, bool& done,
+                                            unsigned* __restrict__ entry, unsigned long long* __restrict__ first) {
+    for (long long w = w0; w < w1; ++w) {
+        if (first) first[chunk0 + w] = total;
+        if (done) { if (entry) entry[chunk0 + w] = 0xFFFFFFFFu; continue; }
+        if (e >= (unsigned long long)DC_CHUNK) { if (entry) entry[chunk0 + w] = 0xFFFFFFFEu; e -= DC_CHUNK; continue; }  // inside a long record
+        if (entry) entry[chunk0 + w] = (unsigned)e;
+        const unsigned x = exit_map[w * DC_CHUNK + e];
         total += cnt_map[w * DC_CHUNK + e];
         if (x == 0xFFFFFFFFu) done = true;
         else e = x & ~DC_EXIT;
     }
+}
+
+__global__ void __launch_bounds__(DC_THREADS) decode_group_maps_kernel(const unsigned* __restrict__ exit_map, const unsigned* __restrict__ cnt_map,
+                                                                      long long nwin, unsigned* __restrict__ gexit, unsigned* __restrict__ gcnt) {
+    const long long w0 = (long long)blockIdx.x * DC_GROUP;
+    const long long w1 = w0 + DC_GROUP < nwin ? w0 + DC_GROUP : nwin;
+    for (int e0 = threadIdx.x; e0 < DC_CHUNK; e0 += DC_THREADS) {
+        unsigned long long e = (unsigned long long)e0, total = 0;
+        bool done = false;
+        walk_chunks(exit_map, cnt_map, w0, w1, 0, e, total, done, nullptr, nullptr);
+        // a record longer than 2 GiB cannot be represented (nor fetched by the reference: int32 lengths)
+        gexit[(long long)blockIdx.x * DC_CHUNK + e0] = done ? 0xFFFFFFFFu : (unsigned)(e > 0x7FFFFFFFull ? 0x7FFFFFFFull : e);
+        gcnt[(long long)blockIdx.x * DC_CHUNK + e0] = (unsigned)total;
+    }
+}
+
+__global__ void decode_thread_groups_kernel(const unsigned* __restrict__ exit_map, const unsigned* __restrict__ cnt_map,
+                                            const unsigned* __restrict__ gexit, const unsigned* __restrict__ gcnt, long long nwin,
+                                            unsigned long long* __restrict__ gentry, unsigned long long* __restrict__ gfirst,
+                                            unsigned long long* __restrict__ gdone, DecodeCarry* __restrict__ carry,
+                                            unsigned long long* __restrict__ nrec_out) {
+    unsigned long long e = carry->entry, total = carry->total;
+    bool done = carry->done != 0;
+    const long long ng = (nwin + DC_GROUP - 1) / DC_GROUP;
+    for (long long g = 0; g < ng; ++g) {
+        gentry[g] = e; gfirst[g] = total; gdone[g] = done ? 1ull : 0ull;
+        if (done) continue;
+        const long long w0 = g * DC_GROUP, w1 = w0 + DC_GROUP < nwin ? w0 + DC_GROUP : nwin;
+        const unsigned long long span = (unsigned long long)(w1 - w0) * DC_CHUNK;
+        if (e >= span) { e -= span; continue; }                      // a long record covers the whole group
+        if (e >= (unsigned long long)DC_CHUNK) {                      // the chain enters in the middle of the group: walk it
+            walk_chunks(exit_map, cnt_map, w0, w1, 0, e, total, done, nullptr, nullptr);
+            continue;
+        }
+        const unsigned x = gexit[g * DC_CHUNK + e];
+        total += gcnt[g * DC_CHUNK + e];
+        if (x == 0xFFFFFFFFu) done = true;
+        else e = x;
+    }
     carry->entry = e; carry->total = total; carry->done = done ? 1ull : 0ull;
     *nrec_out = total;
+}
+
+__global__ void decode_fill_chunks_kernel(const unsigned* __restrict__ exit_map, const unsigned* __restrict__ cnt_map, long long chunk0,
+                                          long long nwin, const unsigned long long* __restrict__ gentry,
+                                          const unsigned long long* __restrict__ gfirst, const unsigned long long* __restrict__ gdone,
+                                          unsigned* __restrict__ entry, unsigned long long* __restrict__ first) {
+    const long long ng = (nwin + DC_GROUP - 1) / DC_GROUP;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < ng; g += (long long)gridDim.x * blockDim.x) {
+        unsigned long long e = gentry[g], total = gfirst[g];
+        bool done = gdone[g] != 0;
+        const long long w0 = g * DC_GROUP, w1 = w0 + DC_GROUP < nwin ? w0 + DC_GROUP : nwin;
+        walk_chunks(exit_map, cnt_map, w0, w1, chunk0, e, total, done, entry, first);
+    }
 }
 
 // Phase 4: every chunk walks its (short) true chain and writes the offsets.
@@ -232,8 +305,9 @@ extern "C" long long uda_ifile_decode_scratch_bytes(long long seg_len) {
     long long nchunks = (seg_len + uda::DC_CHUNK - 1) / uda::DC_CHUNK;
     if (nchunks < 1) nchunks = 1;
     long long win = nchunks < DC_WINDOW_CHUNKS ? nchunks : DC_WINDOW_CHUNKS;
-    // window maps (4+4 B per byte) + per-chunk entry (4 B) and first (8 B) + carry
-    return win * uda::DC_CHUNK * 8 + nchunks * 12 + 1024;
+    // window maps (4+4 B per byte) + per-chunk entry (4 B) and first (8 B) + per-group tables + carry
+    const long long ng = (win + uda::DC_GROUP - 1) / uda::DC_GROUP;
+    return win * uda::DC_CHUNK * 8 + nchunks * 12 + ng * (uda::DC_CHUNK * 8 + 24) + 1024;
 }
 
 // rec_off_out must hold (max_records + 1) entries; *nrec_dev receives the record count and
@@ -249,12 +323,21 @@ extern "C" int uda_ifile_decode_offsets(const void* seg, long long seg_len, long
     unsigned* exit_map = (unsigned*)s; s += win * DC_CHUNK * 4;
     unsigned* cnt_map = (unsigned*)s; s += win * DC_CHUNK * 4;
     unsigned long long* first = (unsigned long long*)s; s += nchunks * 8;
+    const long long ngw = (win + DC_GROUP - 1) / DC_GROUP;
+    unsigned long long* gentry = (unsigned long long*)s; s += ngw * 8;
+    unsigned long long* gfirst = (unsigned long long*)s; s += ngw * 8;
+    unsigned long long* gdone = (unsigned long long*)s; s += ngw * 8;
+    unsigned* gexit = (unsigned*)s; s += ngw * DC_CHUNK * 4;
+    unsigned* gcnt = (unsigned*)s; s += ngw * DC_CHUNK * 4;
     unsigned* entry = (unsigned*)s;
     UDA_CUDA(cudaMemsetAsync(carry, 0, sizeof(DecodeCarry), stream));
     for (long long c0 = 0; c0 < nchunks; c0 += win) {
         const long long nw = nchunks - c0 < win ? nchunks - c0 : win;
         decode_chunk_maps_kernel<<<(unsigned)nw, DC_THREADS, 0, stream>>>((const uint8_t*)seg, seg_len, c0, exit_map, cnt_map);
-        decode_thread_chunks_kernel<<<1, 1, 0, stream>>>(exit_map, cnt_map, c0, nw, entry, first, carry, nrec_dev);
+        const long long ng = (nw + DC_GROUP - 1) / DC_GROUP;
+        decode_group_maps_kernel<<<(unsigned)ng, DC_THREADS, 0, stream>>>(exit_map, cnt_map, nw, gexit, gcnt);
+        decode_thread_groups_kernel<<<1, 1, 0, stream>>>(exit_map, cnt_map, gexit, gcnt, nw, gentry, gfirst, gdone, carry, nrec_dev);
+        decode_fill_chunks_kernel<<<(unsigned)((ng + 127) / 128), 128, 0, stream>>>(exit_map, cnt_map, c0, nw, gentry, gfirst, gdone, entry, first);
     }
     long long b = (nchunks + 127) / 128;
     if (b > kNumSMs * 8) b = kNumSMs * 8;

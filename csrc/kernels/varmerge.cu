@@ -15,10 +15,10 @@
 //   2. exclusive scan of the flags = group id; start[] table per group
 //   3. every non-head position compares itself with its predecessor using the exact comparator; an inversion
 //      claims its group once (high bit of start[]) and appends it to a work list
-//   4. one CTA per listed group: stable rank sort (rank = number of group members that sort before the element)
-//      into a temporary, then copy back.
+//   4. one CTA per listed group: small groups by a stable rank sort (rank = number of group members that sort
+//      before the element) into a temporary, large ones by a bitonic network in place.
 // Groups of equal keys (Zipf heads) never enter the work list because (run, index) order is already right, so
-// the quadratic step 4 only sees groups of distinct keys sharing 10 bytes; the largest such group is reported.
+// step 4 only sees groups of distinct keys sharing 10 bytes; the largest such group is reported.
 #include "common.cuh"
 #include "scan.cuh"
 #include "../../include/uda_b200.h"
@@ -89,7 +89,8 @@ __global__ void tb_claim_kernel(const Entry* __restrict__ S, long long n, const 
     }
 }
 
-constexpr int TB_THREADS = 256;
+constexpr int TB_THREADS = 1024;
+constexpr int TB_RANK_MAX = 64;   // groups up to this size: rank sort; larger: bitonic network
 
 __global__ void __launch_bounds__(TB_THREADS) tb_sort_kernel(Entry* __restrict__ S, Entry* __restrict__ tmp,
                                                              const unsigned long long* __restrict__ run_base,
@@ -104,6 +105,28 @@ __global__ void __launch_bounds__(TB_THREADS) tb_sort_kernel(Entry* __restrict__
         if (threadIdx.x == 0) {
             atomicMax(&stats[1], (unsigned long long)size);
             atomicAdd(&stats[2], (unsigned long long)size);
+        }
+        if (size > TB_RANK_MAX) {
+            // bitonic network over the group in global memory (all comparisons ascending, indices >= size act as +inf):
+            // O(g log^2 g) exact compares instead of the O(g^2) of the rank sort. Equal keys are ordered by
+            // (run, index), which is the order a stable sort would keep.
+            Entry* G = S + s;
+            for (unsigned k = 2; (k >> 1) < (unsigned)size; k <<= 1) {
+                for (unsigned j = k >> 1; j > 0; j >>= 1) {
+                    const unsigned mask = (j == (k >> 1)) ? (k - 1) : j;   // first step of a merge flips, the rest shuffle
+                    for (unsigned i = threadIdx.x; i < (unsigned)size; i += TB_THREADS) {
+                        const unsigned l = i ^ mask;
+                        if (l > i && l < (unsigned)size) {
+                            const Entry a = G[i], b = G[l];
+                            int c = cmp_keys(key_of(b, run_base, run_recoff, key_kind), key_of(a, run_base, run_recoff, key_kind));
+                            if (c == 0) c = (b.w1 & 0xFFFFFFFFFFFFull) < (a.w1 & 0xFFFFFFFFFFFFull) ? -1 : 1;
+                            if (c < 0) { G[i] = b; G[l] = a; }
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
+            continue;
         }
         for (int i = threadIdx.x; i < size; i += TB_THREADS) {
             const Entry ei = S[s + i];
@@ -272,7 +295,7 @@ extern "C" int uda_tiebreak_var(void* sorted_entries, long long n, const unsigne
     if (scan4::exclusive_any(gidx, n, gidx, scan_scratch, stream)) return UDA_E_TOO_LARGE;
     tb_starts_kernel<<<blocks, 256, 0, stream>>>(gidx, n, start);
     tb_claim_kernel<<<blocks, 256, 0, stream>>>(S, n, gidx, run_base_dev, run_recoff_dev, key_kind, start, work, stats);
-    tb_sort_kernel<<<kNumSMs * 4, TB_THREADS, 0, stream>>>(S, (Entry*)tmp_entries, run_base_dev, run_recoff_dev, key_kind, start, work,
+    tb_sort_kernel<<<kNumSMs * 2, TB_THREADS, 0, stream>>>(S, (Entry*)tmp_entries, run_base_dev, run_recoff_dev, key_kind, start, work,
                                                           stats);
     UDA_CHECK_LAUNCH();
     return 0;

@@ -498,14 +498,17 @@ def test_var_merger_with_prefix_ties(K, kind, sizes):
         assert groups > 0 and largest > 1 and moved >= largest  # the tie-break really ran
 
 
-@pytest.mark.parametrize("kind,n,maps", [(2, 30_000, 3), (1, 20_000, 2)])
-def test_sort_job_single_gpu(built, kind, n, maps):
+@pytest.mark.parametrize("kind,n,maps,side", [(2, 30_000, 3, True), (1, 20_000, 2, False), (2, 200_000, 4, True),
+                                               (2, 30_000, 3, False)])   # the third one has tie groups of ~2500 keys
+def test_sort_job_single_gpu(built, kind, n, maps, side):
     from uda_b200.models.sortjob import SortJob
-    job = SortJob(n, maps, device=_dev(), key_kind=kind, key_len=(0, 60), val_len=(0, 150), tie_fraction=0.05).setup()
+    job = SortJob(n, maps, device=_dev(), key_kind=kind, key_len=(0, 60), val_len=(0, 150), tie_fraction=0.05, side_index=side).setup()
     job.step()
     out = job.step()
     res = job.check(out)
     assert res["ok"] and res["records"] == n and res["tiebreak_groups"] > 0, res
+    if n >= 200_000:
+        assert res["tiebreak_largest"] > 1000, res    # large groups go through the bitonic network
     # every map output is a valid MOF: CRC of every segment, sortedness inside every partition
     body = _cmp_body(kind)
     for mof in job.mofs:

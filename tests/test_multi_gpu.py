@@ -52,12 +52,12 @@ def test_side_table_broadcast(built, world):
     assert text.count('"ok": true') == world, text[-6000:]
 
 
-@pytest.mark.parametrize("world,kind", [(2, 2), (2, 1), (8, 2)])
-def test_sort_job_multi_rank(built, world, kind):
+@pytest.mark.parametrize("world,kind,side", [(2, 2, 1), (2, 1, 0), (8, 2, 1)])
+def test_sort_job_multi_rank(built, world, kind, side):
     """Variable-length records, BytesWritable (2) / Text (1) keys, 5 % of the keys tie on the sort prefix."""
     if _ngpu() < world:
         pytest.skip(f"needs {world} GPUs")
-    p = _torchrun(world, "mp_sort.py", 40_000, kind)
+    p = _torchrun(world, "mp_sort.py", 40_000, kind, side)
     text = p.stdout + "\n" + p.stderr
     assert p.returncode == 0, text[-6000:]
     assert text.count("MPRESULT") == world and text.count('"ok": true') == world, text[-6000:]

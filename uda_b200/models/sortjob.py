@@ -31,10 +31,12 @@ from ..utils import ifile
 
 
 def generate_segment(n: int, seed: int, device, key_kind: int = KEY_BYTES_WRITABLE, key_len: Tuple[int, int] = (10, 100),
-                     val_len: Tuple[int, int] = (0, 200), tie_fraction: float = 0.0, tie_pool: int = 4) -> Tuple[torch.Tensor, int]:
+                     val_len: Tuple[int, int] = (0, 200), tie_fraction: float = 0.0, tie_pool: int = 4,
+                     pool_seed: Optional[int] = None) -> Tuple[torch.Tensor, int]:
     """One unsorted IFile segment of ``n`` random records, built on the device (RandomWriter's shape: random
     key/value sizes in a range, random bytes). ``tie_fraction`` of the keys start with one of ``tie_pool`` fixed
-    10-byte strings, so that they tie on the sort prefix and only the exact comparator can order them.
+    10-byte strings (drawn from ``pool_seed``, so that all maps of a job share them), so that they tie on the sort
+    prefix across maps and only the exact comparator can order them.
     Returns ``(segment incl. EOF marker, its length)``."""
     g = torch.Generator(device=device)
     g.manual_seed(seed)
@@ -61,7 +63,9 @@ def generate_segment(n: int, seed: int, device, key_kind: int = KEY_BYTES_WRITAB
     else:
         keys[ko] = klen.to(torch.uint8)
     if tie_fraction > 0 and n:
-        pool = torch.randint(0, 256, (tie_pool, 10), generator=g, device=device, dtype=torch.uint8)
+        gp = torch.Generator(device=device)
+        gp.manual_seed(seed if pool_seed is None else pool_seed)
+        pool = torch.randint(0, 256, (tie_pool, 10), generator=gp, device=device, dtype=torch.uint8)
         sel = torch.rand(n, generator=g, device=device) < tie_fraction
         pid = torch.randint(0, tie_pool, (n,), generator=g, device=device)
         for j in range(10):
@@ -83,7 +87,7 @@ def _sort_key(key_kind: int):
 class SortJob:
     def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 99,
                  key_kind: int = KEY_BYTES_WRITABLE, key_len: Tuple[int, int] = (10, 100), val_len: Tuple[int, int] = (0, 200),
-                 tie_fraction: float = 0.0, group=None, push_ctas: int = 0):
+                 tie_fraction: float = 0.0, group=None, push_ctas: int = 0, side_index: bool = True):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -91,6 +95,9 @@ class SortJob:
         self.n_local, self.maps, self.seed = records_per_rank, maps_per_rank, seed
         self.key_kind, self.key_len, self.val_len, self.tie_fraction = key_kind, key_len, val_len, tie_fraction
         self.push_ctas = push_ctas
+        #: ship the maps' record-offset side index with the segments (8 bytes per record) so that the reducer does not
+        #: rediscover record boundaries; False = segments only, as a MOF written by Hadoop would arrive
+        self.side_index = side_index
         self.mofs: List[DeviceMOF] = []
         self.steps_run = 0
 
@@ -103,7 +110,7 @@ class SortJob:
         self.input_bytes = 0
         for m, nm in enumerate(per_map):
             seg, seg_len = generate_segment(nm, self.seed + 1000 * self.rank + m, dev, self.key_kind, self.key_len, self.val_len,
-                                            self.tie_fraction)
+                                            self.tie_fraction, pool_seed=self.seed)
             self.input_bytes += seg_len - 2
             self.mofs.append(task.run(seg, seg_len, nm, splitters))
             del seg
@@ -141,6 +148,36 @@ class SortJob:
         self.bytes_out = int(sum(r - 2 for _, r, _ in self.segments)) + 2
         self.expect_step = torch.from_numpy(lay.run_bytes.astype(np.int64)).to(dev)
         self.expect = torch.zeros_like(self.expect_step)
+        self.rec_offs = None
+        if self.side_index:
+            # second, small shuffle of the side indexes: own plan (sizes follow from the record counts every rank
+            # already holds), own arena, same push kernel
+            sidx = np.zeros_like(index)
+            for s in range(P):
+                for m in range(self.maps):
+                    cur = 0
+                    for p in range(P):
+                        nb = (int(nrec[s, m, p]) + 1) * 8
+                        sidx[s, m, p] = (cur, nb, nb)
+                        cur = (cur + nb + 15) // 16 * 16
+            self.side_plan = ShufflePlan(sidx, record_stride=0)
+            self.side_arena = SymmetricArena(self.side_plan.max_arena_bytes(), nruns, dev, self.group)
+            self.side_descs_dev = K.to_device_struct(
+                self.side_plan.push_descs(self.rank, [m.meta["side"].data_ptr() for m in self.mofs],
+                                          [self.side_arena.peer_data_ptr(p) for p in range(P)],
+                                          [self.side_arena.peer_flag_ptr(p, 0) for p in range(P)], 0), dev)
+            self.side_scratch = torch.empty(K.push_scratch_bytes(self.nseg), dtype=torch.uint8, device=dev)
+            slay = self.side_plan.layout(self.rank)
+            sdata = self.side_arena.data()
+            self.rec_offs = []
+            for s in range(P):
+                for m in range(self.maps):
+                    rid = self.side_plan.run_id(s, m)
+                    o, nb = int(slay.run_offsets[rid]), (int(nrec[s, m, self.rank]) + 1) * 8
+                    assert o % 8 == 0
+                    self.rec_offs.append(sdata[o:o + nb].view(torch.int64))
+            self.side_expect_step = torch.from_numpy(slay.run_bytes.astype(np.int64)).to(dev)
+            self.side_expect = torch.zeros_like(self.side_expect_step)
         self.merger = VarMerger(dev, self.key_kind, self.n_out, nruns, self.bytes_out)
         torch.cuda.synchronize(dev)
         if P > 1:
@@ -154,13 +191,19 @@ class SortJob:
             self.arena.barrier()
         self.expect.add_(self.expect_step)
         K.shuffle_push(self.push_descs_dev, self.nseg, self.push_scratch, self.push_ctas)
+        if self.side_index:
+            if self.world > 1:
+                self.side_arena.barrier()
+            self.side_expect.add_(self.side_expect_step)
+            K.shuffle_push(self.side_descs_dev, self.nseg, self.side_scratch, self.push_ctas)
+            K.wait_flags(self.side_arena.flags()[: self.plan.nruns], self.side_expect, self.plan.nruns, self.side_arena.status)
         K.wait_flags(self.arena.flags()[: self.plan.nruns], self.expect, self.plan.nruns, self.arena.status)
-        out, _ = self.merger.merge(self.segments, exact_counts=True)
+        out, _ = self.merger.merge(self.segments, exact_counts=True, rec_offs=self.rec_offs)
         return out
 
     @property
     def launches_per_step(self) -> int:
-        return 2 + 1 + VarMerger.launches(len(self.segments)) + (1 if self.world > 1 else 0)
+        return (2 + 1) * (2 if self.side_index else 1) + VarMerger.launches(len(self.segments), self.side_index) + (2 if self.world > 1 else 0)
 
     # ------------------------------------------------------------------------------------ check
     def check(self, out: torch.Tensor) -> dict:
@@ -191,3 +234,5 @@ class SortJob:
 
     def close(self) -> None:
         self.arena.close()
+        if self.side_index and hasattr(self, "side_arena"):
+            self.side_arena.close()

@@ -70,17 +70,25 @@ class VarMerger:
         self.n = 0
         self._keep: List[torch.Tensor] = []
 
-    def merge(self, segments: Sequence[Tuple[torch.Tensor, int, int]], exact_counts: bool = True) -> Tuple[torch.Tensor, int]:
+    def merge(self, segments: Sequence[Tuple[torch.Tensor, int, int]], exact_counts: bool = True,
+              rec_offs: Optional[Sequence[torch.Tensor]] = None) -> Tuple[torch.Tensor, int]:
         """``segments[r] = (uint8 device tensor starting at the segment, seg_len incl. the EOF marker, records)``.
         ``records`` is the exact count (``exact_counts``) or an upper bound (one host sync to learn the counts).
+        ``rec_offs[r]`` (int64, records + 1 entries) is the record-offset side index of segment r when the map side
+        shipped one; without it the boundaries are rediscovered from the bytes (K5).
         Returns ``(merged stream incl. EOF marker, its length in bytes)``."""
         k, dev = len(segments), self.device
         assert k <= self.max_runs
-        rec_offs, nrec_dev = [], []
-        for seg, seg_len, cap in segments:
-            ro, nr = K.ifile_decode_offsets(seg, seg_len, cap)
-            rec_offs.append(ro)
-            nrec_dev.append(nr)
+        nrec_dev = []
+        if rec_offs is None:
+            rec_offs = []
+            for seg, seg_len, cap in segments:
+                ro, nr = K.ifile_decode_offsets(seg, seg_len, cap)
+                rec_offs.append(ro)
+                nrec_dev.append(nr)
+        else:
+            assert exact_counts and len(rec_offs) == k, "a side index implies exact record counts"
+            rec_offs = list(rec_offs)
         if exact_counts:
             counts = [int(c) for _, _, c in segments]
         else:
@@ -113,10 +121,11 @@ class VarMerger:
     def tiebreak_stats(self) -> Tuple[int, int, int]:
         return K.tiebreak_stats(self.tb_scratch, self.n)
 
-    #: kernels per merge of k runs: k x (decode 6 + extract 1) + merge 9 + tie-break 7 + lengths 1 + scan 3 + gather 1 + eof 1
+    #: kernels per merge of k runs: k x (decode 5 [absent with a side index] + extract 1) + merge 9 + tie-break 7 +
+    #: lengths 1 + scan 3 + gather 1 + eof 1
     @staticmethod
-    def launches(k: int) -> int:
-        return 7 * k + 22
+    def launches(k: int, side_index: bool = False) -> int:
+        return (1 if side_index else 6) * k + 22
 
 
 class VarMapTask:
@@ -159,15 +168,25 @@ class VarMapTask:
             cur = (cur + body + SEG_TRAILER + 15) // 16 * 16
         buf = torch.empty(K.GATHER_SLACK + cur + K.GATHER_SLACK + 16, dtype=torch.uint8, device=dev)
         data = buf[K.GATHER_SLACK:]
+        # record-offset side index: per partition the n_p + 1 offsets of its records relative to the segment start
+        # (the last one is the EOF marker), int64, partitions 16-byte aligned. A reducer that receives it next to
+        # the segment does not have to rediscover the record boundaries (K5).
+        side_index = np.zeros((P, 3), dtype=np.int64)
+        scur = 0
+        for p in range(P):
+            nb = (int(nrec[p]) + 1) * 8
+            side_index[p] = (scur, nb, nb)
+            scur = (scur + nb + 15) // 16 * 16
+        side = torch.zeros(scur + 16, dtype=torch.uint8, device=dev)
         for p in range(P):
             b0, b1 = int(bounds[p]), int(bounds[p + 1])
             out = data[int(index[p, 0]):]
+            rel = (off64[b0:b1 + 1] - off64[b0]).contiguous()
             if b1 > b0:
-                # offsets of this partition's records relative to its segment start
-                rel = (off64[b0:b1 + 1] - off64[b0]).contiguous()
                 K.gather_var(ent[b0:b1], b1 - b0, run_base, run_recoff, rel, out)
+            side[int(side_index[p, 0]):int(side_index[p, 0]) + (b1 - b0 + 1) * 8].view(torch.int64).copy_(rel)
             raw = int(index[p, 1])
             K.write_eof_at(out[raw - 2:], None)
             K.crc32(out, raw, out_be4=out[raw:raw + 4])
         torch.cuda.current_stream(dev).synchronize()                      # the temporaries above die with this frame
-        return DeviceMOF(data, index, nrec, meta={"sorted": True, "key_kind": self.key_kind})
+        return DeviceMOF(data, index, nrec, meta={"sorted": True, "key_kind": self.key_kind, "side": side, "side_index": side_index})
