@@ -337,7 +337,8 @@ class TeraSortJob:
     #: kernel launches of this library inside one step (barrier, then per sub-partition: plan, push, wait, merge chain)
     @property
     def launches_per_step(self) -> int:
-        return (1 if self.world > 1 else 0) + self.subparts * (2 + 1 + DeviceMerger.LAUNCHES_PER_MERGE)
+        push = 2 if self.push_mode == "tma" else 2 * self.subparts     # plan + push: one pair for all sub-partitions with tma
+        return (1 if self.world > 1 else 0) + push + self.subparts * (1 + DeviceMerger.LAUNCHES_PER_MERGE)
 
     # ------------------------------------------------------------------------------------ check
     def check(self, out: Optional[torch.Tensor] = None) -> dict:
