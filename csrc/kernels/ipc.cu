@@ -52,6 +52,37 @@ extern "C" int uda_host_free_pinned(void* ptr) {
     return 0;
 }
 
+// Plain runtime services for hosts that drive the kernels through this C ABI without linking a CUDA runtime of their
+// own (the C++ consumer of libuda.so dlopens this library for its device merge).
+extern "C" int uda_device_count(int* out) {
+    cudaError_t e = cudaGetDeviceCount(out);
+    if (e != cudaSuccess) { *out = 0; cudaGetLastError(); return (int)e; }
+    return 0;
+}
+extern "C" int uda_set_device(int dev) {
+    UDA_CUDA(cudaSetDevice(dev));
+    return 0;
+}
+extern "C" int uda_mem_info(long long* free_bytes, long long* total_bytes) {
+    size_t f = 0, t = 0;
+    UDA_CUDA(cudaMemGetInfo(&f, &t));
+    *free_bytes = (long long)f;
+    *total_bytes = (long long)t;
+    return 0;
+}
+extern "C" int uda_memcpy_h2d_async(void* dst_dev, const void* src_host, long long bytes, cudaStream_t stream) {
+    UDA_CUDA(cudaMemcpyAsync(dst_dev, src_host, (size_t)bytes, cudaMemcpyHostToDevice, stream));
+    return 0;
+}
+extern "C" int uda_memcpy_d2h_async(void* dst_host, const void* src_dev, long long bytes, cudaStream_t stream) {
+    UDA_CUDA(cudaMemcpyAsync(dst_host, src_dev, (size_t)bytes, cudaMemcpyDeviceToHost, stream));
+    return 0;
+}
+extern "C" int uda_stream_synchronize(cudaStream_t stream) {
+    UDA_CUDA(cudaStreamSynchronize(stream));
+    return 0;
+}
+
 // Human-readable text for a return code of this library (negative: UDA_E_*, positive: cudaError_t).
 extern "C" const char* uda_error_string(int rc) {
     if (rc == 0) return "success";

@@ -1,5 +1,6 @@
 #include "consumer.h"
 #include "threads.h"
+#include "device_merge.h"
 
 #include <dlfcn.h>
 #include <unistd.h>
@@ -594,6 +595,7 @@ void Consumer::on_init(const HadoopCmd& cmd) {
         int per = (init_.num_maps + lpqs - 1) / lpqs;
         if (init_.num_maps >= lpqs && lpqs > 1) num_kv_bufs = std::min(init_.num_maps, per * parallel);
     }
+    if (opt_.merge_approach == 3) num_kv_bufs = std::min(init_.num_maps, 4);   // the device merge drains 4 sources at a time
     if (num_kv_bufs < 1) num_kv_bufs = 1;
     double ratio = atof(conf_get(host_, "mapred.rdma.compression.buffer.ratio", "0.20").c_str());
     long long cfg_kb = atoll(conf_get(host_, "mapred.rdma.buf.size", "1024").c_str());
@@ -619,7 +621,8 @@ void Consumer::merge_thread_main() {
         switch (opt_.merge_approach) {
             case 1: merge_online(); break;
             case 2: merge_hybrid(); break;
-            default: throw UdaError("unsupported merge approach (only 1=online and 2=hybrid exist)");
+            case 3: merge_device(); break;
+            default: throw UdaError("unsupported merge approach (1=online, 2=hybrid, 3=device exist)");
         }
         UDA_LOG(lsINFO, "merge thread exit");
     } catch (const UdaError& e) {
@@ -718,6 +721,80 @@ void Consumer::merge_online() {
     merging_phase(&heap, [this](const uint8_t* b, size_t n) {
         if (host_ && host_->data_from_uda) host_->data_from_uda(host_->user, b, (int)n);
     }, true);
+}
+
+namespace {
+// a fetched segment served again as a ByteSource (CPU fallback of the device merge)
+class MemorySource : public ByteSource {
+public:
+    MemorySource(const uint8_t* p, size_t n) : p_(p), n_(n) {}
+    bool next_block(const uint8_t** data, size_t* len) override {
+        if (done_) return false;
+        done_ = true;
+        *data = p_;
+        *len = n_;
+        return n_ > 0;
+    }
+private:
+    const uint8_t* p_;
+    size_t n_;
+    bool done_ = false;
+};
+}  // namespace
+
+void Consumer::merge_device() {
+    const int n = init_.num_maps;
+    std::vector<HostSegment> segs;
+    segs.reserve((size_t)n);
+    int progress = 0;
+    ShuffleRng rng(12345u);
+    while ((int)segs.size() < n) {
+        std::vector<FetchOrder> batch;
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            cv_.wait(lk, [&] { return stop_ || !fetch_list_.empty(); });
+            if (stop_) throw UdaError("stopped while fetching");
+            while (!fetch_list_.empty() && (int)(segs.size() + batch.size()) < n) {
+                batch.push_back(fetch_list_.front());
+                fetch_list_.pop_front();
+            }
+        }
+        batch = shuffle_interleave_hosts(std::move(batch), rng, [](const FetchOrder& o) { return o.host; });
+        // at most `parallel` sources hold buffer pairs at a time; each one is drained into host memory
+        const size_t parallel = 4;
+        for (size_t b0 = 0; b0 < batch.size(); b0 += parallel) {
+            std::vector<std::unique_ptr<ByteSource>> started;
+            for (size_t i = b0; i < std::min(batch.size(), b0 + parallel); ++i) started.push_back(make_source(batch[i]));
+            for (auto& src : started) {
+                if (stop_) throw UdaError("stopped while fetching");
+                HostSegment hs;
+                const uint8_t* d;
+                size_t len;
+                while (src->next_block(&d, &len)) hs.bytes.insert(hs.bytes.end(), d, d + len);
+                index_segment(&hs);
+                segs.push_back(std::move(hs));
+                ++progress;
+                if ((progress % kProgressEvery == 0 || progress == n) && host_ && host_->fetch_over_message)
+                    host_->fetch_over_message(host_->user);
+            }
+        }
+    }
+    auto deliver = [this](const uint8_t* b, size_t len) {
+        if (host_ && host_->data_from_uda) host_->data_from_uda(host_->user, b, (int)len);
+    };
+    long long records = 0;
+    std::string why;
+    if (DeviceMerge::instance().merge(segs, key_kind_, kStagingBytes, deliver, &records, &why)) {
+        emitted_ += (uint64_t)records;
+        device_merges_++;
+        UDA_LOG(lsINFO, "device merge of %d segments, %lld records done", n, records);
+        return;
+    }
+    UDA_LOG(lsWARN, "device merge not possible (%s): merging on the CPU", why.c_str());
+    MergeHeap heap(key_kind_);
+    for (auto& hs : segs)
+        heap.insert(std::make_unique<Segment>(std::make_unique<MemorySource>(hs.bytes.data(), (size_t)hs.raw_len()), segment_seq_++));
+    merging_phase(&heap, deliver, true);
 }
 
 void Consumer::merge_hybrid() {

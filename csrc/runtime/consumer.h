@@ -211,6 +211,7 @@ public:
     // statistics for tests
     uint64_t records_emitted() const { return emitted_.load(); }
     int lpqs_spilled() const { return spilled_.load(); }
+    int device_merges() const { return device_merges_.load(); }
 
 private:
     struct FetchOrder { std::string host, job, map; int reduce; };
@@ -218,6 +219,7 @@ private:
     void merge_thread_main();
     void merge_online();
     void merge_hybrid();
+    void merge_device();   // approach 3: fetch to host memory, merge on the GPU (device_merge.h), CPU heap merge as fallback
     // fetch `count` map outputs into `heap`; reports progress every kProgressEvery segments
     void fetching_phase(MergeHeap* heap, int count, int* progress);
     void merging_phase(MergeHeap* heap, const std::function<void(const uint8_t*, size_t)>& sink, bool final_stream);
@@ -240,6 +242,7 @@ private:
     std::vector<uint8_t> staging_[2];
     std::atomic<uint64_t> emitted_{0};
     std::atomic<int> spilled_{0};
+    std::atomic<int> device_merges_{0};
     int segment_seq_ = 0;
 };
 

@@ -1,0 +1,224 @@
+#include "device_merge.h"
+
+#include <dlfcn.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "uda_rt.h"
+#include "vint.h"
+
+namespace uda {
+
+void index_segment(HostSegment* seg) {
+    const uint8_t* p = seg->bytes.data();
+    const uint8_t* end = p + seg->bytes.size();
+    const uint8_t* base = p;
+    seg->rec_off.clear();
+    for (;;) {
+        int64_t kl = 0, vl = 0;
+        const int n1 = vint_decode(p, end, &kl);
+        const int n2 = n1 ? vint_decode(p + n1, end, &vl) : 0;
+        if (!n1 || !n2) throw UdaError("segment ended without EOF marker");
+        seg->rec_off.push_back((long long)(p - base));
+        if (kl == -1 && vl == -1) return;   // the entry just pushed is the EOF marker position
+        if (kl < 0 || vl < 0 || p + n1 + n2 + kl + vl > end) throw UdaError("corrupt record header in a fetched segment");
+        p += n1 + n2 + kl + vl;
+    }
+}
+
+// ---- the C ABI of libuda_kernels.so, resolved at run time (include/uda_b200.h) ----------------------------------
+struct DeviceMerge::Api {
+    int (*device_count)(int*);
+    int (*mem_info)(long long*, long long*);
+    int (*dev_malloc)(void**, long long);
+    int (*dev_free)(void*);
+    int (*h2d)(void*, const void*, long long, void*);
+    int (*d2h)(void*, const void*, long long, void*);
+    int (*sync)(void*);
+    int (*memset_async)(void*, int, long long, void*);
+    int (*extract_keys_var)(const void*, const long long*, long long, int, unsigned, unsigned, void*, unsigned*, void*);
+    long long (*merge_scratch_bytes)(long long, int);
+    int (*kway_merge_entries)(const void*, const long long*, int, long long, void*, void*, void*);
+    long long (*tiebreak_scratch_bytes)(long long);
+    int (*tiebreak_var)(void*, long long, const unsigned long long*, const unsigned long long*, int, void*, void*, void*);
+    int (*gather_var_lengths)(const void*, long long, const unsigned long long*, unsigned*, void*);
+    long long (*scan64_scratch_bytes)(long long);
+    int (*scan64)(const unsigned*, long long, unsigned long long*, void*, void*);
+    int (*gather_var)(const void*, long long, const unsigned long long*, const unsigned long long*, const unsigned long long*, void*, void*);
+    int (*write_eof_at)(void*, const unsigned long long*, void*);
+    const char* (*error_string)(int);
+};
+
+namespace {
+std::string dir_of_this_library() {
+    Dl_info info;
+    if (dladdr((void*)&index_segment, &info) && info.dli_fname) {
+        std::string p = info.dli_fname;
+        size_t s = p.rfind('/');
+        if (s != std::string::npos) return p.substr(0, s);
+    }
+    return ".";
+}
+}  // namespace
+
+DeviceMerge& DeviceMerge::instance() {
+    static DeviceMerge d;
+    return d;
+}
+
+DeviceMerge::DeviceMerge() {
+    const char* env = getenv("UDA_KERNELS_LIB");
+    const std::string path = env && *env ? std::string(env) : dir_of_this_library() + "/libuda_kernels.so";
+    lib_ = dlopen(path.c_str(), RTLD_NOW | RTLD_LOCAL);
+    if (!lib_) { why_ = std::string("cannot load ") + path + ": " + (dlerror() ? dlerror() : "?"); return; }
+    api_ = new Api();
+    bool all = true;
+    auto sym = [&](const char* n) { void* s = dlsym(lib_, n); if (!s) { all = false; why_ = std::string("missing symbol ") + n; } return s; };
+#define UDA_SYM(field, name) api_->field = reinterpret_cast<decltype(api_->field)>(sym(name))
+    UDA_SYM(device_count, "uda_device_count");
+    UDA_SYM(mem_info, "uda_mem_info");
+    UDA_SYM(dev_malloc, "uda_dev_malloc");
+    UDA_SYM(dev_free, "uda_dev_free");
+    UDA_SYM(h2d, "uda_memcpy_h2d_async");
+    UDA_SYM(d2h, "uda_memcpy_d2h_async");
+    UDA_SYM(sync, "uda_stream_synchronize");
+    UDA_SYM(memset_async, "uda_memset_async");
+    UDA_SYM(extract_keys_var, "uda_extract_keys_var");
+    UDA_SYM(merge_scratch_bytes, "uda_merge_scratch_bytes");
+    UDA_SYM(kway_merge_entries, "uda_kway_merge_entries");
+    UDA_SYM(tiebreak_scratch_bytes, "uda_tiebreak_scratch_bytes");
+    UDA_SYM(tiebreak_var, "uda_tiebreak_var");
+    UDA_SYM(gather_var_lengths, "uda_gather_var_lengths");
+    UDA_SYM(scan64_scratch_bytes, "uda_scan_u32_to_u64_scratch_bytes");
+    UDA_SYM(scan64, "uda_scan_u32_to_u64");
+    UDA_SYM(gather_var, "uda_gather_var");
+    UDA_SYM(write_eof_at, "uda_write_eof_at");
+    UDA_SYM(error_string, "uda_error_string");
+#undef UDA_SYM
+    if (!all) return;
+    int n = 0;
+    if (api_->device_count(&n) != 0 || n < 1) { why_ = "no CUDA device visible"; return; }
+    ok_ = true;
+    UDA_LOG(lsINFO, "device merge back-end ready: %s, %d device(s)", path.c_str(), n);
+}
+
+namespace {
+// every device allocation of one merge, released together
+struct DeviceArena {
+    DeviceMerge* owner;
+    int (*free_fn)(void*);
+    std::vector<void*> ptrs;
+    ~DeviceArena() { for (void* p : ptrs) if (p) free_fn(p); }
+};
+inline long long align_up(long long x, long long a) { return (x + a - 1) / a * a; }
+}  // namespace
+
+bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size_t max_block,
+                        const std::function<void(const uint8_t*, size_t)>& sink, long long* records_out, std::string* why) {
+    if (!ok_) { if (why) *why = why_; return false; }
+    const Api& a = *api_;
+    const int k = (int)segs.size();
+    long long n = 0, data_bytes = 64, out_bytes = 2;
+    std::vector<long long> run_off(k + 1, 0), seg_pos(k, 0), ro_pos(k, 0);
+    long long ro_bytes = 0;
+    for (int r = 0; r < k; ++r) {
+        run_off[r] = n;
+        n += segs[r].records();
+        seg_pos[r] = data_bytes;
+        data_bytes = align_up(data_bytes + segs[r].raw_len() + 32, 16);
+        ro_pos[r] = ro_bytes;
+        ro_bytes += (long long)segs[r].rec_off.size() * 8;
+        out_bytes += segs[r].raw_len() - 2;
+    }
+    run_off[k] = n;
+    if (records_out) *records_out = n;
+    if (k == 0 || n == 0) {
+        const uint8_t eof[2] = {0xFF, 0xFF};
+        sink(eof, 2);
+        return true;
+    }
+    if (k > 0xFFFF || n >= (1LL << 31) - 1) { if (why) *why = "partition too large for the device entry format"; return false; }
+    const long long nn = std::max<long long>(n, 1);
+    const long long merge_scratch = a.merge_scratch_bytes(nn, k), tb_scratch = a.tiebreak_scratch_bytes(nn), scan_scratch = a.scan64_scratch_bytes(nn);
+    if (merge_scratch < 0 || tb_scratch < 0 || scan_scratch < 0) { if (why) *why = "scratch size query failed"; return false; }
+    const long long need = data_bytes + ro_bytes + 2 * nn * 16 + merge_scratch + tb_scratch + scan_scratch + nn * 4 + (nn + 1) * 8 + out_bytes + 64 +
+                           (long long)k * 24 + 4096;
+    long long free_b = 0, total_b = 0;
+    if (a.mem_info(&free_b, &total_b) != 0 || need > (long long)(0.9 * (double)free_b)) {
+        if (why) *why = "partition needs " + std::to_string(need >> 20) + " MiB of device memory, " + std::to_string(free_b >> 20) + " MiB free";
+        return false;
+    }
+    DeviceArena arena{this, a.dev_free, {}};
+    auto dmalloc = [&](long long bytes) -> uint8_t* {
+        void* p = nullptr;
+        int rc = a.dev_malloc(&p, std::max<long long>(bytes, 16));
+        if (rc != 0 || !p) throw UdaError(std::string("device allocation failed: ") + a.error_string(rc));
+        arena.ptrs.push_back(p);
+        return (uint8_t*)p;
+    };
+    auto ck = [&](int rc, const char* what) { if (rc != 0) throw UdaError(std::string(what) + ": " + a.error_string(rc)); };
+    void* const stream = nullptr;   // the legacy default stream: this back-end runs one merge at a time
+
+    uint8_t* d_data = dmalloc(data_bytes + 64);
+    uint8_t* d_ro = dmalloc(ro_bytes + 16);
+    uint8_t* d_ent = dmalloc(nn * 16);
+    uint8_t* d_sorted = dmalloc(nn * 16);
+    uint8_t* d_mscr = dmalloc(merge_scratch);
+    uint8_t* d_tscr = dmalloc(tb_scratch);
+    uint8_t* d_sscr = dmalloc(scan_scratch);
+    uint8_t* d_len = dmalloc(nn * 4);
+    uint8_t* d_off = dmalloc((nn + 1) * 8);
+    uint8_t* d_out = dmalloc(out_bytes + 64);
+    uint8_t* d_tab = dmalloc((long long)k * 16 + (long long)(k + 1) * 8 + 16);   // run_base | run_recoff | run_off | flag
+    unsigned long long* d_run_base = (unsigned long long*)d_tab;
+    unsigned long long* d_run_recoff = d_run_base + k;
+    long long* d_run_off = (long long*)(d_run_recoff + k);
+    unsigned* d_flag = (unsigned*)(d_run_off + k + 1);
+
+    std::vector<unsigned long long> h_base(k), h_recoff(k);
+    for (int r = 0; r < k; ++r) {
+        ck(a.h2d(d_data + seg_pos[r], segs[r].bytes.data(), segs[r].raw_len(), stream), "copy of a segment to the device");
+        ck(a.h2d(d_ro + ro_pos[r], segs[r].rec_off.data(), (long long)segs[r].rec_off.size() * 8, stream), "copy of a record-offset table");
+        h_base[r] = (unsigned long long)(uintptr_t)(d_data + seg_pos[r]);
+        h_recoff[r] = (unsigned long long)(uintptr_t)(d_ro + ro_pos[r]);
+    }
+    ck(a.h2d(d_run_base, h_base.data(), (long long)k * 8, stream), "table upload");
+    ck(a.h2d(d_run_recoff, h_recoff.data(), (long long)k * 8, stream), "table upload");
+    ck(a.h2d(d_run_off, run_off.data(), (long long)(k + 1) * 8, stream), "table upload");
+    ck(a.memset_async(d_flag, 0, 4, stream), "memset");
+    const int kk = (int)kind;
+    for (int r = 0; r < k; ++r)
+        if (segs[r].records())
+            ck(a.extract_keys_var(d_data + seg_pos[r], (const long long*)(d_ro + ro_pos[r]), segs[r].records(), kk, (unsigned)r, 0u,
+                                  d_ent + run_off[r] * 16, d_flag, stream), "uda_extract_keys_var");
+    ck(a.kway_merge_entries(d_ent, d_run_off, k, n, d_sorted, d_mscr, stream), "uda_kway_merge_entries");
+    ck(a.tiebreak_var(d_sorted, n, d_run_base, d_run_recoff, kk, d_ent, d_tscr, stream), "uda_tiebreak_var");
+    ck(a.gather_var_lengths(d_sorted, n, d_run_recoff, (unsigned*)d_len, stream), "uda_gather_var_lengths");
+    ck(a.scan64((const unsigned*)d_len, n, (unsigned long long*)d_off, d_sscr, stream), "uda_scan_u32_to_u64");
+    ck(a.gather_var(d_sorted, n, d_run_base, d_run_recoff, (const unsigned long long*)d_off, d_out, stream), "uda_gather_var");
+    ck(a.write_eof_at(d_out, (const unsigned long long*)d_off + n, stream), "uda_write_eof_at");
+
+    std::vector<uint8_t> out((size_t)out_bytes);
+    std::vector<unsigned long long> off((size_t)n + 1);
+    ck(a.d2h(out.data(), d_out, out_bytes, stream), "copy of the merged stream to the host");
+    ck(a.d2h(off.data(), d_off, (n + 1) * 8, stream), "copy of the stream offsets to the host");
+    ck(a.sync(stream), "stream synchronize");
+    if ((long long)off[n] + 2 != out_bytes) throw UdaError("device merge produced a stream of unexpected length");
+
+    // deliver blocks of whole records; the EOF marker rides with the last block (or alone when it does not fit)
+    size_t i = 0;
+    while (i < (size_t)n) {
+        size_t j = i + 1;
+        while (j < (size_t)n && off[j + 1] - off[i] <= max_block) ++j;
+        size_t len = (size_t)(off[j] - off[i]);
+        const bool last = j == (size_t)n;
+        if (last && len + 2 <= max_block) len += 2;
+        sink(out.data() + off[i], len);
+        if (last && len == (size_t)(off[j] - off[i])) sink(out.data() + off[n], 2);
+        i = j;
+    }
+    return true;
+}
+
+}  // namespace uda

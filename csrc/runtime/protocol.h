@@ -18,7 +18,7 @@ enum Mode { STANDALONE = 0, INTEGRATED = 1 };
 struct Options {
     int wqes_per_conn = 256;  // -w  (kept for compatibility: credits per connection)
     int data_port = 9011;     // -r
-    int merge_approach = 1;   // -a  0 unimplemented, 1 online, 2 hybrid
+    int merge_approach = 1;   // -a  0 unimplemented, 1 online, 2 hybrid, 3 device merge (no counterpart in the reference)
     int mode = INTEGRATED;    // -m
     std::string log_dir = "default";  // -g
     int log_threshold = -1;   // -t  (-1: not given)

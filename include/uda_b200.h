@@ -202,6 +202,13 @@ int uda_can_access_peer(int dev, int peer, int* out);
 int uda_memset_async(void* ptr, int value, long long bytes, cudaStream_t stream);
 int uda_host_alloc_pinned(void** ptr, long long bytes);
 int uda_host_free_pinned(void* ptr);
+/* runtime services for hosts that use this ABI without a CUDA runtime of their own (csrc/runtime/device_merge.cc) */
+int uda_device_count(int* out);
+int uda_set_device(int dev);
+int uda_mem_info(long long* free_bytes, long long* total_bytes);
+int uda_memcpy_h2d_async(void* dst_dev, const void* src_host, long long bytes, cudaStream_t stream);
+int uda_memcpy_d2h_async(void* dst_host, const void* src_dev, long long bytes, cudaStream_t stream);
+int uda_stream_synchronize(cudaStream_t stream);
 /* text for a return code of this library (negative: UDA_E_*, positive: cudaError_t) */
 const char* uda_error_string(int rc);
 

@@ -214,6 +214,7 @@ def _run_job(tmp, n_maps, n_reduces, recs, approach=1, buf_kb=8, key_class="org.
                     break
                 time.sleep(0.02)
             assert not cons.failed and cons.failures == 0, cons.last_error
+            cons.final_stats = {k: cons.stat(k) for k in ("records_emitted", "lpqs_spilled", "device_merges")}
             streams.append(cons.stream())
             assert all(len(b) <= (1 << 20) for b in cons.blocks)
             assert cons.fetch_over >= 1
@@ -345,3 +346,17 @@ def test_regression_driver_parses_matrix(tmp_path):
     rep = json.loads((tmp_path / "report.json").read_text())
     names = [t["name"] for t in rep["tests"]]
     assert "terasort-8gpu" in names and "plumbing-online" in names and len(names) >= 10
+
+
+def test_plumbing_device_merge_falls_back_without_a_gpu(built, tmp_path):
+    """Merge approach 3 (device merge) on a box without a usable GPU: the consumer keeps the segments it fetched and
+    merges them on the CPU; the stream is the same as the online merge's."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is visible: the device path is covered by tests/test_device_merge_gpu.py")
+    streams, truth, consumers, _ = _run_job(str(tmp_path), 5, 2, 300, approach=3, seed=3)
+    for r, s in enumerate(streams):
+        want = list(kway_merge(truth[r]))
+        assert parse_stream(s) == want and s == merged_stream(want)
+    assert all(c.final_stats["device_merges"] == 0 for c in consumers)
+    assert any("device merge not possible" in m for c in consumers for _, m in c.logs)
