@@ -34,6 +34,7 @@ def test_from_dict_types_and_unknown_keys():
         UdaConfig.from_dict({"mapred.rdma.buf.size": "8"})          # below the 16 KiB minimum
     with pytest.raises(ValueError):
         UdaConfig.from_dict({"mapred.netmerger.merge.approach": "7"})
+    assert UdaConfig.from_dict({"mapred.netmerger.merge.approach": "3"}).consumer_argv("/l")[5] == "3"   # device merge
 
 
 def test_from_hadoop_xml(tmp_path):

@@ -70,7 +70,7 @@ def _parse_xmx(opts: str) -> int:
 class UdaConfig:
     wqe_per_conn: int = 256
     cma_port: int = 9011
-    merge_approach: int = 1                 # 1 online, 2 hybrid (0 is parsed and rejected like the reference)
+    merge_approach: int = 1                 # 1 online, 2 hybrid, 3 device merge (0 is parsed and rejected like the reference)
     buf_size_kb: int = 1024
     buf_size_min_kb: int = 16
     shuffle_total_size: int = 0             # 0 -> Xmx x shuffle_input_buffer_percent
@@ -139,8 +139,8 @@ class UdaConfig:
         return out
 
     def validate(self) -> None:
-        if self.merge_approach not in (0, 1, 2):
-            raise ValueError("mapred.netmerger.merge.approach must be 0, 1 or 2")
+        if self.merge_approach not in (0, 1, 2, 3):
+            raise ValueError("mapred.netmerger.merge.approach must be 0, 1 (online), 2 (hybrid) or 3 (device merge)")
         if self.buf_size_kb < self.buf_size_min_kb:
             raise ValueError("mapred.rdma.buf.size is below mapred.rdma.buf.size.min")
         if not (0.0 < self.shuffle_input_buffer_percent <= 1.0):
