@@ -91,6 +91,7 @@ def main() -> int:
             while c.stat("records_emitted") < want[r] and not c.failed and time.perf_counter() - t0 < 600:
                 time.sleep(0.005)
             ok = ok and not c.failed and c.stat("records_emitted") == want[r]
+        phase = [{k: c.stat(k) for k in ("device_merges", "fetch_ms", "device_ms")} for c in cons]
         dt = time.perf_counter() - t0
         # validation: order inside every reducer's stream + byte count (TeraValidate-style, done after the clock stops)
         out_bytes = 0
@@ -105,6 +106,10 @@ def main() -> int:
             ok = ok and bool(np.all((a8[1:] > a8[:-1]) | ((a8[1:] == a8[:-1]) & (t2[1:] >= t2[:-1]))))
             c.reduce_exit()
             c.close()
+        if os.environ.get("UDA_BENCH_LOGS"):
+            for c in cons:
+                for sev, m in c.logs:
+                    if "device merge" in m: print(m, file=sys.stderr)
         prov.command(bridge.form_cmd(bridge.EXIT, []))
         prov.close()
     rec_bytes = sum(want) * 100
@@ -112,7 +117,7 @@ def main() -> int:
                       "value": rec_bytes / dt / 1e9, "unit": "GB/s", "seconds": dt, "record_bytes": rec_bytes, "stream_bytes": out_bytes,
                       "ok": bool(ok), "validated": bool(ok),
                       "config": {"maps": a.maps, "reducers": a.reducers, "approach": a.approach, "buf_kb": a.buf_kb, "transport": "tcp loopback",
-                                 "merge_threads": a.reducers}}))
+                                 "merge_threads": a.reducers}, "consumer_stats": phase}))
     return 0 if ok else 1
 
 

@@ -151,6 +151,8 @@ long long uda_rt_stat(uda_role_t h, const char* what) {
         if (w == "records_emitted") return (long long)r->consumer->records_emitted();
         if (w == "lpqs_spilled") return r->consumer->lpqs_spilled();
         if (w == "device_merges") return r->consumer->device_merges();
+        if (w == "fetch_ms") return r->consumer->fetch_ms();
+        if (w == "device_ms") return r->consumer->device_ms();
     }
     if (r->provider && w == "chunks_served") return (long long)r->provider->chunks_served();
     return -1;

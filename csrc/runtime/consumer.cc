@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
 #include <random>
 
 namespace uda {
@@ -595,7 +596,7 @@ void Consumer::on_init(const HadoopCmd& cmd) {
         int per = (init_.num_maps + lpqs - 1) / lpqs;
         if (init_.num_maps >= lpqs && lpqs > 1) num_kv_bufs = std::min(init_.num_maps, per * parallel);
     }
-    if (opt_.merge_approach == 3) num_kv_bufs = std::min(init_.num_maps, 4);   // the device merge drains 4 sources at a time
+    if (opt_.merge_approach == 3) num_kv_bufs = std::min(init_.num_maps, 8);   // the device merge drains 8 sources at a time
     if (num_kv_bufs < 1) num_kv_bufs = 1;
     double ratio = atof(conf_get(host_, "mapred.rdma.compression.buffer.ratio", "0.20").c_str());
     long long cfg_kb = atoll(conf_get(host_, "mapred.rdma.buf.size", "1024").c_str());
@@ -744,6 +745,7 @@ private:
 
 void Consumer::merge_device() {
     const int n = init_.num_maps;
+    const auto t_start = std::chrono::steady_clock::now();
     std::vector<HostSegment> segs;
     segs.reserve((size_t)n);
     int progress = 0;
@@ -760,17 +762,39 @@ void Consumer::merge_device() {
             }
         }
         batch = shuffle_interleave_hosts(std::move(batch), rng, [](const FetchOrder& o) { return o.host; });
-        // at most `parallel` sources hold buffer pairs at a time; each one is drained into host memory
-        const size_t parallel = 4;
+        // at most `parallel` sources hold buffer pairs at a time; they are drained round-robin so that every one of them
+        // keeps its two chunks in flight (draining one source after the other leaves the rest idle)
+        const size_t parallel = 8;
         for (size_t b0 = 0; b0 < batch.size(); b0 += parallel) {
             std::vector<std::unique_ptr<ByteSource>> started;
             for (size_t i = b0; i < std::min(batch.size(), b0 + parallel); ++i) started.push_back(make_source(batch[i]));
-            for (auto& src : started) {
-                if (stop_) throw UdaError("stopped while fetching");
-                HostSegment hs;
-                const uint8_t* d;
-                size_t len;
-                while (src->next_block(&d, &len)) hs.bytes.insert(hs.bytes.end(), d, d + len);
+            std::vector<HostSegment> part(started.size());
+            std::vector<bool> open(started.size(), true);
+            size_t left = started.size();
+            while (left) {
+                for (size_t i = 0; i < started.size(); ++i) {
+                    if (!open[i]) continue;
+                    if (stop_) throw UdaError("stopped while fetching");
+                    const uint8_t* d;
+                    size_t len;
+                    auto ta = std::chrono::steady_clock::now();
+                    bool got = started[i]->next_block(&d, &len);
+                    auto tb = std::chrono::steady_clock::now();
+                    dbg_wait_us_ += std::chrono::duration_cast<std::chrono::microseconds>(tb - ta).count();
+                    if (got) {
+                        if (part[i].bytes.empty()) {
+                            const long long hint = started[i]->size_hint();
+                            if (hint > 0) part[i].bytes.reserve((size_t)hint + 16);
+                        }
+                        part[i].bytes.insert(part[i].bytes.end(), d, d + len);
+                        dbg_copy_us_ += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - tb).count();
+                    } else {
+                        open[i] = false;
+                        --left;
+                    }
+                }
+            }
+            for (auto& hs : part) {
                 index_segment(&hs);
                 segs.push_back(std::move(hs));
                 ++progress;
@@ -784,10 +808,15 @@ void Consumer::merge_device() {
     };
     long long records = 0;
     std::string why;
+    const auto t_fetched = std::chrono::steady_clock::now();
+    fetch_ms_ = (int)std::chrono::duration_cast<std::chrono::milliseconds>(t_fetched - t_start).count();
+    UDA_LOG(lsINFO, "device merge fetch: %d ms total, %lld ms waiting for chunks, %lld ms copying", fetch_ms_.load(), dbg_wait_us_ / 1000, dbg_copy_us_ / 1000);
     if (DeviceMerge::instance().merge(segs, key_kind_, kStagingBytes, deliver, &records, &why)) {
         emitted_ += (uint64_t)records;
         device_merges_++;
-        UDA_LOG(lsINFO, "device merge of %d segments, %lld records done", n, records);
+        device_ms_ = (int)std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t_fetched).count();
+        UDA_LOG(lsINFO, "device merge of %d segments, %lld records done: fetch %d ms, device merge + delivery %d ms", n, records,
+                fetch_ms_.load(), device_ms_.load());
         return;
     }
     UDA_LOG(lsWARN, "device merge not possible (%s): merging on the CPU", why.c_str());

@@ -47,6 +47,8 @@ public:
     // Next block of the logical stream; the previous block becomes invalid. false = end of stream.
     // Throws UdaError when the underlying fetch failed.
     virtual bool next_block(const uint8_t** data, size_t* len) = 0;
+    // Total bytes this source will deliver when that is known after the first block (-1 otherwise)
+    virtual long long size_hint() const { return -1; }
 };
 
 struct BufferPair {
@@ -93,6 +95,7 @@ public:
     bool next_block(const uint8_t** data, size_t* len) override;
     long long raw_length() const { return raw_len_; }
     long long part_length() const { return part_len_; }
+    long long size_hint() const override { return part_len_; }
     const std::string& map_id() const { return req_.map_id; }
 
 private:
@@ -121,6 +124,10 @@ class DecompressingSource : public ByteSource {
 public:
     DecompressingSource(std::unique_ptr<ByteSource> inner, Codec codec, long long raw_total, const HostCallbacks* host);
     bool next_block(const uint8_t** data, size_t* len) override;
+    long long size_hint() const override {   // rawLength of the index record, learnt by the inner fetch from the first ack
+        auto* fs = dynamic_cast<const FetchSource*>(inner_.get());
+        return fs ? fs->raw_length() : -1;
+    }
 
 private:
     bool read_exact(uint8_t* dst, size_t n);
@@ -212,6 +219,8 @@ public:
     uint64_t records_emitted() const { return emitted_.load(); }
     int lpqs_spilled() const { return spilled_.load(); }
     int device_merges() const { return device_merges_.load(); }
+    int fetch_ms() const { return fetch_ms_.load(); }
+    int device_ms() const { return device_ms_.load(); }
 
 private:
     struct FetchOrder { std::string host, job, map; int reduce; };
@@ -242,8 +251,9 @@ private:
     std::vector<uint8_t> staging_[2];
     std::atomic<uint64_t> emitted_{0};
     std::atomic<int> spilled_{0};
-    std::atomic<int> device_merges_{0};
+    std::atomic<int> device_merges_{0}, fetch_ms_{0}, device_ms_{0};
     int segment_seq_ = 0;
+    long long dbg_wait_us_ = 0, dbg_copy_us_ = 0;   // merge_device(): time blocked in next_block / appending to host memory
 };
 
 }  // namespace uda
