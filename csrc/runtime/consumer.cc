@@ -608,6 +608,8 @@ void Consumer::on_init(const HadoopCmd& cmd) {
     UDA_LOG(lsINFO, " After RDMA buffers registration: buffer1 = %d bytes , buffer2 = %d bytes , buffers count = %d , total = %lld bytes)",
             (int)plan_.pair_size[0], (int)plan_.pair_size[1], plan_.pairs, (long long)pool_->total_bytes());
     initialised_ = true;
+    if (opt_.merge_approach == 3)
+        warm_thread_ = spawn_guarded("device-warm-up", nullptr, nullptr, [] { DeviceMerge::instance().warm_up(); });
     merge_thread_ = std::thread([this] { merge_thread_main(); });
 }
 
@@ -746,6 +748,8 @@ private:
 void Consumer::merge_device() {
     const int n = init_.num_maps;
     const auto t_start = std::chrono::steady_clock::now();
+    // (the CUDA context is created by the warm-up thread that on_init started: about a second on a cold process,
+    //  overlapped with the wait for the first map-completion events and with the fetches)
     std::vector<HostSegment> segs;
     segs.reserve((size_t)n);
     int progress = 0;
@@ -901,6 +905,7 @@ void Consumer::exit_msg() {
     cv_.notify_all();
     if (client_) client_->stop();  // fails in-flight fetches so that a blocked merge thread wakes up
     if (merge_thread_.joinable()) merge_thread_.join();
+    if (warm_thread_.joinable()) warm_thread_.join();
     pool_.reset();
     client_.reset();
     log_close();

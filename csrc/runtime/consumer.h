@@ -247,7 +247,7 @@ private:
     std::condition_variable cv_;
     std::list<FetchOrder> fetch_list_;
     std::atomic<bool> stop_{false}, failed_{false}, initialised_{false};
-    std::thread merge_thread_;
+    std::thread merge_thread_, warm_thread_;
     std::vector<uint8_t> staging_[2];
     std::atomic<uint64_t> emitted_{0};
     std::atomic<int> spilled_{0};

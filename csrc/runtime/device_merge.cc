@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 
 #include "uda_rt.h"
 #include "vint.h"
@@ -48,6 +49,7 @@ struct DeviceMerge::Api {
     int (*gather_var)(const void*, long long, const unsigned long long*, const unsigned long long*, const unsigned long long*, void*, void*);
     int (*write_eof_at)(void*, const unsigned long long*, void*);
     const char* (*error_string)(int);
+    int (*host_alloc_pinned)(void**, long long);
 };
 
 namespace {
@@ -95,12 +97,19 @@ DeviceMerge::DeviceMerge() {
     UDA_SYM(gather_var, "uda_gather_var");
     UDA_SYM(write_eof_at, "uda_write_eof_at");
     UDA_SYM(error_string, "uda_error_string");
+    UDA_SYM(host_alloc_pinned, "uda_host_alloc_pinned");
 #undef UDA_SYM
     if (!all) return;
     int n = 0;
     if (api_->device_count(&n) != 0 || n < 1) { why_ = "no CUDA device visible"; return; }
     ok_ = true;
     UDA_LOG(lsINFO, "device merge back-end ready: %s, %d device(s)", path.c_str(), n);
+}
+
+void DeviceMerge::warm_up() {
+    if (!ok_) return;
+    long long f = 0, t = 0;
+    api_->mem_info(&f, &t);   // the first runtime call that needs a context creates it (about a second on a cold process)
 }
 
 namespace {
@@ -149,6 +158,9 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
         if (why) *why = "partition needs " + std::to_string(need >> 20) + " MiB of device memory, " + std::to_string(free_b >> 20) + " MiB free";
         return false;
     }
+    using Clk = std::chrono::steady_clock;
+    auto ms_since = [](Clk::time_point t) { return (long long)std::chrono::duration_cast<std::chrono::milliseconds>(Clk::now() - t).count(); };
+    const auto t0 = Clk::now();
     DeviceArena arena{this, a.dev_free, {}};
     auto dmalloc = [&](long long bytes) -> uint8_t* {
         void* p = nullptr;
@@ -176,6 +188,8 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
     long long* d_run_off = (long long*)(d_run_recoff + k);
     unsigned* d_flag = (unsigned*)(d_run_off + k + 1);
 
+    const long long ms_alloc = ms_since(t0);
+    const auto t1 = Clk::now();
     std::vector<unsigned long long> h_base(k), h_recoff(k);
     for (int r = 0; r < k; ++r) {
         ck(a.h2d(d_data + seg_pos[r], segs[r].bytes.data(), segs[r].raw_len(), stream), "copy of a segment to the device");
@@ -199,25 +213,78 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
     ck(a.gather_var(d_sorted, n, d_run_base, d_run_recoff, (const unsigned long long*)d_off, d_out, stream), "uda_gather_var");
     ck(a.write_eof_at(d_out, (const unsigned long long*)d_off + n, stream), "uda_write_eof_at");
 
-    std::vector<uint8_t> out((size_t)out_bytes);
+    ck(a.sync(stream), "stream synchronize");
+    const long long ms_h2d_kernels = ms_since(t1);
+    const auto t2 = Clk::now();
     std::vector<unsigned long long> off((size_t)n + 1);
-    ck(a.d2h(out.data(), d_out, out_bytes, stream), "copy of the merged stream to the host");
     ck(a.d2h(off.data(), d_off, (n + 1) * 8, stream), "copy of the stream offsets to the host");
     ck(a.sync(stream), "stream synchronize");
     if ((long long)off[n] + 2 != out_bytes) throw UdaError("device merge produced a stream of unexpected length");
+    const long long ms_d2h = ms_since(t2);
+    const auto t3 = Clk::now();
 
-    // deliver blocks of whole records; the EOF marker rides with the last block (or alone when it does not fit)
-    size_t i = 0;
-    while (i < (size_t)n) {
-        size_t j = i + 1;
-        while (j < (size_t)n && off[j + 1] - off[i] <= max_block) ++j;
-        size_t len = (size_t)(off[j] - off[i]);
-        const bool last = j == (size_t)n;
-        if (last && len + 2 <= max_block) len += 2;
-        sink(out.data() + off[i], len);
-        if (last && len == (size_t)(off[j] - off[i])) sink(out.data() + off[n], 2);
-        i = j;
+    // The merged stream comes back window by window through two pinned staging buffers: the copy of window w+1 is
+    // in flight while window w is delivered in blocks of whole records; the EOF marker rides with the last block
+    // (or alone when it does not fit). A record larger than a window travels through a one-off pageable buffer.
+    std::lock_guard<std::mutex> stage_lock(stage_mu_);
+    if (!stage_[0]) {
+        for (int b = 0; b < 2; ++b) {
+            void* p = nullptr;
+            if (a.host_alloc_pinned(&p, (long long)kStageBytes) != 0 || !p) throw UdaError("pinned staging buffer allocation failed");
+            stage_[b] = (uint8_t*)p;
+        }
     }
+    struct Window { size_t r0, r1; };            // records [r0, r1)
+    auto next_window = [&](size_t r0) {
+        size_t r1 = r0 + 1;
+        // largest r1 with off[r1] - off[r0] (+2 for the EOF marker at the very end) <= kStageBytes, found by bisection
+        size_t lo = r0 + 1, hi = (size_t)n;
+        while (lo < hi) {
+            size_t mid = lo + (hi - lo + 1) / 2;
+            if (off[mid] - off[r0] + (mid == (size_t)n ? 2 : 0) <= kStageBytes) lo = mid; else hi = mid - 1;
+        }
+        r1 = std::max(r1, lo);
+        return Window{r0, r1};
+    };
+    std::vector<uint8_t> big[2];                 // only for a record that does not fit a staging buffer (one per slot)
+    auto start_copy = [&](const Window& w, int slot) -> uint8_t* {
+        const size_t bytes = (size_t)(off[w.r1] - off[w.r0]) + (w.r1 == (size_t)n ? 2 : 0);
+        uint8_t* dst = stage_[slot];
+        if (bytes > kStageBytes) { big[slot].resize(bytes); dst = big[slot].data(); }
+        ck(a.d2h(dst, d_out + off[w.r0], (long long)bytes, stream), "copy of the merged stream to the host");
+        return dst;
+    };
+    Window cur = next_window(0);
+    uint8_t* cur_buf = start_copy(cur, 0);
+    int slot = 0;
+    while (true) {
+        ck(a.sync(stream), "stream synchronize");
+        const bool final_window = cur.r1 == (size_t)n;
+        Window nxt{0, 0};
+        uint8_t* nxt_buf = nullptr;
+        if (!final_window) {
+            nxt = next_window(cur.r1);
+            nxt_buf = start_copy(nxt, slot ^ 1);
+        }
+        const unsigned long long base = off[cur.r0];
+        size_t i = cur.r0;
+        while (i < cur.r1) {
+            size_t j = i + 1;
+            while (j < cur.r1 && off[j + 1] - off[i] <= max_block) ++j;
+            size_t len = (size_t)(off[j] - off[i]);
+            const bool last = final_window && j == cur.r1;
+            if (last && len + 2 <= max_block) len += 2;
+            sink(cur_buf + (off[i] - base), len);
+            if (last && len == (size_t)(off[j] - off[i])) sink(cur_buf + (off[n] - base), 2);
+            i = j;
+        }
+        if (final_window) break;
+        cur = nxt;
+        cur_buf = nxt_buf;
+        slot ^= 1;
+    }
+    UDA_LOG(lsINFO, "device merge phases: alloc %lld ms, H2D + kernels %lld ms, D2H %lld ms, delivery %lld ms (%lld records, %lld bytes, %d runs)",
+            ms_alloc, ms_h2d_kernels, ms_d2h, ms_since(t3), n, out_bytes, k);
     return true;
 }
 

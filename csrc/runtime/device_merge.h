@@ -15,6 +15,7 @@
 #pragma once
 #include <cstdint>
 #include <functional>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -37,6 +38,8 @@ public:
     // Loads the kernel library (UDA_KERNELS_LIB, else libuda_kernels.so next to libuda.so). Never throws.
     static DeviceMerge& instance();
     bool available() const { return ok_; }
+    // Creates the CUDA context now (call it from a helper thread while the fetches are still running)
+    void warm_up();
     const std::string& why_not() const { return why_; }
 
     // Merges the segments (each sorted by `kind`'s comparator) and calls `sink` with consecutive blocks of the merged
@@ -53,6 +56,9 @@ private:
     void* lib_ = nullptr;
     struct Api;
     Api* api_ = nullptr;
+    static constexpr size_t kStageBytes = 32u << 20;   // pinned D2H staging, two buffers, allocated on first use
+    std::mutex stage_mu_;                               // one merge at a time streams through the staging buffers
+    uint8_t* stage_[2] = {nullptr, nullptr};
 };
 
 }  // namespace uda
