@@ -43,9 +43,9 @@ def parse_args():
     ap.add_argument("--records-per-gpu", type=int, default=125_000_000)
     ap.add_argument("--maps-per-gpu", type=int, default=8)
     ap.add_argument("--subparts", type=int, default=0,
-                    help="sub-partitions per reducer pushed/merged as a pipeline (0 = auto: 1 on one GPU, 8 on several)")
+                    help="sub-partitions per reducer pushed/merged as a pipeline (0 = auto: 1 on one GPU, 12 on several)")
     ap.add_argument("--push-ctas", type=int, default=-1,
-                    help="grid of the push kernel (-1 = auto: all SMs on one GPU; pipelined: 32 SMs for tma, 296 CTAs for lsu)")
+                    help="grid of the push kernel (-1 = auto: all SMs on one GPU; pipelined: 36 SMs for tma, 296 CTAs for lsu)")
     ap.add_argument("--push-mode", default="auto", choices=["auto", "lsu", "tma"],
                     help="lsu: load/store push kernel on all SMs; tma: copy-engine push on --push-ctas SMs of its own (one launch "
                          "for all sub-partitions); auto: lsu on one GPU, tma on several")
@@ -157,16 +157,16 @@ def main():
     else:
         from uda_b200.models.terasort import TeraSortJob as Job
 
-    # measured on 8xB200 (profiles/pipeline_sweep.md): 8 sub-partitions pushed by the copy-engine kernel on 32 SMs
-    # of its own while the merge keeps the other 116 take the 8-GPU step from 33.6 ms (push, then merge) and 29.6 ms
-    # (4 sub-partitions, load/store push sharing all SMs with the merge) to 25.5 ms; on one GPU (no NVLink wait to
+    # measured on 8xB200 (profiles/pipeline_sweep.md): 12 sub-partitions pushed by the copy-engine kernel on 36 SMs
+    # of its own while the merge keeps the other 112 take the 8-GPU step from 33.6 ms (push, then merge) and 29.6 ms
+    # (4 sub-partitions, load/store push sharing all SMs with the merge) to 23.8 ms; on one GPU (no NVLink wait to
     # hide) pipelining does not pay
     if a.push_mode == "auto":
         a.push_mode = "tma" if world > 1 else "lsu"
     if a.subparts <= 0:
-        a.subparts = 8 if world > 1 else 1
+        a.subparts = 12 if world > 1 else 1
     if a.push_ctas < 0:
-        a.push_ctas = (32 if a.push_mode == "tma" else 296) if a.subparts > 1 else 0
+        a.push_ctas = (36 if a.push_mode == "tma" else 296) if a.subparts > 1 else 0
     if a.tma_flush > 0:
         from uda_b200._lib import check, kernels
         check(kernels().uda_shuffle_push_tma_set_flush(a.tma_flush), "uda_shuffle_push_tma_set_flush")
