@@ -122,7 +122,7 @@ def kernels() -> C.CDLL:
     """The CUDA kernel library. Raises loudly when it has not been built."""
     global _kernels
     if _kernels is None:
-        p = lib_path("libuda_kernels.so")
+        p = Path(os.environ["UDA_B200_KERNELS_LIB"]) if os.environ.get("UDA_B200_KERNELS_LIB") else lib_path("libuda_kernels.so")
         if not p.exists():
             raise NativeLibraryMissing(
                 f"{p} not found: run `python tools/build.py` (or __graft_entry__.build()) first; "
