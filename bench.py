@@ -51,6 +51,7 @@ def parse_args():
                          "for all sub-partitions); auto: lsu on one GPU, tma on several")
     ap.add_argument("--tma-flush", type=int, default=0, help="tma push: chunks between landed-counter advances (0 = library default)")
     ap.add_argument("--merge-ctas-per-sm", type=int, default=0, help="cap on resident merge CTAs per SM (0 = occupancy limit)")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to the CPUs local to its GPU")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-check", action="store_true")
     return ap.parse_args()
@@ -134,6 +135,11 @@ def main():
         raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    affinity = {"bound": False}
+    if not a.no_numa_bind:
+        # before any pinned allocation: first-touch then places the staging buffers next to this rank's GPU
+        from uda_b200.utils.affinity import bind_to_gpu_numa
+        affinity = bind_to_gpu_numa(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if not os.environ.get("UDA_KEEP_NCCL_DEBUG"):
@@ -244,7 +250,7 @@ def main():
                 "l2_policy": "inputs (12.75 GB/GPU) larger than the 126 MB L2; no flush needed",
                 "timed_region": "shuffle push + flag acquire + key normalise + k-way merge + record gather (map-side sort is set-up)",
             },
-            "clocks": clocks, "e2e": e2e, "phases_ms_max_over_ranks": phases,
+            "clocks": clocks, "e2e": e2e, "phases_ms_max_over_ranks": phases, "cpu_affinity_rank0": affinity,
             "gpu_launches": int(getattr(job, "launches_per_step", 0)) * a.steps,
             "validated": None if check is None else check["ok"],
         }

@@ -91,3 +91,12 @@ def test_fallback_controller_contract(caplog):
     with pytest.raises(FallbackImpossible):
         with late.guard("merge"):
             raise RuntimeError("CUDA error after the first block was delivered")
+
+
+def test_affinity_helper_is_safe_without_a_gpu():
+    from uda_b200.utils.affinity import _parse_cpulist, bind_to_gpu_numa
+    assert _parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11} and _parse_cpulist("") == set()
+    import os
+    before = os.sched_getaffinity(0)
+    info = bind_to_gpu_numa(0)
+    assert info["bound"] is False and os.sched_getaffinity(0) == before
