@@ -51,6 +51,8 @@ def parse_args():
                          "for all sub-partitions); auto: lsu on one GPU, tma on several")
     ap.add_argument("--tma-flush", type=int, default=0, help="tma push: chunks between landed-counter advances (0 = library default)")
     ap.add_argument("--merge-ctas-per-sm", type=int, default=0, help="cap on resident merge CTAs per SM (0 = occupancy limit)")
+    ap.add_argument("--local-zero-copy", action="store_true",
+                    help="merge this rank's own map outputs in place instead of copying them into its arena (implies --no-e2e)")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to the CPUs local to its GPU")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-check", action="store_true")
@@ -180,7 +182,7 @@ def main():
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev).setup()
     else:
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev, subparts=a.subparts, push_ctas=a.push_ctas,
-                  merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode).setup()
+                  merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode, local_zero_copy=a.local_zero_copy).setup()
     total_bytes = float(a.records_per_gpu) * RECORD_BYTES * world
 
     def timed(fn, steps, warmup, sample_clocks):
@@ -221,7 +223,7 @@ def main():
             return 1
 
     e2e = None
-    if not a.no_e2e and hasattr(job, "e2e_setup"):
+    if not a.no_e2e and not a.local_zero_copy and hasattr(job, "e2e_setup"):
         try:
             job.e2e_setup()
             ems, _ = timed(job.e2e_step, a.steps, max(1, min(a.warmup, 3)), False)
@@ -245,7 +247,7 @@ def main():
                 "model": "TeraSort 100 GB/8 GPUs (12.5 GB per GPU), 100-byte teragen records, IFile-framed sorted MOFs in HBM",
                 "global_batch": a.records_per_gpu * world, "seq_len": RECORD_BYTES,
                 "records_per_gpu": a.records_per_gpu, "maps_per_gpu": a.maps_per_gpu, "runs_per_reducer": a.maps_per_gpu * world,
-                "subparts": a.subparts, "push_mode": a.push_mode, "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
+                "subparts": a.subparts, "push_mode": a.push_mode, "local_zero_copy": a.local_zero_copy, "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
                 "parallelism": f"partition-parallel a2a x{world} (one reducer per GPU)",
                 "l2_policy": "inputs (12.75 GB/GPU) larger than the 126 MB L2; no flush needed",
                 "timed_region": "shuffle push + flag acquire + key normalise + k-way merge + record gather (map-side sort is set-up)",

@@ -15,13 +15,14 @@ def main():
     steps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
     subparts = int(sys.argv[4]) if len(sys.argv) > 4 else 1
     mode = sys.argv[5] if len(sys.argv) > 5 else "lsu"
+    zero_copy = len(sys.argv) > 6 and sys.argv[6] == "1"
     lr = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(lr)
     dev = torch.device("cuda", lr)
     dist.init_process_group("nccl", device_id=dev)
     from uda_b200.models.terasort import TeraSortJob
 
-    job = TeraSortJob(n, maps, device=dev, subparts=subparts, push_mode=mode, push_ctas=16 if mode == "tma" else 0).setup()
+    job = TeraSortJob(n, maps, device=dev, subparts=subparts, push_mode=mode, push_ctas=16 if mode == "tma" else 0, local_zero_copy=zero_copy).setup()
     out = None
     for _ in range(steps):
         out = job.step()

@@ -333,6 +333,24 @@ def test_terasort_job_single_gpu(built, n, maps, key_bits, subparts, mode):
         job.close()
 
 
+@pytest.mark.parametrize("subparts,mode", [(1, "lsu"), (3, "tma")])
+def test_terasort_job_local_zero_copy(built, subparts, mode):
+    """Own map outputs merged in place: nothing is pushed on one GPU, the result is the same stream."""
+    from uda_b200.models.terasort import TeraSortJob
+    job = TeraSortJob(120_000, 4, device=_dev(), subparts=subparts, push_mode=mode, push_ctas=8 if mode == "tma" else 0,
+                      local_zero_copy=True).setup()
+    ref = TeraSortJob(120_000, 4, device=_dev()).setup()
+    try:
+        for _ in range(2):
+            out = job.step()
+        assert job.check(out)["ok"]
+        assert int(job.arena.flags().abs().sum().item()) == 0          # no byte went through the arena
+        assert torch.equal(out, ref.step())
+    finally:
+        job.close()
+        ref.close()
+
+
 # ------------------------------------------------------------------------------------------- partition / combine / wordcount
 @pytest.mark.parametrize("mode,P,stride", [(0, 7, 16), (1, 5, 16), (0, 3, 102), (1, 8, 102)])
 def test_partition_count_and_scatter(K, mode, P, stride):

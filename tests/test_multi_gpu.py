@@ -32,6 +32,15 @@ def test_terasort_multi_rank(built, world, subparts, mode):
     assert text.count("MPRESULT") == world and text.count('"ok": true') == world, text[-6000:]
 
 
+def test_terasort_local_zero_copy_two_ranks(built):
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    p = _torchrun(2, "mp_terasort.py", 500_000, 3, 3, 4, "tma", 1)
+    text = p.stdout + "\n" + p.stderr
+    assert p.returncode == 0, text[-6000:]
+    assert text.count("MPRESULT") == 2 and text.count('"ok": true') == 2, text[-6000:]
+
+
 @pytest.mark.parametrize("world", [2, 8])
 def test_wordcount_multi_rank(built, world):
     if _ngpu() < world:

@@ -54,7 +54,7 @@ class TeraSortJob:
 
     def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 1234,
                  key_bits: int = 0, group=None, push_ctas: int = 0, subparts: int = 1, merge_ctas_per_sm: int = 0,
-                 push_mode: str = "lsu"):
+                 push_mode: str = "lsu", local_zero_copy: bool = False):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -72,6 +72,10 @@ class TeraSortJob:
         #: launch for all sub-partitions on `push_ctas` SMs of its own, the merge keeps the remaining SMs
         assert push_mode in ("lsu", "tma")
         self.push_mode = push_mode
+        #: merge this rank's own map outputs where they lie instead of copying them into the arena first (the
+        #: reference and Hadoop copy local fetches like remote ones). Off by default: the headline benchmark moves
+        #: every segment. Not available on the end-to-end path, whose map outputs alternate between two buffers.
+        self.local_zero_copy = local_zero_copy
         #: polls of the landed-byte counters before the wait kernel gives up and records a time-out in the arena's
         #: status word (the watchdog that turns a lost push into a failure up-call instead of a hang)
         self.wait_max_spins = 50_000_000
@@ -125,6 +129,13 @@ class TeraSortJob:
         max_sub = 1
         for j in range(C):
             rd, run_off, run_base, run_bytes = self.plan.run_descs(self.rank, self.arena.peer_data_ptr(self.rank), j)
+            if self.local_zero_copy:
+                for m, mof in enumerate(self.mofs):
+                    rid = self.plan.run_id(self.rank, m)
+                    base = mof.data.data_ptr() + int(self.plan.index[self.rank, m, self.rank * C + j, 0])
+                    rd["base"][rid] = base
+                    run_base[rid] = base
+                    run_bytes[rid] = 0                       # nothing will land for this run
             self.sub_n.append(int(run_off[-1]))
             max_sub = max(max_sub, self.sub_n[-1])
             expect.append(run_bytes.astype(np.int64))
@@ -150,9 +161,14 @@ class TeraSortJob:
     # ------------------------------------------------------------------------------------ step
     def _push_tables(self, mof_ptrs) -> List[torch.Tensor]:
         P = self.world
-        return [K.to_device_struct(self.plan.push_descs(self.rank, mof_ptrs, [self.arena.peer_data_ptr(p) for p in range(P)],
-                                                        [self.arena.peer_flag_ptr(p, 0) for p in range(P)], j), self.device)
-                for j in range(self.subparts)]
+        tables = []
+        for j in range(self.subparts):
+            d = self.plan.push_descs(self.rank, mof_ptrs, [self.arena.peer_data_ptr(p) for p in range(P)],
+                                     [self.arena.peer_flag_ptr(p, 0) for p in range(P)], j)
+            if self.local_zero_copy:
+                d["bytes"][(P - 1) * self.maps:] = 0      # the last `maps` descriptors are the ones addressed to this rank
+            tables.append(K.to_device_struct(d, self.device))
+        return tables
 
     def _merge_sub(self, j: int, out: torch.Tensor) -> None:
         C, nruns = self.subparts, self.plan.nruns
@@ -270,6 +286,7 @@ class TeraSortJob:
         output buffers are double-buffered so H2D of step i+1, compute of step i and D2H of step i-1
         overlap on three streams."""
         dev = self.device
+        assert not self.local_zero_copy, "the end-to-end path double-buffers the map outputs: local_zero_copy is not supported there"
         out_bytes = self.n_out * TERA_STRIDE + 2
         need = sum(int(m.index[-1, 0] + m.index[-1, 2]) for m in self.mofs) + 2 * self.E2E_RING_BYTES
         avail = _host_mem_available()
