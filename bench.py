@@ -51,6 +51,7 @@ def parse_args():
                          "for all sub-partitions); auto: lsu on one GPU, tma on several")
     ap.add_argument("--tma-flush", type=int, default=0, help="tma push: chunks between landed-counter advances (0 = library default)")
     ap.add_argument("--merge-ctas-per-sm", type=int, default=0, help="cap on resident merge CTAs per SM (0 = occupancy limit)")
+    ap.add_argument("--graph", action="store_true", help="time replays of the step captured as a CUDA graph (one GPU, no pipelining)")
     ap.add_argument("--local-zero-copy", action="store_true",
                     help="merge this rank's own map outputs in place instead of copying them into its arena (implies --no-e2e)")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to the CPUs local to its GPU")
@@ -203,7 +204,15 @@ def main():
         clocks = sampler.stop() if sampler else None
         return ms, clocks
 
-    ms, clocks = timed(job.step, a.steps, a.warmup, True)
+    step_fn = job.step
+    if a.graph and a.impl == "uda_b200":
+        if world > 1 or a.subparts > 1:
+            raise SystemExit("--graph is offered for the single-stream configuration (one GPU, --subparts 1)")
+        for _ in range(2):
+            job.step()
+        graph, _graph_out = job.capture()
+        step_fn = graph.replay
+    ms, clocks = timed(step_fn, a.steps, a.warmup, True)
     ms_per_step = ms / a.steps
     value = total_bytes / (ms_per_step * 1e-3) / 1e9
 
@@ -247,7 +256,7 @@ def main():
                 "model": "TeraSort 100 GB/8 GPUs (12.5 GB per GPU), 100-byte teragen records, IFile-framed sorted MOFs in HBM",
                 "global_batch": a.records_per_gpu * world, "seq_len": RECORD_BYTES,
                 "records_per_gpu": a.records_per_gpu, "maps_per_gpu": a.maps_per_gpu, "runs_per_reducer": a.maps_per_gpu * world,
-                "subparts": a.subparts, "push_mode": a.push_mode, "local_zero_copy": a.local_zero_copy, "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
+                "subparts": a.subparts, "push_mode": a.push_mode, "local_zero_copy": a.local_zero_copy, "cuda_graph": bool(a.graph), "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
                 "parallelism": f"partition-parallel a2a x{world} (one reducer per GPU)",
                 "l2_policy": "inputs (12.75 GB/GPU) larger than the 126 MB L2; no flush needed",
                 "timed_region": "shuffle push + flag acquire + key normalise + k-way merge + record gather (map-side sort is set-up)",

@@ -134,6 +134,28 @@ __global__ void barrier_kernel(unsigned long long* const* __restrict__ pads /* [
     }
 }
 
+// Same barrier, epoch taken from (and advanced in) a counter in this rank's own memory: the launch has no
+// host-side state, so it can sit inside a captured CUDA graph that is replayed once per step. Every rank runs the
+// same sequence of barriers, so the counters stay in step.
+__global__ void barrier_counted_kernel(unsigned long long* const* __restrict__ pads, int rank, int world,
+                                       unsigned long long* __restrict__ counter, unsigned long long max_spins,
+                                       unsigned* __restrict__ status) {
+    __shared__ unsigned long long s_epoch;
+    if (threadIdx.x == 0) { s_epoch = *counter + 1ull; *counter = s_epoch; }
+    __syncthreads();
+    const unsigned long long epoch = s_epoch;
+    const int p = threadIdx.x;
+    if (p < world) {
+        __threadfence_system();
+        st_release_sys(pads[p] + rank, epoch);
+        unsigned long long spins = 0;
+        while (ld_acquire_sys(pads[rank] + p) < epoch) {
+            if (++spins > max_spins) { atomicExch(status, 2u); break; }
+            __nanosleep(200);
+        }
+    }
+}
+
 }  // namespace uda
 
 // process-wide interleave factor for uda_shuffle_push (set once per job to the number of destination ranks)
@@ -171,6 +193,14 @@ extern "C" int uda_barrier_all(unsigned long long* const* pads_dev, int rank, in
                                unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream) {
     if (world < 1 || world > 64) return UDA_E_INVALID;
     uda::barrier_kernel<<<1, 64, 0, stream>>>(pads_dev, rank, world, epoch, max_spins, status_dev);
+    UDA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int uda_barrier_all_counted(unsigned long long* const* pads_dev, int rank, int world, unsigned long long* counter_dev,
+                                       unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream) {
+    if (world < 1 || world > 64 || !counter_dev) return UDA_E_INVALID;
+    uda::barrier_counted_kernel<<<1, 64, 0, stream>>>(pads_dev, rank, world, counter_dev, max_spins, status_dev);
     UDA_CHECK_LAUNCH();
     return 0;
 }

@@ -160,6 +160,10 @@ int uda_wait_flags(const unsigned long long* flags_dev, const unsigned long long
                    unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream);
 int uda_barrier_all(unsigned long long* const* pads_dev, int rank, int world, unsigned long long epoch,
                     unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream);
+/* the same barrier with the epoch kept in *counter_dev (this rank's memory, advanced by the kernel): no host-side
+ * state, so the launch can be part of a captured CUDA graph that is replayed every step */
+int uda_barrier_all_counted(unsigned long long* const* pads_dev, int rank, int world, unsigned long long* counter_dev,
+                            unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream);
 
 /* ---- K7 CRC32, zlib polynomial (no reference counterpart: the reference transfers Hadoop's IFile
  *      checksum and ignores it, src/MOFServer/IndexInfo.cc:308-310, src/Merger/StreamRW.cc:361-367) - */

@@ -333,6 +333,25 @@ def test_terasort_job_single_gpu(built, n, maps, key_bits, subparts, mode):
         job.close()
 
 
+def test_terasort_step_as_cuda_graph(built):
+    """The whole step replays from a captured graph: flag expectations advance on the device, so every replay waits
+    for its own push."""
+    from uda_b200.models.terasort import TeraSortJob
+    job = TeraSortJob(150_000, 4, device=_dev()).setup()
+    try:
+        want = job.step().clone()
+        g, out = job.capture()
+        for _ in range(3):
+            out.zero_()
+            g.replay()
+            torch.cuda.synchronize()
+            assert torch.equal(out, want)
+        assert job.check(out)["ok"]
+        job.raise_on_failure()
+    finally:
+        job.close()
+
+
 @pytest.mark.parametrize("subparts,mode", [(1, "lsu"), (3, "tma")])
 def test_terasort_job_local_zero_copy(built, subparts, mode):
     """Own map outputs merged in place: nothing is pushed on one GPU, the result is the same stream."""

@@ -70,6 +70,7 @@ _PROTOS = {
     "uda_shuffle_push_tma": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_int, c_vp]),
     "uda_wait_flags": (c_int, [c_vp, c_vp, c_int, c_ull, c_vp, c_vp]),
     "uda_barrier_all": (c_int, [c_vp, c_int, c_int, c_ull, c_ull, c_vp, c_vp]),
+    "uda_barrier_all_counted": (c_int, [c_vp, c_int, c_int, c_vp, c_ull, c_vp, c_vp]),
     "uda_partition_count": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp]),
     "uda_partition_scatter": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp, c_vp]),
     "uda_combine_heads": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_vp, c_vp]),

@@ -215,6 +215,18 @@ class TeraSortJob:
             cur.wait_event(self.ev_pushed)  # the step is over only when this rank's own pushes have retired
         return out[: self.n_out * TERA_STRIDE + 2]
 
+    def capture(self):
+        """Captures one :meth:`step` into a CUDA graph and returns ``(graph, out)``; ``graph.replay()`` then runs a
+        whole shuffle + merge with one launch from the host (16 kernels on one GPU, ~170 on eight). Nothing in a step
+        depends on host state: the landed-byte expectations and the barrier epoch advance on the device. With
+        sub-partition pipelining the graph has two branches (push, wait + merge) that must run concurrently, exactly
+        as the two streams do in eager mode."""
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            out = self.step()
+        return g, out
+
     def step_timeline(self) -> dict:
         """One pipelined step with an event after every push (side stream) and around every sub-partition merge
         (main stream); times in ms since the start of the step (diagnostics for the overlap)."""

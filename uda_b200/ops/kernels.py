@@ -236,6 +236,13 @@ def barrier_all(pads_dev: torch.Tensor, rank: int, world: int, epoch: int, statu
           "uda_barrier_all")
 
 
+def barrier_all_counted(pads_dev: torch.Tensor, rank: int, world: int, counter: torch.Tensor, status: torch.Tensor,
+                        max_spins: int = 50_000_000) -> None:
+    """All-rank barrier whose epoch lives in ``counter`` (int64[1], this rank's memory): graph-capturable."""
+    check(kernels().uda_barrier_all_counted(pads_dev.data_ptr(), rank, world, counter.data_ptr(), max_spins, status.data_ptr(), _stream()),
+          "uda_barrier_all_counted")
+
+
 # ------------------------------------------------------------------------------------------------ crc / ifile
 def crc32(data: torch.Tensor, n: Optional[int] = None, out_be4: Optional[torch.Tensor] = None) -> torch.Tensor:
     """CRC32 (zlib) of the first ``n`` bytes; returns a 1-element int32 device tensor (no sync)."""

@@ -12,7 +12,7 @@ into it over NVLink and publish flags that live in the same arena.
 Arena layout (offsets in bytes)::
 
     0      barrier pad   64 x u64   slot[r] written by rank r (uda_barrier_all)
-    512    status words  64 x u32
+    512    status words  16 x u32, then the barrier epoch counter (u64 at 576)
     4096   flags         max_runs x u64  "bytes landed" counter per incoming run
     D      data          receive segments (D = 4096-aligned)
 """
@@ -101,7 +101,8 @@ class SymmetricArena:
         # device table of barrier-pad pointers (one per rank)
         self.pads_dev = torch.tensor([p + BARRIER_OFF for p in self.peer_ptrs], dtype=torch.int64, device=device)
         self.status = self.local_tensor()[STATUS_OFF:STATUS_OFF + 8].view(torch.int32)
-        self.epoch = 0
+        #: barrier epoch, kept on the device so that a barrier launch carries no host state (CUDA-graph replay)
+        self.epoch_dev = self.local_tensor()[STATUS_OFF + 64:STATUS_OFF + 72].view(torch.int64)
 
     # ---- views -------------------------------------------------------------------------------
     def local_tensor(self) -> torch.Tensor:
@@ -125,10 +126,9 @@ class SymmetricArena:
 
     def barrier(self) -> None:
         """All-rank barrier over peer memory on the current stream (no NCCL, no host sync)."""
-        from ..ops.kernels import barrier_all
+        from ..ops.kernels import barrier_all_counted
 
-        self.epoch += 1
-        barrier_all(self.pads_dev, self.rank, self.world, self.epoch, self.status)
+        barrier_all_counted(self.pads_dev, self.rank, self.world, self.epoch_dev, self.status)
 
     def close(self) -> None:
         for p in self.peers:
