@@ -3,7 +3,7 @@
 # this file only gives the usual verbs.
 PY ?= python
 
-.PHONY: all native java test test-gpu bench sass sanitize asan tsan wheel rpm clean
+.PHONY: all native java test test-gpu bench sass sanitize asan tsan analyze wheel rpm clean
 
 all: native
 
@@ -35,6 +35,10 @@ asan:
 	scripts/ci/host_sanitizers.sh address
 tsan:
 	scripts/ci/host_sanitizers.sh thread
+
+# stricter warning set + cppcheck (when installed) over the host runtime
+analyze:
+	scripts/ci/static_analysis.sh
 
 wheel: native
 	$(PY) -m pip wheel --no-deps --no-build-isolation -w dist .

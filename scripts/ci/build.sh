@@ -14,6 +14,8 @@ python -m pytest tests/ -x -q -m "not gpu"
 echo "== host sanitizers =="
 scripts/ci/host_sanitizers.sh address
 scripts/ci/host_sanitizers.sh thread
+echo "== static analysis =="
+scripts/ci/static_analysis.sh
 echo "== SASS evidence =="
 python tools/sass_listing.py > /dev/null
 grep -q "UBLKCP" profiles/SASS_SUMMARY.md || { echo "no TMA bulk copies in the merge/push kernels"; exit 1; }
