@@ -784,14 +784,14 @@ void Consumer::merge_device() {
                     auto ta = std::chrono::steady_clock::now();
                     bool got = started[i]->next_block(&d, &len);
                     auto tb = std::chrono::steady_clock::now();
-                    dbg_wait_us_ += std::chrono::duration_cast<std::chrono::microseconds>(tb - ta).count();
+                    fetch_wait_us_ += std::chrono::duration_cast<std::chrono::microseconds>(tb - ta).count();
                     if (got) {
                         if (part[i].bytes.empty()) {
                             const long long hint = started[i]->size_hint();
                             if (hint > 0) part[i].bytes.reserve((size_t)hint + 16);
                         }
                         part[i].bytes.insert(part[i].bytes.end(), d, d + len);
-                        dbg_copy_us_ += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - tb).count();
+                        fetch_copy_us_ += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - tb).count();
                     } else {
                         open[i] = false;
                         --left;
@@ -814,7 +814,7 @@ void Consumer::merge_device() {
     std::string why;
     const auto t_fetched = std::chrono::steady_clock::now();
     fetch_ms_ = (int)std::chrono::duration_cast<std::chrono::milliseconds>(t_fetched - t_start).count();
-    UDA_LOG(lsINFO, "device merge fetch: %d ms total, %lld ms waiting for chunks, %lld ms copying", fetch_ms_.load(), dbg_wait_us_ / 1000, dbg_copy_us_ / 1000);
+    UDA_LOG(lsINFO, "device merge fetch: %d ms total, %lld ms waiting for chunks, %lld ms copying", fetch_ms_.load(), fetch_wait_us_ / 1000, fetch_copy_us_ / 1000);
     if (DeviceMerge::instance().merge(segs, key_kind_, kStagingBytes, deliver, &records, &why)) {
         emitted_ += (uint64_t)records;
         device_merges_++;

@@ -253,7 +253,7 @@ private:
     std::atomic<int> spilled_{0};
     std::atomic<int> device_merges_{0}, fetch_ms_{0}, device_ms_{0};
     int segment_seq_ = 0;
-    long long dbg_wait_us_ = 0, dbg_copy_us_ = 0;   // merge_device(): time blocked in next_block / appending to host memory
+    long long fetch_wait_us_ = 0, fetch_copy_us_ = 0;   // merge_device(): time blocked in next_block / appending to host memory
 };
 
 }  // namespace uda
