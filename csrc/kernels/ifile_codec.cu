@@ -47,6 +47,9 @@ __global__ void unframe_fixed_kernel(const uint8_t* __restrict__ framed, long lo
 }
 
 // ---------------------------------------------------------------------------------- general decode
+#ifndef UDA_DC_DOUBLING
+#define UDA_DC_DOUBLING 0   // 1 = the earlier pointer-doubling resolution of the chunk maps
+#endif
 constexpr int DC_CHUNK = 4096;           // bytes per chunk (one CTA)
 constexpr int DC_THREADS = 256;
 constexpr unsigned DC_EXIT = 0x80000000u;  // high bit: the chain left the chunk; low bits = overshoot
@@ -107,6 +110,7 @@ __global__ void __launch_bounds__(DC_THREADS) decode_chunk_maps_kernel(const uin
         else { nxt[e] = (unsigned)(nx - base); cnt[e] = 1; }
     }
     __syncthreads();
+#if UDA_DC_DOUBLING
     // pointer doubling: a record is >= 2 bytes so at most DC_CHUNK/2 hops = 12 rounds; stop as soon as every chain
     // has left the chunk (records of ~100 bytes need 6 rounds)
     for (int round = 0; round < 12; ++round) {
@@ -127,6 +131,51 @@ __global__ void __launch_bounds__(DC_THREADS) decode_chunk_maps_kernel(const uin
         }
         __syncthreads();
     }
+#else
+    // Chains only move forward (a record is >= 2 bytes), so "where does the chain from e leave the chunk" resolves in
+    // ONE backward sweep: when offset e is visited, everything its hop can reach has been resolved already. Pointer
+    // doubling did the same with log2(hops) rounds over all 4096 entries and was bound by shared-memory wavefronts
+    // (~18 k per chunk); the sweep needs ~1.5 k.
+    //   pass A: every warp sweeps its own strip of 512 offsets from the top, 32 offsets at a time. A hop that stays
+    //           inside the group of 32 (< 32 bytes: rare) is resolved with shuffles, highest offset first.
+    //           After the pass an entry holds its final exit, or an offset inside a LATER strip.
+    //   pass B: strips from the second-to-last down to the first pick up the (already final) value of that offset.
+    {
+        constexpr int STRIP = DC_CHUNK / (DC_THREADS / 32);
+        const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+        const int s0 = wrp * STRIP, s1 = s0 + STRIP;
+        for (int g = s1 - 32; g >= s0; g -= 32) {
+            const int e = g + lane;
+            const unsigned t = nxt[e], c = cnt[e];
+            unsigned ex = t, cc = c;
+            const bool ingroup = !(t & DC_EXIT) && t < (unsigned)(g + 32);
+            bool resolved = true;
+            if (!(t & DC_EXIT) && t < (unsigned)s1) {
+                if (!ingroup) { ex = nxt[t]; cc = c + cnt[t]; }   // a later group of this strip: already swept
+                else resolved = false;
+            }
+            unsigned pending = __ballot_sync(0xffffffffu, !resolved);
+            while (pending) {
+                const int tl = ingroup ? (int)(t - (unsigned)g) : lane;
+                const unsigned vex = __shfl_sync(0xffffffffu, ex, tl), vcc = __shfl_sync(0xffffffffu, cc, tl);
+                const int vres = __shfl_sync(0xffffffffu, (int)resolved, tl);
+                if (!resolved && vres) { ex = vex; cc = c + vcc; resolved = true; }
+                pending = __ballot_sync(0xffffffffu, !resolved);
+            }
+            nxt[e] = ex;
+            cnt[e] = cc;
+            __syncwarp();
+        }
+        for (int s = DC_THREADS / 32 - 2; s >= 0; --s) {
+            __syncthreads();
+            for (int e = s * STRIP + threadIdx.x; e < (s + 1) * STRIP; e += DC_THREADS) {
+                const unsigned t = nxt[e];
+                if (!(t & DC_EXIT)) { nxt[e] = nxt[t]; cnt[e] += cnt[t]; }   // t lies in a later strip: final by now
+            }
+        }
+        __syncthreads();
+    }
+#endif
     for (int e = threadIdx.x; e < DC_CHUNK; e += DC_THREADS) {
         exit_map[wbase + e] = nxt[e];
         cnt_map[wbase + e] = cnt[e];

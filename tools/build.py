@@ -84,7 +84,7 @@ def build(verbose: bool = False) -> dict:
     version = uda_version()
     cu = sorted((ROOT / "csrc" / "kernels").glob("*.cu"))
     cc = sorted((ROOT / "csrc" / "runtime").glob("*.cc")) + sorted((ROOT / "csrc" / "jni").glob("*.cc"))
-    vflag = [f'-DVERSION_UDA="{version}"'] + [f"-D{k}={v}" for k, v in sorted(os.environ.items()) if k.startswith(("UDA_FR_", "UDA_TP_"))]
+    vflag = [f'-DVERSION_UDA="{version}"'] + [f"-D{k}={v}" for k, v in sorted(os.environ.items()) if k.startswith(("UDA_FR_", "UDA_TP_", "UDA_DC_"))]
     with cf.ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
         cu_objs = list(ex.map(lambda s: _compile(s, NVCC, NVCC_FLAGS + vflag), cu))
         cc_objs = list(ex.map(lambda s: _compile(s, CXX, CXX_FLAGS + vflag), cc))
