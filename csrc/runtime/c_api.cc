@@ -274,6 +274,17 @@ long long uda_rt_snappy_compress(const unsigned char* in, long long n, unsigned 
     return (long long)v.size();
 }
 
+long long uda_rt_lzo1x_compress(const unsigned char* in, long long n, unsigned char* out, long long cap) {
+    std::vector<uint8_t> v;
+    lzo1x_compress(in, (size_t)n, &v);
+    if ((long long)v.size() > cap) return -1;
+    memcpy(out, v.data(), v.size());
+    return (long long)v.size();
+}
+int uda_rt_lzo1x_decompress(const unsigned char* in, long long n, unsigned char* out, long long out_len) {
+    return lzo1x_decompress_builtin(in, (size_t)n, out, (size_t)out_len) ? 0 : -1;
+}
+
 // out4 = {buffer_size, pairs, pair0, pair1}; returns 0, or 1/2 for the two sizing failures
 int uda_rt_plan_memory(int num_maps, long long max_buf, long long min_buf, long long shuffle_mem, int compressed, double ratio,
                        long long* out4) {

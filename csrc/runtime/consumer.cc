@@ -247,10 +247,15 @@ bool codec_decompress(Codec c, const uint8_t* in, size_t in_len, uint8_t* out, s
         return snappy_uncompress_builtin(in, in_len, out, out_len);
     }
     if (c == Codec::LZO) {
-        auto fn = load_lzo(host);
-        if (!fn) throw UdaError("LZO map-output compression needs liblzo2, which cannot be loaded");
-        unsigned long ol = out_len;
-        return fn(in, in_len, out, &ol, nullptr) == 0 && ol == out_len;
+        if (auto fn = load_lzo(host)) {
+            unsigned long ol = out_len;
+            return fn(in, in_len, out, &ol, nullptr) == 0 && ol == out_len;
+        }
+        // no liblzo2 on this machine: the built-in decoder handles the LZO1X family's stream format (LZO1X-1, -999)
+        std::string which = conf_get(host, "io.compression.codec.lzo.decompressor", "LZO1X");
+        if (which.compare(0, 5, "LZO1X") != 0)
+            throw UdaError("LZO decompressor " + which + " needs liblzo2, which cannot be loaded (built in: LZO1X only)");
+        return lzo1x_decompress_builtin(in, in_len, out, out_len);
     }
     if (in_len != out_len) return false;
     memcpy(out, in, in_len);

@@ -360,3 +360,80 @@ def test_plumbing_device_merge_falls_back_without_a_gpu(built, tmp_path):
         assert parse_stream(s) == want and s == merged_stream(want)
     assert all(c.final_stats["device_merges"] == 0 for c in consumers)
     assert any("device merge not possible" in m for c in consumers for _, m in c.logs)
+
+
+# ------------------------------------------------------------------------------------------ built-in LZO1X
+def _lzo_dec(L, stream, n):
+    out = _buf(max(n, 1))
+    rc = L.uda_rt_lzo1x_decompress(stream, len(stream), out, n)
+    return rc, out.raw[:n]
+
+
+def test_lzo1x_decoder_hand_made_streams(L):
+    """Streams written by hand from the format description (not by this repo's compressor), one per instruction form."""
+    end = bytes([0x11, 0, 0])
+    # first-byte literal (17+3), then 001L LLLL match: len 2+7=9, distance 3, no trailing literals
+    assert _lzo_dec(L, bytes([20]) + b"abc" + bytes([0x27, (3 - 1) << 2, 0]) + end, 12) == (0, b"abcabcabcabc")
+    # first-byte literal of 5 (state 4), then 0000 DDSS H = 3-byte match at distance 2049 + D + 4H: not reachable with 5
+    # bytes of history -> the decoder must refuse instead of reading before the buffer
+    assert _lzo_dec(L, bytes([22]) + b"hello" + bytes([0x00, 0x00]) + end, 8)[0] == -1
+    # 01LD DDSS H: len 3+L, distance = 8H + D + 1; "abcdef" + copy 4 bytes from distance 6 + 1 trailing literal 'X'
+    m2 = bytes([0x40 | (1 << 5) | ((6 - 1) << 2) | 1, 0])
+    assert _lzo_dec(L, bytes([17 + 6]) + b"abcdef" + m2 + b"X" + end, 11) == (0, b"abcdefabcdX")
+    # 1LLD DDSS H: len 5+LL=8, distance 2 (overlapping copy = repeating pattern)
+    m2b = bytes([0x80 | (3 << 5) | ((2 - 1) << 2), 0])
+    assert _lzo_dec(L, bytes([17 + 2]) + b"xy" + m2b + end, 10) == (0, b"xyxyxyxyxy")
+    # 0000 LLLL literal run in the middle (state 0): "ab" + match len 4 dist 2 + run of 3+1=4 literals "WXYZ"
+    m3 = bytes([0x20 | (4 - 2), (2 - 1) << 2, 0])
+    assert _lzo_dec(L, bytes([19]) + b"ab" + m3 + bytes([1]) + b"WXYZ" + end, 10) == (0, b"abababWXYZ")
+    # state 1..3 then 0000 DDSS H = 2-byte match at distance 4H + D + 1: "abcd" + match(len 3, dist 4, 1 trailing 'Q') + 2-byte match dist 1
+    m3s = bytes([0x20 | (3 - 2), ((4 - 1) << 2) | 1, 0])
+    assert _lzo_dec(L, bytes([21]) + b"abcd" + m3s + b"Q" + bytes([0x00, 0x00]) + end, 10) == (0, b"abcdabcQQQ")
+    # 0001 HLLL far match (distance 16384 + D): 16400 bytes of history, copy 5 from 16390 back
+    hist = bytes(i % 251 for i in range(16400))
+    t = 16400 - 18
+    run = bytes([0]) + bytes(t // 255 if t % 255 else t // 255 - 1) + bytes([t % 255 or 255])
+    far = bytes([0x10 | (5 - 2), ((16390 - 16384) << 2) & 0xFF, ((16390 - 16384) << 2) >> 8])
+    rc, out = _lzo_dec(L, run + hist + far + end, 16405)
+    assert rc == 0 and out == hist + hist[16400 - 16390:16400 - 16390 + 5]
+    # truncated stream and wrong output length are errors
+    good = bytes([20]) + b"abc" + bytes([0x27, 8, 0]) + end
+    assert _lzo_dec(L, good[:-1], 12)[0] == -1 and _lzo_dec(L, good, 11)[0] == -1 and _lzo_dec(L, good, 13)[0] == -1
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 4, 5, 18, 19, 238, 239, 240, 1000, 70000, 300000])
+def test_lzo1x_round_trip(L, n):
+    L.uda_rt_lzo1x_compress.restype = C.c_longlong
+    rng = random.Random(n)
+    for kind in range(4):
+        if kind == 0:
+            data = bytes(rng.randrange(256) for _ in range(n))
+        elif kind == 1:
+            data = (b"abcabcabd" * (n // 9 + 1))[:n]
+        elif kind == 2:
+            data = bytes(rng.choice(b"ab") for _ in range(n))
+        else:   # short literal runs between matches: every state value appears
+            data = b"".join(b"0123456789ABCDEF" + bytes(rng.randrange(256) for _ in range(rng.randint(0, 5))) for _ in range(n // 16 + 1))[:n]
+        cap = n + n // 16 + 64 + 3
+        out = _buf(cap)
+        m = L.uda_rt_lzo1x_compress(data, C.c_longlong(n), out, C.c_longlong(cap))
+        assert m >= 3, (n, kind, m)
+        rc, back = _lzo_dec(L, out.raw[:m], n)
+        assert rc == 0 and back == data, (n, kind)
+        if kind == 1 and n >= 1000:
+            assert m < n // 4
+
+
+def test_plumbing_lzo_compressed_segments(built, tmp_path, L):
+    """LZO map outputs through provider -> consumer without liblzo2 on the box: the built-in LZO1X decoder serves."""
+    L.uda_rt_lzo1x_compress.restype = C.c_longlong
+
+    def comp(b):
+        out = _buf(len(b) + len(b) // 16 + 80)
+        n = L.uda_rt_lzo1x_compress(bytes(b), C.c_longlong(len(b)), out, C.c_longlong(len(out)))
+        assert n > 0
+        return out.raw[:n]
+
+    streams, truth, _, _ = _run_job(str(tmp_path), 3, 2, 250, compress=comp, codec="com.hadoop.compression.lzo.LzoCodec", seed=6)
+    for r, s in enumerate(streams):
+        assert parse_stream(s) == list(kway_merge(truth[r]))
