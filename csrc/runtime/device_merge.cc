@@ -73,7 +73,11 @@ DeviceMerge::DeviceMerge() {
     const char* env = getenv("UDA_KERNELS_LIB");
     const std::string path = env && *env ? std::string(env) : dir_of_this_library() + "/libuda_kernels.so";
     lib_ = dlopen(path.c_str(), RTLD_NOW | RTLD_LOCAL);
-    if (!lib_) { why_ = std::string("cannot load ") + path + ": " + (dlerror() ? dlerror() : "?"); return; }
+    if (!lib_) {
+        const char* err = dlerror();   // a second call would return null: the message is consumed by the first
+        why_ = std::string("cannot load ") + path + ": " + (err ? err : "unknown error");
+        return;
+    }
     api_ = new Api();
     bool all = true;
     auto sym = [&](const char* n) { void* s = dlsym(lib_, n); if (!s) { all = false; why_ = std::string("missing symbol ") + n; } return s; };

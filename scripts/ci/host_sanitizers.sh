@@ -14,4 +14,13 @@ tmp="$(mktemp -d)"
 trap 'rm -rf "$tmp"' EXIT
 # the test program dlopens the library it is given: the sanitizer runtime must come first in the process
 "build/$kind/test_jni_mock" "build/$kind/libuda.so" "$tmp"
+if [ "$kind" = "address" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
+    # the whole CPU suite of the runtime (plumbing over TCP, hybrid merge, Snappy / LZO segments, approach 3 fallback)
+    # against the instrumented library: the sanitizer runtime and libstdc++ are preloaded into the Python process
+    asan_lib="$(/usr/bin/g++ -print-file-name=libasan.so)"
+    stdcpp="$(/usr/bin/g++ -print-file-name=libstdc++.so.6)"
+    UDA_B200_SKIP_BUILD=1 UDA_B200_RUNTIME_LIB="$root/build/address/libuda.so" LD_PRELOAD="$asan_lib $stdcpp" \
+        ASAN_OPTIONS="detect_leaks=0:abort_on_error=0:protect_shadow_gap=0" \
+        python -m pytest tests/test_runtime_cpu.py -x -q -p no:cacheprovider -k "not reader_bench and not regression_driver"
+fi
 echo "host sanitizer run ($kind): ok"

@@ -34,4 +34,10 @@ def built():
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
     import build as _b
 
+    if os.environ.get("UDA_B200_SKIP_BUILD"):
+        # sanitizer runs preload a runtime into this process; the compilers must not inherit it, and the libraries
+        # under test were built beforehand
+        root = _b.ROOT
+        return {"kernels": _b.LIB_DIR / "libuda_kernels.so", "runtime": _b.LIB_DIR / "libuda.so",
+                "test_jni_mock": root / "build" / "bin" / "test_jni_mock", "reader_bench": root / "build" / "bin" / "reader_bench"}
     return _b.build()

@@ -139,7 +139,7 @@ def runtime() -> C.CDLL:
     """The C++ runtime / JNI bridge library (CPU only, no CUDA dependency)."""
     global _runtime
     if _runtime is None:
-        p = lib_path("libuda.so")
+        p = Path(os.environ["UDA_B200_RUNTIME_LIB"]) if os.environ.get("UDA_B200_RUNTIME_LIB") else lib_path("libuda.so")
         if not p.exists():
             raise NativeLibraryMissing(f"{p} not found: run `python tools/build.py` first")
         _runtime = C.CDLL(str(p), mode=os.RTLD_NOW)
