@@ -23,4 +23,15 @@ if [ "$kind" = "address" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
         ASAN_OPTIONS="detect_leaks=0:abort_on_error=0:protect_shadow_gap=0" \
         python -m pytest tests/test_runtime_cpu.py -x -q -p no:cacheprovider -k "not reader_bench and not regression_driver"
 fi
+if [ "$kind" = "thread" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
+    # the multi-threaded part of the suite (provider, consumers, transport, hybrid merge, decompression) under TSAN
+    tsan_lib="$(/usr/bin/g++ -print-file-name=libtsan.so)"
+    stdcpp="$(/usr/bin/g++ -print-file-name=libstdc++.so.6)"
+    log="$(mktemp)"
+    UDA_KERNELS_LIB=/nonexistent.so UDA_B200_SKIP_BUILD=1 UDA_B200_RUNTIME_LIB="$root/build/thread/libuda.so" LD_PRELOAD="$tsan_lib $stdcpp" \
+        TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0" \
+        python -m pytest tests/test_runtime_cpu.py -x -q -p no:cacheprovider -k "plumbing or queues or thread_wrapper" > "$log" 2>&1 || { tail -30 "$log"; exit 1; }
+    tail -1 "$log"
+    if grep -q "WARNING: ThreadSanitizer" "$log"; then grep "SUMMARY: ThreadSanitizer" "$log" | sort | uniq -c; exit 1; fi
+fi
 echo "host sanitizer run ($kind): ok"
