@@ -21,7 +21,7 @@ if [ "$kind" = "address" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
     stdcpp="$(/usr/bin/g++ -print-file-name=libstdc++.so.6)"
     UDA_B200_SKIP_BUILD=1 UDA_B200_RUNTIME_LIB="$root/build/address/libuda.so" LD_PRELOAD="$asan_lib $stdcpp" \
         ASAN_OPTIONS="detect_leaks=0:abort_on_error=0:protect_shadow_gap=0" \
-        python -m pytest tests/test_runtime_cpu.py -x -q -p no:cacheprovider -k "not reader_bench and not regression_driver"
+        python -m pytest tests/test_runtime_cpu.py tests/test_fuzz_cpu.py -x -q -p no:cacheprovider -k "not reader_bench and not regression_driver"
 fi
 if [ "$kind" = "thread" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
     # the multi-threaded part of the suite (provider, consumers, transport, hybrid merge, decompression) under TSAN

@@ -1,0 +1,89 @@
+"""Property / fuzz tests of the host runtime's parsers and decoders (hypothesis): arbitrary and mutated inputs must be
+rejected or decoded, never crash. `scripts/ci/host_sanitizers.sh address` runs the same tests against the ASAN build,
+where an out-of-bounds access is a failure rather than luck."""
+import ctypes as C
+import random
+
+import pytest
+from hypothesis import HealthCheck, given, settings
+from hypothesis import strategies as st
+
+from uda_b200 import bridge
+
+FUZZ = settings(max_examples=300, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+
+
+@pytest.fixture(scope="module")
+def L(built):
+    """A private handle of the runtime library: its functions carry no argtypes, so raw ctypes arrays can be passed."""
+    import os
+    from uda_b200 import _lib
+    bridge.lib()   # makes sure the library loads the regular way first
+    path = os.environ.get("UDA_B200_RUNTIME_LIB") or str(_lib.lib_path("libuda.so"))
+    lib = C.CDLL(path)
+    lib.uda_rt_snappy_compress.restype = C.c_longlong
+    lib.uda_rt_lzo1x_compress.restype = C.c_longlong
+    return lib
+
+
+def _exact(data: bytes):
+    """A heap buffer of exactly len(data) bytes, so that a read past the end is visible to a sanitizer."""
+    return (C.c_ubyte * max(len(data), 1)).from_buffer_copy(data if data else b"\0"), len(data)
+
+
+@FUZZ
+@given(data=st.binary(max_size=600), out_len=st.integers(0, 2000))
+def test_snappy_decoder_never_crashes(L, data, out_len):
+    buf, n = _exact(data)
+    out = (C.c_ubyte * max(out_len, 1))()
+    assert L.uda_rt_snappy_uncompress(buf, C.c_longlong(n), out, C.c_longlong(out_len)) in (0, -1)
+
+
+@FUZZ
+@given(data=st.binary(max_size=600), out_len=st.integers(0, 2000))
+def test_lzo_decoder_never_crashes(L, data, out_len):
+    buf, n = _exact(data)
+    out = (C.c_ubyte * max(out_len, 1))()
+    assert L.uda_rt_lzo1x_decompress(buf, C.c_longlong(n), out, C.c_longlong(out_len)) in (0, -1)
+
+
+@FUZZ
+@given(seed=st.integers(0, 10**6), flips=st.integers(1, 6), codec=st.sampled_from(["snappy", "lzo"]))
+def test_mutated_compressed_streams(L, seed, flips, codec):
+    rng = random.Random(seed)
+    plain = b"".join(rng.choice([b"shuffle", b"merge", b"segment", bytes([rng.randrange(256)])]) for _ in range(rng.randint(1, 300)))
+    cap = len(plain) + len(plain) // 6 + 80
+    comp = (C.c_ubyte * cap)()
+    fn = L.uda_rt_snappy_compress if codec == "snappy" else L.uda_rt_lzo1x_compress
+    m = fn(plain, C.c_longlong(len(plain)), comp, C.c_longlong(cap))
+    assert m > 0
+    stream = bytearray(bytes(comp)[:m])
+    dec = L.uda_rt_snappy_uncompress if codec == "snappy" else L.uda_rt_lzo1x_decompress
+    out = (C.c_ubyte * max(len(plain), 1))()
+    buf, n = _exact(bytes(stream))
+    assert dec(buf, C.c_longlong(n), out, C.c_longlong(len(plain))) == 0 and bytes(out)[:len(plain)] == plain
+    for _ in range(flips):
+        stream[rng.randrange(len(stream))] ^= 1 << rng.randrange(8)
+    cut = rng.randint(0, len(stream))
+    for s in (bytes(stream), bytes(stream[:cut])):
+        buf, n = _exact(s)
+        assert dec(buf, C.c_longlong(n), out, C.c_longlong(len(plain))) in (0, -1)
+
+
+@FUZZ
+@given(text=st.text(alphabet=st.characters(min_codepoint=32, max_codepoint=126), max_size=200))
+def test_text_protocol_parsers_never_crash(L, text):
+    out = C.create_string_buffer(4096)
+    s = text.encode()
+    L.uda_rt_parse_cmd(s, out, len(out))
+    L.uda_rt_fetch_request_roundtrip(s, out, len(out))
+    L.uda_rt_fetch_ack_roundtrip(s, out, len(out))
+
+
+@FUZZ
+@given(data=st.binary(min_size=0, max_size=12))
+def test_vint_decoder_bounds(L, data):
+    buf, n = _exact(data)
+    got = C.c_longlong()
+    r = L.uda_rt_vint_decode(buf, n, C.byref(got))
+    assert 0 <= r <= max(n, 0) and r <= 9
