@@ -52,3 +52,67 @@ def test_push_descs_cover_everything_and_rotate_peers():
     rd, off, base, nbytes = plan.run_descs(1, 7_000_000)
     assert off[-1] == rd["nrec"].sum() and (base == 7_000_000 + plan.layouts[1].run_offsets).all()
     assert (nbytes == plan.layouts[1].run_bytes).all()
+
+
+def _var_index(world, maps, seed=0):
+    """Index tables with arbitrary (non-stride) segment sizes, 16-byte aligned starts."""
+    rng = np.random.RandomState(seed)
+    idx = np.zeros((world, maps, world, 3), dtype=np.int64)
+    for s in range(world):
+        for m in range(maps):
+            cur = 0
+            for p in range(world):
+                body = int(rng.randint(0, 5000))
+                idx[s, m, p] = (cur, body + 2, body + 6)
+                cur = (cur + body + 6 + 15) // 16 * 16
+    return idx
+
+
+def test_variable_length_plan_and_sub_partitions():
+    """stride 0 = variable-length job: no record counts, byte-exact coverage; sub-partitions share one arena and
+    every (sub, run) owns its own landed-byte counter slot."""
+    world, maps, C = 3, 2, 4
+    rng = np.random.RandomState(5)
+    idx = np.zeros((world, maps, world * C, 3), dtype=np.int64)
+    for s in range(world):
+        for m in range(maps):
+            cur = 0
+            for lp in range(world * C):
+                body = int(rng.randint(0, 3000))
+                idx[s, m, lp] = (cur, body + 2, body + 6)
+                cur = (cur + body + 6 + 15) // 16 * 16
+    plan = ShufflePlan(idx, record_stride=0, subparts=C)
+    assert plan.P == world and plan.nruns == world * maps and len(plan.layouts) == world * C
+    for r in range(world):
+        spans = []
+        for j in range(C):
+            lay = plan.layout(r, j)
+            assert (lay.run_nrec == -1).all()
+            for rid in range(plan.nruns):
+                spans.append((int(lay.run_offsets[rid]), int(lay.run_offsets[rid] + lay.run_bytes[rid])))
+        spans.sort()
+        assert all(a[1] <= b[0] for a, b in zip(spans, spans[1:]))          # nothing overlaps inside the arena
+        assert spans[-1][1] + 32 <= plan.arena_bytes[r]
+    flags = set()
+    total = 0
+    for j in range(C):
+        d = plan.push_descs(0, [1 << 20, 2 << 20], [10 << 20, 20 << 20, 30 << 20], [1 << 30, 2 << 30, 3 << 30], j)
+        total += int(d["bytes"].sum())
+        flags |= {int(f) for f in d["flag"]}
+        # the descriptors addressed to the rank itself come last: that is what local_zero_copy relies on
+        assert all(int(x) // (10 << 20) == 1 for x in d["dst"][-maps:])
+    assert total == int(idx[0, :, :, 2].sum()) and len(flags) == C * world * maps
+
+
+def test_plan_is_identical_on_every_rank():
+    """Every rank derives layouts and peer offsets from the same all-gathered tables: no addresses are exchanged."""
+    idx = _var_index(4, 3, seed=9)
+    a, b = ShufflePlan(idx.copy(), 0), ShufflePlan(idx.copy(), 0)
+    assert a.arena_bytes == b.arena_bytes
+    for la, lb in zip(a.layouts, b.layouts):
+        assert (la.run_offsets == lb.run_offsets).all() and (la.run_bytes == lb.run_bytes).all()
+    # what rank 2 pushes to rank 1 lands exactly where rank 1 expects run (2, m)
+    d = a.push_descs(2, [0, 0, 0], [0, 1 << 32, 0, 0], [0, 0, 0, 0])
+    to1 = [x for x in d if int(x["dst"]) >> 32 == 1]
+    lay1 = b.layout(1)
+    assert sorted(int(x["dst"]) - (1 << 32) for x in to1) == sorted(int(lay1.run_offsets[a.run_id(2, m)]) for m in range(3))
