@@ -437,3 +437,13 @@ def test_plumbing_lzo_compressed_segments(built, tmp_path, L):
     streams, truth, _, _ = _run_job(str(tmp_path), 3, 2, 250, compress=comp, codec="com.hadoop.compression.lzo.LzoCodec", seed=6)
     for r, s in enumerate(streams):
         assert parse_stream(s) == list(kway_merge(truth[r]))
+
+
+@pytest.mark.parametrize("approach", [1, 2])
+def test_example_fake_hadoop_plumbing(built, approach):
+    import subprocess, sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    p = subprocess.run([sys.executable, str(root / "examples" / "fake_hadoop_plumbing.py"), "--approach", str(approach)],
+                       capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0 and p.stdout.strip().endswith("OK"), p.stdout + p.stderr
