@@ -100,3 +100,22 @@ def test_affinity_helper_is_safe_without_a_gpu():
     before = os.sched_getaffinity(0)
     info = bind_to_gpu_numa(0)
     assert info["bound"] is False and os.sched_getaffinity(0) == before
+
+
+def test_log_collector_and_pre_req(tmp_path):
+    """utils/job_log_collector.py keeps the lines post-mortems need; scripts/regression/pre_req.py reports the host state."""
+    import json, subprocess, sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    (tmp_path / "stdout.log").write_text('noise\nUDA version is b200-1.0.1\n{"metric": "x", "value": 1}\nmore noise\n')
+    (tmp_path / "stderr.log").write_text("blah\nUDA has encountered a critical error and will try to fallback to vanilla MSG=x\nTraceback (most recent call last):\n")
+    out = tmp_path / "collected.log"
+    p = subprocess.run([sys.executable, str(root / "utils" / "job_log_collector.py"), "--dir", str(tmp_path), "--out", str(out), "--log-dirs", str(tmp_path)],
+                       capture_output=True, text=True, timeout=60)
+    assert p.returncode == 0
+    text = out.read_text()
+    assert "UDA version is" in text and "fallback" in text and '"metric"' in text and "Traceback" in text and "noise" not in text
+    q = subprocess.run([sys.executable, str(root / "scripts" / "regression" / "pre_req.py"), "--json", "--min-free-ram-gb", "0.001", "--min-free-disk-gb", "0.001"],
+                       capture_output=True, text=True, timeout=60)
+    r = json.loads(q.stdout)
+    assert q.returncode == 0 and r["failed"] == [] and r["cpus"] >= 1 and r["dir_writable"] is True
