@@ -119,3 +119,12 @@ def test_log_collector_and_pre_req(tmp_path):
                        capture_output=True, text=True, timeout=60)
     r = json.loads(q.stdout)
     assert q.returncode == 0 and r["failed"] == [] and r["cpus"] >= 1 and r["dir_writable"] is True
+
+
+def test_job_kwargs_from_config():
+    c = UdaConfig()
+    assert c.terasort_job_kwargs(1) == {"subparts": 1, "push_mode": "lsu", "push_ctas": 0, "merge_ctas_per_sm": 0}
+    assert c.terasort_job_kwargs(2) == {"subparts": 8, "push_mode": "tma", "push_ctas": 32, "merge_ctas_per_sm": 0}
+    assert c.terasort_job_kwargs(8)["subparts"] == 12 and c.terasort_job_kwargs(8)["push_ctas"] == 36
+    c2 = UdaConfig.from_dict({"uda.b200.shuffle.subpartitions": 4, "uda.b200.shuffle.push.ctas": 24})
+    assert c2.terasort_job_kwargs(8) == {"subparts": 4, "push_mode": "tma", "push_ctas": 24, "merge_ctas_per_sm": 0}

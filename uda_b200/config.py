@@ -91,7 +91,7 @@ class UdaConfig:
     map_output_key_class: str = "org.apache.hadoop.io.Text"
     child_java_opts: str = "-Xmx200m"
     hbm_budget_bytes: int = 0               # 0 -> 80 % of the free HBM at job set-up
-    subparts: int = 0                       # 0 -> 1 on one GPU, 4 on several
+    subparts: int = 0                       # 0 -> 1 on one GPU, 8 on two, 12 on more
     push_ctas: int = 0                      # 0 -> library default
     merge_ctas_per_sm: int = 0
     verify_crc: bool = False
@@ -199,6 +199,16 @@ class UdaConfig:
         return [str(num_maps), job_id, reduce_attempt_id, str(self.hybrid_lpq_size), str(self.buf_size_kb * 1024),
                 str(self.buf_size_min_kb * 1024), self.map_output_key_class, codec, str(self.codec_block_size()),
                 str(self.shuffle_memory_bytes()), str(len(dirs)), *dirs]
+
+    def terasort_job_kwargs(self, world: int) -> Dict[str, object]:
+        """Keyword arguments for :class:`uda_b200.models.terasort.TeraSortJob` derived from the ``uda.b200.*`` keys:
+        zeros mean "measured default for this many GPUs" (one GPU: load/store push, no pipelining; two: copy-engine
+        push on 32 SMs, 8 sub-partitions; more: 36 SMs, 12 sub-partitions — profiles/pipeline_sweep.md)."""
+        multi = world > 1
+        subparts = self.subparts if self.subparts > 0 else ((12 if world > 2 else 8) if multi else 1)
+        mode = "tma" if multi and subparts > 1 else "lsu"
+        ctas = self.push_ctas if self.push_ctas > 0 else ((36 if world > 2 else 32) if mode == "tma" else 0)
+        return {"subparts": subparts, "push_mode": mode, "push_ctas": ctas, "merge_ctas_per_sm": self.merge_ctas_per_sm}
 
     def replace(self, **kw) -> "UdaConfig":
         c = dataclasses.replace(self, **kw)
