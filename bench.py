@@ -145,9 +145,7 @@ def main():
         affinity = bind_to_gpu_numa(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if not os.environ.get("UDA_KEEP_NCCL_DEBUG"):
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=dev)   # NCCL's own log level is left to the caller (fd 1 is parked above)
 
     def barrier():
         if world > 1:
@@ -176,14 +174,11 @@ def main():
         a.subparts = (12 if world > 2 else 8) if world > 1 else 1   # 2 GPUs: 8 / 32 measured 3 % better than 12 / 36
     if a.push_ctas < 0:
         a.push_ctas = ((36 if world > 2 else 32) if a.push_mode == "tma" else 296) if a.subparts > 1 else 0
-    if a.tma_flush > 0:
-        from uda_b200._lib import check, kernels
-        check(kernels().uda_shuffle_push_tma_set_flush(a.tma_flush), "uda_shuffle_push_tma_set_flush")
     if a.impl == "nccl_sort":
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev).setup()
     else:
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev, subparts=a.subparts, push_ctas=a.push_ctas,
-                  merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode, local_zero_copy=a.local_zero_copy).setup()
+                  merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode, local_zero_copy=a.local_zero_copy, tma_flush=a.tma_flush).setup()
     total_bytes = float(a.records_per_gpu) * RECORD_BYTES * world
 
     def timed(fn, steps, warmup, sample_clocks):

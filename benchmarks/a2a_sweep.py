@@ -38,7 +38,6 @@ def main():
     send = torch.randint(0, 255, (P * smax,), dtype=torch.uint8, device=dev)
     recv_nccl = torch.empty_like(send)
     status = arena.status
-    K.shuffle_push_set_interleave(P)
     for S in sizes:
         d = np.zeros(P, dtype=K.PUSH_DESC_DTYPE)
         for i in range(P):
@@ -52,7 +51,7 @@ def main():
         for ctas in [int(c) for c in a.ctas.split(",")]:
             def push():
                 arena.barrier()
-                K.shuffle_push(descs, P, scratch, ctas)
+                K.shuffle_push(descs, P, scratch, ctas, P)
                 expect.add_(step)
                 K.wait_flags(arena.flags(), expect, P, status)
             for _ in range(3):

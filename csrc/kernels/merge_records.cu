@@ -16,28 +16,29 @@
 //                        for small k and with overwhelming probability for large k; oversize buckets take the
 //                        bisection path below.
 //   5. fr_merge        : per bucket, TMA bulk copies (cp.async.bulk, mbarrier expect_tx/complete_tx) land the
-//                        k record slices in shared memory; 16-byte entries (key prefix, slot) are built from
-//                        the staged records; the pairwise merge-path tree orders them; records leave shared
-//                        memory in merged order as coalesced stores straight to their final position.
+//                        k record slices in shared memory. The tile is then ORDERED IN O(1) PASSES, independent
+//                        of k: every staged record is dropped into one of FR_NBIN equal-width key bins of the
+//                        bucket's key range (a monotone map, so bins are ordered), a shared-memory counting pass
+//                        + scan gives each bin its output range, and the few records that share a bin are ranked
+//                        exactly against each other on (80-bit key, slot). Buckets are ~400 records wide, so for
+//                        any smooth key distribution a bin holds < 1 record on average. Tiles whose keys pile up
+//                        in one bin (duplicate-heavy data) fall back to the pairwise merge-path tree (one
+//                        block-wide level per log2 k). Records leave shared memory in merged order as coalesced
+//                        16-byte stores straight to their final position.
 //
 // Output order is (key, run, index-in-run), identical to merge.cu + gather.cu.
 #include "common.cuh"
 #include "merge_tree.cuh"
 #include "scan.cuh"
 #include "../../include/uda_b200.h"
+#include <cstdlib>
 
 namespace uda {
 
-// Tuning (measured on B200, 125 M records, k = 8; ms per TeraSort step incl. the 4.4 ms push):
+// Tuning history (B200, 125 M records, k = 8; ms per TeraSort step incl. the 4.4 ms push), tree ordering:
 //   VT=3 / 2 CTAs per SM 13.95   VT=2 / 3 CTAs 13.53   VT=4 / 1 CTA 17.76   VT=2 / 3 CTAs, 128 merge threads 13.91
 #ifndef UDA_FR_VT
 #define UDA_FR_VT 2
-#endif
-#ifndef UDA_FR_OUT32
-#define UDA_FR_OUT32 0   // measured: 9.23 ms vs 8.95 ms for the 16-byte path on the 125 M record merge
-#endif
-#ifndef UDA_FR_MERGE_THREADS
-#define UDA_FR_MERGE_THREADS UDA_FR_THREADS
 #endif
 #ifndef UDA_FR_CTAS
 #define UDA_FR_CTAS 3
@@ -45,22 +46,33 @@ namespace uda {
 #ifndef UDA_FR_THREADS
 #define UDA_FR_THREADS 256
 #endif
+#ifndef UDA_FR_MERGE_THREADS
+#define UDA_FR_MERGE_THREADS UDA_FR_THREADS
+#endif
+#ifndef UDA_FR_BIN_LIMIT
+#define UDA_FR_BIN_LIMIT 48   // records in one key bin beyond which a tile is ordered by the merge tree instead
+#endif
 constexpr int FR_THREADS = UDA_FR_THREADS;
 constexpr int FR_VT = UDA_FR_VT;
-constexpr int FR_TILE = FR_THREADS * FR_VT;  // record slots per tile (512 by default)
+constexpr int FR_TILE = FR_THREADS * FR_VT;  // largest tile capacity in record slots (512); the capacity in use is a launch parameter
+constexpr int FR_CAP_MIN = 128;              // smallest capacity the host ever picks (bounds the scratch size)
 constexpr int FR_MERGE_THREADS = UDA_FR_MERGE_THREADS;   // threads that run the merge tree (fewer = more items per thread)
 constexpr int FR_MERGE_VT = FR_TILE / FR_MERGE_THREADS;
-constexpr int FR_TARGET = FR_TILE * 3 / 4;   // target bucket size: a quarter of the tile absorbs the sampling error
+constexpr int FR_NBIN = 2 * FR_THREADS;      // key bins per tile: two per thread in the scan
+constexpr int FR_BIN_LIMIT = UDA_FR_BIN_LIMIT;
 constexpr int FR_SAMPLE = 8;
 constexpr int FR_NB_LOG = 22;
 constexpr int FR_NB = 1 << FR_NB_LOG;
 constexpr int FR_KMAX = 1024;
 constexpr int FR_SLICE_PAD = 48;             // bytes of shared memory reserved per run for 16-byte alignment slop
+// target bucket size for a tile capacity: a quarter of the tile absorbs the sampling error
+__host__ __device__ inline int fr_target(int cap) { return cap * 3 / 4; }
 
 struct FrParams {
     unsigned long long kmin, kmax;
     int shift, pad;
     unsigned long long fallback_buckets, fallback_iters;
+    unsigned long long tree_tiles;    // tiles ordered by the merge tree instead of the key bins
     unsigned int next_bucket, pad2;   // dynamic bucket scheduler of fr_merge_kernel (reset by fr_range_kernel)
 };
 
@@ -121,7 +133,7 @@ __global__ void fr_range_kernel(const UdaRunDesc* __restrict__ runs, int k, int 
         int shift = 0;
         while (shift < 64 && (range >> shift) >= (unsigned long long)FR_NB) ++shift;
         prm->kmin = lo; prm->kmax = hi; prm->shift = shift;
-        prm->fallback_buckets = 0; prm->fallback_iters = 0;
+        prm->fallback_buckets = 0; prm->fallback_iters = 0; prm->tree_tiles = 0;
         prm->next_bucket = 0;
     }
 }
@@ -147,10 +159,10 @@ __global__ void fr_sample_hist_kernel(const UdaRunDesc* __restrict__ runs, int s
 // ------------------------------------------------------------------------------------------- 3
 // boundary key of every bucket: bkey[q] = first key of bucket q (w0 only, tail 0); kind[q]: 0 = start of the
 // run (q == 0), 1 = search for bkey[q], 2 = end of the run (past the last sample / q == G)
-__global__ void fr_bkeys_kernel(int G, const uint32_t* __restrict__ cum, const FrParams* __restrict__ prm,
+__global__ void fr_bkeys_kernel(int G, int per, const uint32_t* __restrict__ cum, const FrParams* __restrict__ prm,
                                 unsigned long long* __restrict__ bkey, uint8_t* __restrict__ kind) {
     for (int q = blockIdx.x * blockDim.x + threadIdx.x; q <= G; q += gridDim.x * blockDim.x) {
-        const unsigned long long want = (unsigned long long)q * (FR_TARGET / FR_SAMPLE);
+        const unsigned long long want = (unsigned long long)q * (unsigned long long)per;
         int lo = 0, hi = FR_NB;
         while (lo < hi) {
             int mid = (lo + hi) >> 1;
@@ -193,7 +205,7 @@ __global__ void fr_partition_search_kernel(const UdaRunDesc* __restrict__ runs, 
 // sector-sparse pass (2 ms for 125 M records) replaces (G+1)*k independent binary searches over strided
 // records, which for k = 64 dragged the whole data set through DRAM at 2 TB/s (6.3 ms). Runs that are much
 // shorter than the bucket count keep the per-boundary binary search (their gaps would serialise one thread).
-__global__ void fr_partition_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride, int key_off, int key_len,
+__global__ void fr_partition_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int per_i, int stride, int key_off, int key_len,
                                     const uint32_t* __restrict__ cum, const FrParams* __restrict__ prm,
                                     const unsigned long long* __restrict__ bkey, const uint8_t* __restrict__ kind,
                                     uint32_t* __restrict__ P) {
@@ -214,7 +226,7 @@ __global__ void fr_partition_kernel(const UdaRunDesc* __restrict__ runs, int k, 
     }
     const unsigned long long kmin = prm->kmin;
     const int shift = prm->shift;
-    const uint32_t per = FR_TARGET / FR_SAMPLE;
+    const uint32_t per = (uint32_t)per_i;
     auto bucket_of = [&](long long i) -> int {
         unsigned long long w0;
         uint32_t t;
@@ -251,116 +263,236 @@ __global__ void fr_sizes_kernel(const uint32_t* __restrict__ P, int k, int G, ui
 }
 
 // ------------------------------------------------------------------------------------------- 5
+// Shared memory of one merge CTA (`cap` = tile capacity in record slots):
+//   rec                      staged record bytes of the k slices
+//   work  (cap * 36 bytes)   bin ordering: skey[cap] u64 | sts[cap] u32 | bincnt[NBIN] | binbase[NBIN + 1]
+//                            tree ordering (fallback): entA[cap] | entB[cap] | slotaddr[cap]      (same bytes)
+//   srcaddr[cap]             byte offset inside rec of the record that goes to output position p
+//   per-run tables           lo, hi, bend, sbase [k]; soff, doff [k + 1]
 struct FrSmem {
-    uint8_t* rec;        // staged record bytes
+    uint8_t* rec;
     Entry* entA;
     Entry* entB;
-    uint32_t* slotaddr;  // [FR_TILE] byte offset of slot j's record inside rec
-    uint32_t* lo;        // [k]
-    uint32_t* hi;        // [k]
-    uint32_t* bend;      // [k]
+    uint32_t* slotaddr;
+    unsigned long long* skey;
+    uint32_t* sts;
+    uint32_t* bincnt;    // all zero between tiles
+    uint32_t* binbase;
+    uint32_t* srcaddr;
+    uint32_t* lo;
+    uint32_t* hi;
+    uint32_t* bend;
     uint32_t* sbase;     // [k] byte offset of the first record of run r's slice inside rec
     uint32_t* soff;      // [k+1] slot offsets (list boundaries for the merge tree)
     uint32_t* doff;      // [k+1]
 };
 
-__host__ __device__ inline size_t fr_smem_bytes(int k, int stride) {
-    size_t rec = ((size_t)FR_TILE * stride + (size_t)FR_SLICE_PAD * k + 64 + 15) & ~(size_t)15;
-    return rec + 2 * (size_t)FR_TILE * sizeof(Entry) + (size_t)FR_TILE * 4 + ((size_t)4 * k + 2 * ((size_t)k + 1)) * 4 + 16;
+__host__ __device__ inline size_t fr_rec_bytes(int cap, int k, int stride) {
+    return ((size_t)cap * stride + (size_t)FR_SLICE_PAD * k + 64 + 15) & ~(size_t)15;
+}
+__host__ __device__ inline size_t fr_work_bytes(int cap) {
+    const size_t tree = (size_t)cap * 36, bins = (size_t)cap * 12 + ((size_t)2 * FR_NBIN + 2) * 4;
+    return ((tree > bins ? tree : bins) + 15) & ~(size_t)15;
+}
+__host__ __device__ inline size_t fr_smem_bytes(int cap, int k, int stride) {
+    return fr_rec_bytes(cap, k, stride) + fr_work_bytes(cap) + (size_t)cap * 4 + ((size_t)4 * k + 2 * ((size_t)k + 1)) * 4 + 16;
 }
 
 __device__ __forceinline__ void mbar_expect_tx_only(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 
+// key range of one tile and the monotone key -> bin map derived from it
+struct FrBinMap {
+    unsigned long long klo, kspan;   // bins cover [klo, klo + kspan]
+};
+
 template <bool ALIGN2, int STRIDE>
 __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ runs, const FrSmem& sm, int k, int stride_rt,
-                                                int key_off, int key_len, uint32_t total, uint8_t* __restrict__ out,
-                                                uint64_t* mbar, uint32_t& phase) {
+                                                int key_off, int key_len, uint32_t total, const FrBinMap bm, int force_tree,
+                                                uint8_t* __restrict__ out, uint64_t* mbar, uint32_t& phase, uint32_t* s_ws,
+                                                uint32_t* s_flag, FrParams* __restrict__ prm) {
     const int stride = STRIDE > 0 ? STRIDE : stride_rt;
-    const int tid = threadIdx.x;
-    const int rpt = (k + FR_THREADS - 1) / FR_THREADS;
-    const int r0 = tid * rpt, r1 = min(k, r0 + rpt);
-    uint32_t mine = 0;
-    for (int r = r0; r < r1; ++r) mine += sm.hi[r] - sm.lo[r];
-    uint32_t tot;
-    uint32_t slot = block_exclusive_scan<FR_THREADS>(mine, &tot);
-    fence_proxy_async_smem();  // previous tile's generic-proxy accesses to `rec` are ordered before the TMA writes
-    for (int r = r0; r < r1; ++r) {
-        const uint32_t len = sm.hi[r] - sm.lo[r];
-        sm.soff[r] = slot;
-        const uint32_t B = ((slot * (uint32_t)stride + (uint32_t)FR_SLICE_PAD * r) + 15u) & ~15u;
-        if (len) {
-            const uint8_t* src = (const uint8_t*)runs[r].base + (unsigned long long)sm.lo[r] * stride;
-            const uint32_t mis = (uint32_t)((uintptr_t)src & 15);
-            const uint32_t nbytes = (mis + len * (uint32_t)stride + 15u) & ~15u;
-            sm.sbase[r] = B + mis;
-            mbar_expect_tx_only(mbar, nbytes);
-            tma_load_1d(sm.rec + B, src - mis, nbytes, mbar);
-        } else {
-            sm.sbase[r] = B;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // ---- stage the k slices: warp 0 lays them out (slot offsets by a shuffle scan, 32 runs at a time) and issues one
+    //      bulk copy per non-empty slice; everybody then waits on the mbarrier. No block-wide barrier in this phase.
+    if (warp == 0) {
+        fence_proxy_async_smem();  // previous tile's generic-proxy accesses to `rec` are ordered before the TMA writes
+        uint32_t run_slot = 0;
+        for (int r0 = 0; r0 < k; r0 += 32) {
+            const int r = r0 + lane;
+            const uint32_t lo = r < k ? sm.lo[r] : 0u;
+            const uint32_t len = r < k ? sm.hi[r] - lo : 0u;
+            uint32_t x = len;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+                if (lane >= o) x += y;
+            }
+            const uint32_t slot = run_slot + x - len;
+            if (r < k) {
+                sm.soff[r] = slot;
+                const uint32_t B = ((slot * (uint32_t)stride + (uint32_t)FR_SLICE_PAD * r) + 15u) & ~15u;
+                if (len) {
+                    const uint8_t* src = (const uint8_t*)runs[r].base + (unsigned long long)lo * stride;
+                    const uint32_t mis = (uint32_t)((uintptr_t)src & 15);
+                    const uint32_t nbytes = (mis + len * (uint32_t)stride + 15u) & ~15u;
+                    sm.sbase[r] = B + mis;
+                    mbar_expect_tx_only(mbar, nbytes);
+                    tma_load_1d(sm.rec + B, src - mis, nbytes, mbar);
+                } else {
+                    sm.sbase[r] = B;
+                }
+            }
+            run_slot += __shfl_sync(0xffffffffu, x, 31);
         }
-        slot += len;
+        if (lane == 0) { sm.soff[k] = total; *s_flag = (uint32_t)force_tree; }
+        __syncwarp();                      // every expect_tx and table store precedes the single arrival
+        if (lane == 0) mbar_arrive(mbar);
     }
-    if (tid == 0) sm.soff[k] = total;
-    __syncthreads();               // every expect_tx precedes the single arrival
-    if (tid == 0) mbar_arrive(mbar);
-    mbar_wait(mbar, phase);
+    mbar_wait(mbar, phase);                // acquire: the tables written by warp 0 are visible too
     phase ^= 1u;
 
-    // entries from the staged records
-    for (uint32_t j = tid; j < total; j += FR_THREADS) {
-        int lo = 0, hi = k - 1;  // run owning slot j: last r with soff[r] <= j
-        while (lo < hi) {
-            int mid = (lo + hi + 1) >> 1;
-            if (sm.soff[mid] <= j) lo = mid; else hi = mid - 1;
+    // ---- A: key of every staged record -> bin, position inside the bin by a shared-memory atomic
+    const int bits = 64 - __clzll((long long)bm.kspan);
+    const int sh = bits > 32 ? bits - 32 : 0;
+    const float scale = (float)FR_NBIN / (__uint2float_rz((uint32_t)(bm.kspan >> sh)) + 1.0f);
+    unsigned long long kw0[FR_VT];
+    uint32_t kts[FR_VT], kaddr[FR_VT], kbin[FR_VT];
+#pragma unroll
+    for (int v = 0; v < FR_VT; ++v) {
+        const uint32_t j = (uint32_t)tid + (uint32_t)v * FR_THREADS;
+        kw0[v] = 0; kts[v] = 0; kaddr[v] = 0; kbin[v] = 0;
+        if (j < total) {
+            int lo = 0, hi = k - 1;  // run owning slot j: last r with soff[r] <= j
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (sm.soff[mid] <= j) lo = mid; else hi = mid - 1;
+            }
+            const uint32_t addr = sm.sbase[lo] + (j - sm.soff[lo]) * (uint32_t)stride;
+            const uint8_t* kp = sm.rec + addr + key_off;
+            unsigned long long w0 = 0;
+            uint32_t t = 0;
+            if (ALIGN2 && key_len == 10) {
+                const uint16_t* h = reinterpret_cast<const uint16_t*>(kp);
+                const uint32_t h0 = h[0], h1 = h[1], h2 = h[2], h3 = h[3], h4 = h[4];
+                // bytes are big-endian key digits; each little-endian half holds (b0 | b1 << 8)
+                auto sw = [](uint32_t x) { return ((x & 0xFFu) << 8) | (x >> 8); };
+                w0 = ((unsigned long long)sw(h0) << 48) | ((unsigned long long)sw(h1) << 32) | ((unsigned long long)sw(h2) << 16) | sw(h3);
+                t = sw(h4);
+            } else {
+                key_prefix(kp, key_len, &w0, &t);
+            }
+            unsigned long long rel = w0 > bm.klo ? w0 - bm.klo : 0ull;
+            if (rel > bm.kspan) rel = bm.kspan;
+            uint32_t b = __float2uint_rz(__uint2float_rz((uint32_t)(rel >> sh)) * scale);   // monotone in the key
+            b = b < (uint32_t)FR_NBIN - 1u ? b : (uint32_t)FR_NBIN - 1u;
+            const uint32_t o = atomicAdd(&sm.bincnt[b], 1u);
+            kw0[v] = w0; kts[v] = (t << 16) | j; kaddr[v] = addr; kbin[v] = b | (o << 16);
         }
-        const uint32_t addr = sm.sbase[lo] + (j - sm.soff[lo]) * (uint32_t)stride;
-        const uint8_t* kp = sm.rec + addr + key_off;
-        unsigned long long w0 = 0;
-        uint32_t t = 0;
-        if (ALIGN2 && key_len == 10) {
-            const uint16_t* h = reinterpret_cast<const uint16_t*>(kp);
-            const uint32_t h0 = h[0], h1 = h[1], h2 = h[2], h3 = h[3], h4 = h[4];
-            // bytes are big-endian key digits; each little-endian half holds (b0 | b1 << 8)
-            auto sw = [](uint32_t x) { return ((x & 0xFFu) << 8) | (x >> 8); };
-            w0 = ((unsigned long long)sw(h0) << 48) | ((unsigned long long)sw(h1) << 32) | ((unsigned long long)sw(h2) << 16) | sw(h3);
-            t = sw(h4);
-        } else {
-            key_prefix(kp, key_len, &w0, &t);
-        }
-        Entry e;
-        e.w0 = w0;
-        e.w1 = ((unsigned long long)t << 48) | j;
-        sm.entA[j] = e;
-        sm.slotaddr[j] = addr;
     }
     __syncthreads();
 
-    Entry* src = sm.entA; Entry* dst = sm.entB;
-    uint32_t* soff = sm.soff; uint32_t* doff = sm.doff;
-    int L = k;
-    while (L > 1) {
-        if (tid < FR_MERGE_THREADS) merge_level<FR_MERGE_THREADS, FR_MERGE_VT>(src, soff, L, dst, doff, total);
+    // ---- B: exclusive scan of the bin counts (two bins per thread); the counters go back to zero for the next tile
+    {
+        const uint2 c = *reinterpret_cast<const uint2*>(&sm.bincnt[2 * tid]);
+        *reinterpret_cast<uint2*>(&sm.bincnt[2 * tid]) = make_uint2(0u, 0u);
+        const uint32_t s2 = c.x + c.y;
+        uint32_t x = s2;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) s_ws[warp] = x;
+        if ((c.x > (uint32_t)FR_BIN_LIMIT) | (c.y > (uint32_t)FR_BIN_LIMIT)) *s_flag = 1u;
         __syncthreads();
-        Entry* te = src; src = dst; dst = te;
-        uint32_t* tu = soff; soff = doff; doff = tu;
-        L = (L + 1) >> 1;
+        uint32_t wp = lane < warp ? s_ws[lane] : 0u;   // FR_THREADS / 32 <= 32 warps
+#pragma unroll
+        for (int o = 16; o; o >>= 1) wp += __shfl_xor_sync(0xffffffffu, wp, o);
+        const uint32_t e = wp + x - s2;
+        sm.binbase[2 * tid] = e;
+        sm.binbase[2 * tid + 1] = e + c.x;
+        if (tid == FR_THREADS - 1) sm.binbase[FR_NBIN] = e + s2;
+    }
+    __syncthreads();
+
+    if (*s_flag == 0u) {
+        // ---- C: a record alone in its bin knows its output position; the others are staged by bin
+        uint32_t b0[FR_VT], cn[FR_VT];
+#pragma unroll
+        for (int v = 0; v < FR_VT; ++v) {
+            const uint32_t j = (uint32_t)tid + (uint32_t)v * FR_THREADS;
+            b0[v] = 0; cn[v] = 0;
+            if (j < total) {
+                const uint32_t b = kbin[v] & 0xFFFFu, o = kbin[v] >> 16;
+                b0[v] = sm.binbase[b];
+                cn[v] = sm.binbase[b + 1] - b0[v];
+                if (cn[v] == 1u) sm.srcaddr[b0[v]] = kaddr[v];
+                else { sm.skey[b0[v] + o] = kw0[v]; sm.sts[b0[v] + o] = kts[v]; }
+            }
+        }
+        __syncthreads();
+        // ---- D: exact rank among the records of the same bin on (key, tail, slot); slots are run-major, so equal
+        //         keys come out in (run, index) order
+#pragma unroll
+        for (int v = 0; v < FR_VT; ++v) {
+            if (cn[v] > 1u) {
+                uint32_t rank = 0;
+                for (uint32_t i = 0; i < cn[v]; ++i) {
+                    const unsigned long long a = sm.skey[b0[v] + i];
+                    const uint32_t bt = sm.sts[b0[v] + i];
+                    rank += (a < kw0[v]) || (a == kw0[v] && bt < kts[v]) ? 1u : 0u;
+                }
+                sm.srcaddr[b0[v] + rank] = kaddr[v];
+            }
+        }
+        __syncthreads();
+    } else {
+        // ---- fallback: many records share a key bin (duplicate-heavy keys). Pairwise merge-path tree over 16-byte
+        //      entries, one block-wide level per log2 k.
+        if (tid == 0) atomicAdd(&prm->tree_tiles, 1ull);
+        __syncthreads();               // nobody reads binbase / bincnt any more: the work area becomes entA | entB | slotaddr
+#pragma unroll
+        for (int v = 0; v < FR_VT; ++v) {
+            const uint32_t j = (uint32_t)tid + (uint32_t)v * FR_THREADS;
+            if (j < total) {
+                Entry e;
+                e.w0 = kw0[v];
+                e.w1 = ((unsigned long long)(kts[v] >> 16) << 48) | j;
+                sm.entA[j] = e;
+                sm.slotaddr[j] = kaddr[v];
+            }
+        }
+        __syncthreads();
+        Entry* src = sm.entA; Entry* dst = sm.entB;
+        uint32_t* soff = sm.soff; uint32_t* doff = sm.doff;
+        int L = k;
+        while (L > 1) {
+            if (tid < FR_MERGE_THREADS) merge_level<FR_MERGE_THREADS, FR_MERGE_VT>(src, soff, L, dst, doff, total);
+            __syncthreads();
+            Entry* te = src; src = dst; dst = te;
+            uint32_t* tu = soff; soff = doff; doff = tu;
+            L = (L + 1) >> 1;
+        }
+        for (uint32_t p = tid; p < total; p += FR_THREADS) sm.srcaddr[p] = sm.slotaddr[(uint32_t)src[p].w1 & 0xFFFFu];
+        __syncthreads();
+        for (int b = tid; b < FR_NBIN; b += FR_THREADS) sm.bincnt[b] = 0u;   // restore the invariant the bin path relies on
     }
 
-    // Records leave in merged order. One thread per 16-byte *destination* word (all 32 lanes busy, the
+    // ---- E: records leave in merged order. One thread per 16-byte *destination* word (all 32 lanes busy, the
     // per-record work is amortised over the lanes): the word's bytes come from at most two staged records at
     // arbitrary (even) shared-memory offsets, each fetched as aligned 32-bit shared loads + funnel shifts.
     // Shared-space addresses are explicit so the loads are LDS, not generic LD.
-    const uint32_t rec_s = smem_u32(sm.rec), ent_s = smem_u32(src), slot_s = smem_u32(sm.slotaddr);
+    const uint32_t rec_s = smem_u32(sm.rec), sa_s = smem_u32(sm.srcaddr);
     auto slot_addr = [&](uint32_t p) -> uint32_t {  // shared address of merged record p
-        uint32_t j, sa;
-        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(j) : "r"(ent_s + p * 16u + 8u));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sa) : "r"(slot_s + j * 4u));
+        uint32_t sa;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sa) : "r"(sa_s + p * 4u));
         return rec_s + sa;
     };
     auto lds16 = [](uint32_t a) -> uint4 {  // 16 bytes at arbitrary shared address a
-        const uint32_t w = a & ~3u, sh = (a & 3u) * 8u;
+        const uint32_t w = a & ~3u, sh8 = (a & 3u) * 8u;
         uint32_t x0, x1, x2, x3, x4;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(x0) : "r"(w));
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(x1) : "r"(w + 4u));
@@ -368,8 +500,8 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(x3) : "r"(w + 12u));
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(x4) : "r"(w + 16u));
         uint4 r;
-        r.x = __funnelshift_r(x0, x1, sh); r.y = __funnelshift_r(x1, x2, sh);
-        r.z = __funnelshift_r(x2, x3, sh); r.w = __funnelshift_r(x3, x4, sh);
+        r.x = __funnelshift_r(x0, x1, sh8); r.y = __funnelshift_r(x1, x2, sh8);
+        r.z = __funnelshift_r(x2, x3, sh8); r.w = __funnelshift_r(x3, x4, sh8);
         return r;
     };
     const uint32_t span = total * (uint32_t)stride;
@@ -392,43 +524,8 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
         }
         st_stream(reinterpret_cast<int4*>(out + rel), make_int4((int)v.x, (int)v.y, (int)v.z, (int)v.w));
     };
-#if UDA_FR_OUT32
-    // 32 bytes per thread and iteration (strides >= 40): the record look-up, the division and the straddle handling
-    // are paid once per 32 bytes instead of once per 16
-    auto lds32 = [](uint32_t a, uint32_t (&r)[8]) {  // 32 bytes at arbitrary shared address a
-        const uint32_t w = a & ~3u, sh = (a & 3u) * 8u;
-        uint32_t x[9];
-#pragma unroll
-        for (int i = 0; i < 9; ++i) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(x[i]) : "r"(w + 4u * i));
-#pragma unroll
-        for (int i = 0; i < 8; ++i) r[i] = __funnelshift_r(x[i], x[i + 1], sh);
-    };
-    const uint32_t nunits = stride >= 40 ? (nfull >> 1) : 0u;
-    for (uint32_t un = tid; un < nunits; un += FR_THREADS) {
-        const uint32_t rel = head + (un << 5);
-        const uint32_t p = rel / (uint32_t)stride;
-        const uint32_t o = rel - p * (uint32_t)stride;
-        const uint32_t len0 = (uint32_t)stride - o < 32u ? (uint32_t)stride - o : 32u;
-        uint32_t v[8];
-        lds32(slot_addr(p) + o, v);
-        if (len0 < 32u) {  // the 32 bytes straddle two records (stride >= 40: never three)
-            uint32_t u[8];
-            lds32(slot_addr(p + 1) - len0, u);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int rem = (int)len0 - 4 * i;   // bytes of word i that still belong to the first record
-                const uint32_t m = rem >= 4 ? 0xFFFFFFFFu : rem <= 0 ? 0u : ((1u << (8 * rem)) - 1u);
-                v[i] = (v[i] & m) | (u[i] & ~m);
-            }
-        }
-        st_stream(reinterpret_cast<int4*>(out + rel), make_int4((int)v[0], (int)v[1], (int)v[2], (int)v[3]));
-        st_stream(reinterpret_cast<int4*>(out + rel + 16), make_int4((int)v[4], (int)v[5], (int)v[6], (int)v[7]));
-    }
-    for (uint32_t w = (nunits << 1) + tid; w < nfull; w += FR_THREADS) emit16(w);
-#else
 #pragma unroll 2
     for (uint32_t w = tid; w < nfull; w += FR_THREADS) emit16(w);
-#endif
     // unaligned head and tail bytes of the tile's span (< 16 bytes each)
     {
         const uint32_t tail0 = head + (nfull << 4);
@@ -446,28 +543,36 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
 
 template <bool ALIGN2, int STRIDE>
 __global__ void __launch_bounds__(FR_THREADS, UDA_FR_CTAS)
-fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride_rt, int key_off, int key_len,
-                const uint32_t* __restrict__ P, const uint32_t* __restrict__ outoff, FrParams* __restrict__ prm,
-                uint8_t* __restrict__ out) {
+fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int stride_rt, int key_off, int key_len, int force_tree,
+                const uint32_t* __restrict__ P, const uint32_t* __restrict__ outoff, const unsigned long long* __restrict__ bkey,
+                const uint8_t* __restrict__ kind, FrParams* __restrict__ prm, uint8_t* __restrict__ out) {
     const int stride = STRIDE > 0 ? STRIDE : stride_rt;
     extern __shared__ __align__(128) uint8_t fr_smem_raw[];
     __shared__ __align__(8) uint64_t mbar;
-    __shared__ uint32_t s_cnt;
+    __shared__ uint32_t s_cnt, s_flag;
+    __shared__ uint32_t s_ws[32];
     FrSmem sm;
-    const size_t rec_bytes = ((size_t)FR_TILE * stride + (size_t)FR_SLICE_PAD * k + 64 + 15) & ~(size_t)15;
     sm.rec = fr_smem_raw;
-    sm.entA = reinterpret_cast<Entry*>(fr_smem_raw + rec_bytes);
-    sm.entB = sm.entA + FR_TILE;
-    sm.slotaddr = reinterpret_cast<uint32_t*>(sm.entB + FR_TILE);
-    sm.lo = sm.slotaddr + FR_TILE;
+    uint8_t* work = fr_smem_raw + fr_rec_bytes(cap, k, stride);
+    sm.entA = reinterpret_cast<Entry*>(work);
+    sm.entB = sm.entA + cap;
+    sm.slotaddr = reinterpret_cast<uint32_t*>(sm.entB + cap);
+    sm.skey = reinterpret_cast<unsigned long long*>(work);
+    sm.sts = reinterpret_cast<uint32_t*>(sm.skey + cap);
+    sm.bincnt = sm.sts + cap;
+    sm.binbase = sm.bincnt + FR_NBIN;
+    sm.srcaddr = reinterpret_cast<uint32_t*>(work + fr_work_bytes(cap));
+    sm.lo = sm.srcaddr + cap;
     sm.hi = sm.lo + k;
     sm.bend = sm.hi + k;
     sm.sbase = sm.bend + k;
     sm.soff = sm.sbase + k;
     sm.doff = sm.soff + (k + 1);
     if (threadIdx.x == 0) { mbar_init(&mbar, 1); mbar_fence_init(); }
+    for (int b = threadIdx.x; b < FR_NBIN; b += FR_THREADS) sm.bincnt[b] = 0u;
     __syncthreads();
     uint32_t phase = 0;
+    const unsigned long long gmin = prm->kmin, gmax = prm->kmax;
 
     // Buckets are handed out through a counter, not by blockIdx stride: when part of the SMs is held by a
     // concurrently running push kernel, the CTAs that do get an SM still share the work evenly.
@@ -486,9 +591,14 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride_rt
             sm.bend[r] = P[(long long)(q + 1) * k + r];
             sm.hi[r] = sm.bend[r];
         }
+        FrBinMap bm;   // the bucket's key range: [first key of the bucket, last key before the next bucket]
+        bm.klo = kind[q] == 1 ? bkey[q] : gmin;
+        const unsigned long long khi = kind[q + 1] == 1 ? bkey[q + 1] - 1ull : gmax;
+        bm.kspan = khi > bm.klo ? khi - bm.klo : 0ull;
         __syncthreads();
-        if (total <= (uint32_t)FR_TILE) {
-            fr_process_tile<ALIGN2, STRIDE>(runs, sm, k, stride, key_off, key_len, total, out + (unsigned long long)obase * stride, &mbar, phase);
+        if (total <= (uint32_t)cap) {
+            fr_process_tile<ALIGN2, STRIDE>(runs, sm, k, stride, key_off, key_len, total, bm, force_tree,
+                                            out + (unsigned long long)obase * stride, &mbar, phase, s_ws, &s_flag, prm);
             continue;
         }
         // ---- oversize bucket: split by bisection over the 128-bit value (key80 | run | index)
@@ -497,7 +607,7 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride_rt
         unsigned __int128 vlo = 0;
         while (remaining > 0) {
             uint32_t cnt;
-            if (remaining <= (uint32_t)FR_TILE) {
+            if (remaining <= (uint32_t)cap) {
                 for (int r = threadIdx.x; r < k; r += FR_THREADS) sm.hi[r] = sm.bend[r];
                 cnt = remaining;
                 __syncthreads();
@@ -529,10 +639,10 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride_rt
                     __syncthreads();
                     c = s_cnt;
                     ++iters;
-                    if (c > (uint32_t)FR_TILE) hi128 = mid;
+                    if (c > (uint32_t)cap) hi128 = mid;
                     else {
                         lo128 = mid; best = mid; bestc = c;
-                        if (c >= (uint32_t)FR_TILE / 2) break;
+                        if (c >= (uint32_t)cap / 2) break;
                     }
                 }
                 if (threadIdx.x == 0) atomicAdd(&prm->fallback_iters, (unsigned long long)iters);
@@ -541,7 +651,8 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride_rt
                 vlo = best;
                 __syncthreads();
             }
-            if (cnt) fr_process_tile<ALIGN2, STRIDE>(runs, sm, k, stride, key_off, key_len, cnt, out + (unsigned long long)(obase + done) * stride, &mbar, phase);
+            if (cnt) fr_process_tile<ALIGN2, STRIDE>(runs, sm, k, stride, key_off, key_len, cnt, bm, force_tree,
+                                                     out + (unsigned long long)(obase + done) * stride, &mbar, phase, s_ws, &s_flag, prm);
             done += cnt;
             remaining -= cnt;
             for (int r = threadIdx.x; r < k; r += FR_THREADS) sm.lo[r] = sm.hi[r];
@@ -552,7 +663,7 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride_rt
 
 __global__ void fr_eof_kernel(uint8_t* dst) { dst[0] = 0xFF; dst[1] = 0xFF; }
 
-static inline int fr_num_buckets(long long n) { return (int)(n / FR_TARGET) + 2; }
+static inline int fr_num_buckets(long long n, int cap) { return (int)(n / fr_target(cap)) + 2; }
 static inline size_t fr_al(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct FrScratch {
@@ -565,9 +676,9 @@ struct FrScratch {
     uint8_t* kind;     // [G+1]
     size_t bytes;
 };
-static FrScratch fr_layout(void* base, long long n, int k) {
+static FrScratch fr_layout(void* base, long long n, int k, int cap) {
     FrScratch s;
-    const int G = fr_num_buckets(n);
+    const int G = fr_num_buckets(n, cap);
     uint8_t* b = (uint8_t*)base;
     size_t off = 0;
     s.prm = (FrParams*)(b + off); off += fr_al(sizeof(FrParams));
@@ -581,48 +692,71 @@ static FrScratch fr_layout(void* base, long long n, int k) {
     return s;
 }
 
-}  // namespace uda
-
-// cap on resident merge CTAs per SM (0 = as many as fit): lowered when the merge shares the GPU with a
-// concurrently running push kernel, so that the push CTAs find registers and thread slots
-static int g_fr_ctas_per_sm = 0;
-extern "C" int uda_merge_records_set_ctas_per_sm(int n) {
-    if (n < 0 || n > 32) return UDA_E_INVALID;
-    g_fr_ctas_per_sm = n;
-    return 0;
+// Tile capacity for a run count and stride: the largest multiple of 32 slots (<= FR_TILE) whose shared memory lets
+// `want_ctas` CTAs share an SM (227 KB per SM, 1 KB reserved per CTA + the kernel's static shared memory).
+static int fr_pick_cap(int k, int stride, int want_ctas) {
+    const size_t budget = (size_t)232448 / (size_t)want_ctas - 1024 - 256;
+    int cap = FR_TILE;
+    while (cap > FR_CAP_MIN && fr_smem_bytes(cap, k, stride) > budget) cap -= 32;
+    return cap;
 }
+// UDA_FR_CAP (tile capacity) / UDA_FR_WANT_CTAS / UDA_FR_FORCE_TREE: experiment overrides, read once
+struct FrEnv { int cap, want_ctas, force_tree; };
+static const FrEnv& fr_env() {
+    static const FrEnv e = [] {
+        FrEnv x{0, 0, 0};
+        if (const char* s = getenv("UDA_FR_CAP")) x.cap = atoi(s);
+        if (const char* s = getenv("UDA_FR_WANT_CTAS")) x.want_ctas = atoi(s);
+        if (const char* s = getenv("UDA_FR_FORCE_TREE")) x.force_tree = atoi(s) != 0;
+        return x;
+    }();
+    return e;
+}
+static int fr_cap_for(int k, int stride) {
+    const FrEnv& e = fr_env();
+    if (e.cap >= 32 && e.cap <= FR_TILE) return e.cap & ~31;
+    int want = e.want_ctas >= 1 && e.want_ctas <= 8 ? e.want_ctas : UDA_FR_CTAS;
+    int cap = fr_pick_cap(k, stride, want);
+    while (want > 1 && fr_smem_bytes(cap, k, stride) > (size_t)232448 / (size_t)want - 1024 - 256) cap = fr_pick_cap(k, stride, --want);
+    return cap;
+}
+
+}  // namespace uda
 
 extern "C" long long uda_merge_records_scratch_bytes(long long n, int nruns) {
     if (n < 0 || nruns < 1) return UDA_E_INVALID;
-    return (long long)uda::fr_layout(nullptr, n, nruns).bytes;
+    return (long long)uda::fr_layout(nullptr, n, nruns, uda::FR_CAP_MIN).bytes;   // upper bound over every tile capacity
 }
 
 extern "C" int uda_merge_records_supported(int nruns, long long n, int stride, int key_len) {
     using namespace uda;
     return nruns >= 1 && nruns <= FR_KMAX && n >= 0 && n < (1LL << 32) - FR_TILE && stride >= 16 && stride <= 128 && key_len >= 1 &&
-           key_len <= 10 && n / FR_TARGET + 2 <= scan4::MAX_ELEMS && fr_smem_bytes(nruns, stride) <= 200 * 1024;
+           key_len <= 10 && n / fr_target(FR_CAP_MIN) + 2 <= scan4::MAX_ELEMS && fr_smem_bytes(FR_CAP_MIN, nruns, stride) <= 200 * 1024;
 }
 
 // Merge nruns sorted fixed-stride runs into `out` (n*stride bytes, + 2 bytes EOF marker if write_eof).
 // Runs must not alias `out`; every run needs 32 readable bytes after its last record.
 extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, long long n, long long max_nrec, int stride,
                                        int key_off, int key_len, int align2, void* out, int write_eof, void* scratch,
-                                       cudaStream_t stream) {
+                                       int ctas_per_sm, cudaStream_t stream) {
     using namespace uda;
     if (!uda_merge_records_supported(nruns, n, stride, key_len)) return UDA_E_INVALID;
     if (align2 && ((stride | key_off) & 1)) return UDA_E_INVALID;
+    if (ctas_per_sm < 0 || ctas_per_sm > 32) return UDA_E_INVALID;
     uint8_t* o = (uint8_t*)out;
     if (n > 0) {
-        FrScratch s = fr_layout(scratch, n, nruns);
-        const int G = fr_num_buckets(n);
+        const int cap = fr_cap_for(nruns, stride);
+        const int per = fr_target(cap) / FR_SAMPLE;     // samples per bucket
+        FrScratch s = fr_layout(scratch, n, nruns, cap);
+        const int G = fr_num_buckets(n, cap);
         fr_range_kernel<<<1, 256, 0, stream>>>(runs_dev, nruns, stride, key_off, key_len, s.prm);
         UDA_CUDA(cudaMemsetAsync(s.hist, 0, (size_t)(FR_NB + 1) * 4, stream));
         {
             long long ns = max_nrec / FR_SAMPLE;
             long long bx = (ns + 255) / 256;
-            long long cap = (kNumSMs * 16 + nruns - 1) / nruns;
-            if (cap < 1) cap = 1;
-            if (bx > cap) bx = cap;
+            long long capb = (kNumSMs * 16 + nruns - 1) / nruns;
+            if (capb < 1) capb = 1;
+            if (bx > capb) bx = capb;
             if (bx < 1) bx = 1;
             dim3 grid((unsigned)bx, (unsigned)nruns);
             fr_sample_hist_kernel<<<grid, 256, 0, stream>>>(runs_dev, stride, key_off, key_len, s.prm, s.hist);
@@ -632,7 +766,7 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
         {
             int bq = (G + 1 + 255) / 256;
             if (bq > kNumSMs * 8) bq = kNumSMs * 8;
-            fr_bkeys_kernel<<<bq, 256, 0, stream>>>(G, s.hist, s.prm, s.bkey, s.kind);
+            fr_bkeys_kernel<<<bq, 256, 0, stream>>>(G, per, s.hist, s.prm, s.bkey, s.kind);
             if (nruns <= 16) {  // measured: search 0.4 ms vs streaming 2.0 ms at k = 8; search 5.5 ms vs streaming 2.4 ms at k = 64
                 long long t = (long long)(G + 1) * nruns;
                 long long b = (t + 255) / 256;
@@ -640,12 +774,12 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
                 fr_partition_search_kernel<<<(int)b, 256, 0, stream>>>(runs_dev, nruns, G, stride, key_off, key_len, s.bkey, s.kind, s.P);
             } else {
                 long long bx = (max_nrec + 255) / 256;
-                long long cap = (kNumSMs * 16 + nruns - 1) / nruns;
-                if (cap < 1) cap = 1;
-                if (bx > cap) bx = cap;
+                long long capb = (kNumSMs * 16 + nruns - 1) / nruns;
+                if (capb < 1) capb = 1;
+                if (bx > capb) bx = capb;
                 if (bx < 1) bx = 1;
                 dim3 grid((unsigned)bx, (unsigned)nruns);
-                fr_partition_kernel<<<grid, 256, 0, stream>>>(runs_dev, nruns, G, stride, key_off, key_len, s.hist, s.prm, s.bkey, s.kind, s.P);
+                fr_partition_kernel<<<grid, 256, 0, stream>>>(runs_dev, nruns, G, per, stride, key_off, key_len, s.hist, s.prm, s.bkey, s.kind, s.P);
             }
         }
         {
@@ -656,25 +790,24 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
         rc = scan4::exclusive(s.sizes, G, s.sizes, s.sums, stream);
         if (rc) return rc;
         {
-            const size_t smem = fr_smem_bytes(nruns, stride);
-            void (*kern)(const UdaRunDesc*, int, int, int, int, int, const uint32_t*, const uint32_t*, FrParams*, uint8_t*);
-            int slot;
-            if (align2 && stride == 102) { kern = fr_merge_kernel<true, 102>; slot = 0; }
-            else if (align2 && stride == 100) { kern = fr_merge_kernel<true, 100>; slot = 1; }
-            else if (align2) { kern = fr_merge_kernel<true, 0>; slot = 2; }
-            else { kern = fr_merge_kernel<false, 0>; slot = 3; }
-            static size_t configured[4] = {0, 0, 0, 0};
-            if (smem > configured[slot]) {
-                UDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                configured[slot] = smem;
-            }
+            const size_t smem = fr_smem_bytes(cap, nruns, stride);
+            void (*kern)(const UdaRunDesc*, int, int, int, int, int, int, int, const uint32_t*, const uint32_t*, const unsigned long long*,
+                         const uint8_t*, FrParams*, uint8_t*);
+            if (align2 && stride == 102) kern = fr_merge_kernel<true, 102>;
+            else if (align2 && stride == 100) kern = fr_merge_kernel<true, 100>;
+            else if (align2) kern = fr_merge_kernel<true, 0>;
+            else kern = fr_merge_kernel<false, 0>;
+            // the opt-in is a per-device attribute of the function: set it on every call (a few hundred ns) rather than
+            // remembering it per process, which breaks the second device of a multi-GPU process
+            UDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int per_sm = 0;
             UDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FR_THREADS, smem));
             if (per_sm < 1) return UDA_E_TOO_LARGE;
-            if (g_fr_ctas_per_sm > 0 && per_sm > g_fr_ctas_per_sm) per_sm = g_fr_ctas_per_sm;
+            if (ctas_per_sm > 0 && per_sm > ctas_per_sm) per_sm = ctas_per_sm;
             int grid = kNumSMs * per_sm;
             if (grid > G) grid = G;
-            kern<<<grid, FR_THREADS, smem, stream>>>(runs_dev, nruns, G, stride, key_off, key_len, s.P, s.sizes, s.prm, o);
+            kern<<<grid, FR_THREADS, smem, stream>>>(runs_dev, nruns, G, cap, stride, key_off, key_len, fr_env().force_tree, s.P, s.sizes,
+                                                     s.bkey, s.kind, s.prm, o);
         }
     }
     if (write_eof) uda::fr_eof_kernel<<<1, 1, 0, stream>>>(o + n * stride);
@@ -686,6 +819,21 @@ extern "C" int uda_merge_records_stats(const void* scratch, unsigned long long* 
     const uda::FrParams* p = (const uda::FrParams*)scratch;
     UDA_CUDA(cudaMemcpyAsync(out2_host, &p->fallback_buckets, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
     UDA_CUDA(cudaStreamSynchronize(stream));
+    return 0;
+}
+// {oversize buckets, bisection iterations, tiles ordered by the merge tree} of the last merge; synchronises the stream
+extern "C" int uda_merge_records_stats3(const void* scratch, unsigned long long* out3_host, cudaStream_t stream) {
+    const uda::FrParams* p = (const uda::FrParams*)scratch;
+    UDA_CUDA(cudaMemcpyAsync(out3_host, &p->fallback_buckets, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+    UDA_CUDA(cudaStreamSynchronize(stream));
+    return 0;
+}
+// tile capacity (record slots) and shared memory per CTA the merge would use for this shape
+extern "C" int uda_merge_records_tile(int nruns, int stride, int* cap_out, long long* smem_out) {
+    if (nruns < 1 || stride < 16) return UDA_E_INVALID;
+    const int cap = uda::fr_cap_for(nruns, stride);
+    if (cap_out) *cap_out = cap;
+    if (smem_out) *smem_out = (long long)uda::fr_smem_bytes(cap, nruns, stride);
     return 0;
 }
 

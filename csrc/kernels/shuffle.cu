@@ -158,25 +158,26 @@ __global__ void barrier_counted_kernel(unsigned long long* const* __restrict__ p
 
 }  // namespace uda
 
-// process-wide interleave factor for uda_shuffle_push (set once per job to the number of destination ranks)
-static int g_push_nway = 1;
-extern "C" int uda_shuffle_push_set_interleave(int nway) {
-    if (nway < 1 || nway > 4096) return UDA_E_INVALID;
-    g_push_nway = nway;
-    return 0;
-}
-
 extern "C" long long uda_push_scratch_bytes(int nseg) { return ((long long)nseg + 1) * (long long)sizeof(unsigned); }
 
-extern "C" int uda_shuffle_push(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, cudaStream_t stream) {
+// `nway` interleaves the chunk order over the peer-major descriptor table (number of destination ranks: the local
+// copy and the remote pushes then run concurrently); 1 = chunks in descriptor order. It is a call parameter: the
+// library keeps no per-process push state, so several jobs / devices in one process cannot disturb each other.
+extern "C" int uda_shuffle_push_nway(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, int nway,
+                                     cudaStream_t stream) {
     using namespace uda;
+    if (nway < 1 || nway > 4096) return UDA_E_INVALID;
     if (nseg <= 0) return 0;
     unsigned* prefix = (unsigned*)scratch;
     push_plan_kernel<<<1, 1024, 0, stream>>>(descs_dev, nseg, prefix);
     int grid = max_ctas > 0 ? max_ctas : kNumSMs * 8;
-    push_kernel<<<grid, PUSH_THREADS, 0, stream>>>(descs_dev, nseg, prefix, g_push_nway > 0 ? (unsigned)g_push_nway : 1u);
+    push_kernel<<<grid, PUSH_THREADS, 0, stream>>>(descs_dev, nseg, prefix, (unsigned)nway);
     UDA_CHECK_LAUNCH();
     return 0;
+}
+
+extern "C" int uda_shuffle_push(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, cudaStream_t stream) {
+    return uda_shuffle_push_nway(descs_dev, nseg, scratch, max_ctas, 1, stream);
 }
 
 extern "C" int uda_wait_flags(const unsigned long long* flags_dev, const unsigned long long* expect_dev, int n,

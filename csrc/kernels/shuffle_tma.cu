@@ -249,21 +249,16 @@ __global__ void __launch_bounds__(32 * TP_WARPS, 1) push_tma_kernel(const UdaPus
 }  // namespace
 }  // namespace uda
 
-static int g_tp_flush = 8;
-extern "C" int uda_shuffle_push_tma_set_flush(int chunks) {
-    if (chunks < 1 || chunks > uda::TP_FLUSH_MAX) return UDA_E_INVALID;
-    g_tp_flush = chunks;
-    return 0;
-}
-
 extern "C" long long uda_push_tma_scratch_bytes(int nseg) {
     if (nseg < 0) return UDA_E_INVALID;
     return ((long long)(nseg + 1) * 4 + 15) / 16 * 16 + (long long)sizeof(uda::TpSub) + 64;
 }
 
 extern "C" int uda_shuffle_push_tma(const UdaPushDesc* descs_dev, int nseg, int nsub, int nway, void* scratch, int num_ctas,
-                                    cudaStream_t stream) {
+                                    int flush_chunks, cudaStream_t stream) {
     using namespace uda;
+    if (flush_chunks == 0) flush_chunks = 8;
+    if (flush_chunks < 1 || flush_chunks > TP_FLUSH_MAX) return UDA_E_INVALID;
     if (nseg <= 0) return 0;
     if (nsub < 1 || nsub > TP_MAXSUB || nseg % nsub != 0 || nway < 1) return UDA_E_INVALID;
     if (num_ctas <= 0) num_ctas = 32;
@@ -279,7 +274,7 @@ extern "C" int uda_shuffle_push_tma(const UdaPushDesc* descs_dev, int nseg, int 
         attr_set[dev] = true;
     }
     tp_plan_kernel<<<1, 1024, 0, stream>>>(descs_dev, nseg, nsub, (unsigned)nway, chunk_prefix, sub);
-    push_tma_kernel<<<num_ctas, 32 * TP_WARPS, smem, stream>>>(descs_dev, nseg, nsub, (unsigned)nway, chunk_prefix, sub, g_tp_flush);
+    push_tma_kernel<<<num_ctas, 32 * TP_WARPS, smem, stream>>>(descs_dev, nseg, nsub, (unsigned)nway, chunk_prefix, sub, flush_chunks);
     UDA_CHECK_LAUNCH();
     return 0;
 }

@@ -79,22 +79,25 @@ int uda_merge_runs_fixed(const UdaRunDesc* runs_dev, const long long* run_off_de
                          long long max_nrec, int stride, int key_off, int key_len, void* entries_tmp,
                          void* sorted_out, void* scratch, cudaStream_t stream);
 /* Fused fixed-stride merge that reads and writes every record exactly once (sampled k-way merge-path
- * partition, TMA-staged record tiles, in-shared-memory merge tree, records stored straight to their merged
- * position). out: n*stride bytes (+2 for the EOF marker). align2 = 1 when stride, key_off, every run base
- * and `out` are even (TeraSort). Runs need 32 readable bytes after their last record. */
+ * partition, TMA-staged record tiles ordered in shared memory by key bins + exact in-bin ranking, independent of
+ * the run count; merge tree for duplicate-heavy tiles; records stored straight to their merged position). out: n*stride bytes (+2 for the EOF marker). align2 = 1 when stride, key_off, every run base
+ * and `out` are even (TeraSort). Runs need 32 readable bytes after their last record. ctas_per_sm caps the
+ * resident merge CTAs per SM (0 = occupancy limit; lower it when a push kernel runs concurrently). */
 long long uda_merge_records_scratch_bytes(long long n, int nruns);
 int uda_merge_records_supported(int nruns, long long n, int stride, int key_len);
 int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, long long n, long long max_nrec, int stride,
                             int key_off, int key_len, int align2, void* out, int write_eof, void* scratch,
-                            cudaStream_t stream);
+                            int ctas_per_sm, cudaStream_t stream);
 /* key-range cuts of a sorted fixed-stride run (spill path): equi-depth splitters, and positions of splitters */
 int uda_sample_splitters(const void* base, long long n, int stride, int key_off, int key_len, int nkeys,
                          unsigned long long* keys_out_dev, cudaStream_t stream);
 int uda_lower_bound_records(const void* base, long long n, int stride, int key_off, int key_len,
                             const unsigned long long* keys_dev, int nkeys, long long* pos_out_dev, cudaStream_t stream);
-/* cap on resident merge CTAs per SM (0 = occupancy limit); use < max when a push kernel runs concurrently */
-int uda_merge_records_set_ctas_per_sm(int n);
 int uda_merge_records_stats(const void* scratch, unsigned long long* out2_host, cudaStream_t stream);
+/* {oversize buckets, bisection iterations, tiles ordered by the merge tree instead of the key bins}; synchronises */
+int uda_merge_records_stats3(const void* scratch, unsigned long long* out3_host, cudaStream_t stream);
+/* tile capacity (record slots) and dynamic shared memory per CTA the fused merge uses for this shape */
+int uda_merge_records_tile(int nruns, int stride, int* cap_out, long long* smem_out);
 /* synchronises the stream; out2_host = {oversize buckets, bisection iterations} of the last merge */
 int uda_merge_stats(const void* scratch, unsigned long long* out2_host, cudaStream_t stream);
 
@@ -132,21 +135,22 @@ int uda_write_eof_at(void* dst, const unsigned long long* total_dev, cudaStream_
  *      :44-136 credits) --------------------------------------------------------------------------- */
 long long uda_push_scratch_bytes(int nseg);
 int uda_shuffle_push(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, cudaStream_t stream);
+/* the same push with the chunk order interleaved over `nway` destination ranks (peer-major descriptor table), so the
+ * local copy and the remote pushes run concurrently; uda_shuffle_push is nway = 1 (chunks in descriptor order) */
+int uda_shuffle_push_nway(const UdaPushDesc* descs_dev, int nseg, void* scratch, int max_ctas, int nway,
+                          cudaStream_t stream);
 /* Copy-engine variant of the push: `nsub` descriptor tables of nseg/nsub entries each, concatenated in the order
  * they must land (sub-partition 0 first). `num_ctas` single-warp CTAs (default 32) each claim one SM through a
  * 192 KiB shared-memory ring and move 32 KiB chunks with cp.async.bulk in both directions; the landed-byte counters
  * are advanced per chunk exactly as by uda_shuffle_push. `nway` interleaves the chunk order inside a sub-partition
  * over the peer-major descriptor order. scratch: uda_push_tma_scratch_bytes(nseg). */
 long long uda_push_tma_scratch_bytes(int nseg);
+/* flush_chunks: chunks (16 KiB each) a copy warp completes between two advances of the landed-byte counters
+ * (1..64, 0 = default 8): each advance costs one system-scope fence. */
 int uda_shuffle_push_tma(const UdaPushDesc* descs_dev, int nseg, int nsub, int nway, void* scratch, int num_ctas,
-                         cudaStream_t stream);
-/* chunks (16 KiB each) a copy warp completes between two advances of the landed-byte counters (1..64, default 8):
- * each advance costs one system-scope fence */
-int uda_shuffle_push_tma_set_flush(int chunks);
-/* chunk-order interleave factor of uda_shuffle_push (number of destination ranks; 1 = sequential) */
-int uda_shuffle_push_set_interleave(int nway);
+                         int flush_chunks, cudaStream_t stream);
 /* No counterpart in the reference (it has no device code and nothing that must avoid allocation).
- * Same push as uda_shuffle_push, but the chunk-prefix scratch is a fixed array inside the library,
+ * Same push as uda_shuffle_push (chunks in descriptor order), but the chunk-prefix scratch is a fixed array inside the library,
  * so the call never allocates: for providers embedded in a process that does not own the GPU's free
  * memory (JNI plugin next to another runtime, fixed-budget services) or that must not trigger the
  * implicit device synchronisation of cudaMalloc. At most UDA_PUSH_STATIC_MAX_SEGMENTS descriptors per

@@ -228,6 +228,9 @@ def test_kway_merge_and_gather(K, sizes, key_bits):
     ([6000, 7000, 5000], 3, False),   # 8 distinct keys: oversize buckets -> (key, run, index) bisection
     ([4000] * 9, 10, False), ([5000, 3000, 4000], 0, True),  # odd base addresses: byte-granular path
     ([3] * 20 + [5000] * 4, 0, False),                       # k > 16: streaming partition, tiny runs take the search path
+    ([9000] * 64, 0, False),                                 # k = 64: slices of ~6 records per tile
+    ([30000] * 6, 14, False),                                # 16384 distinct keys: several equal keys per bin, still the bin path
+    ([2000] * 200, 0, False),                                # k = 200: smaller tile capacity (per-run shared-memory tables)
 ])
 def test_fused_record_merge(K, sizes, key_bits, odd):
     dev = _dev()
@@ -247,6 +250,7 @@ def test_fused_record_merge(K, sizes, key_bits, odd):
     scratch = torch.empty(K.merge_records_scratch_bytes(n, k), dtype=torch.uint8, device=dev)
     K.merge_records_fixed(K.to_device_struct(desc, dev), k, n, max(sizes), 102, 2, 10, out, scratch, write_eof=True, align2=not odd)
     fb, iters = K.merge_records_stats(scratch)
+    _fb3, _it3, tree_tiles = K.merge_records_stats3(scratch) if n else (0, 0, 0)
     w0 = np.concatenate([_entries_np(h, run=r)[0] for r, h in enumerate(host_runs)]) if n else np.zeros(0, np.uint64)
     w1 = np.concatenate([_entries_np(h, run=r)[1] for r, h in enumerate(host_runs)]) if n else np.zeros(0, np.uint64)
     order = _sort_order(w0, w1)
@@ -256,6 +260,9 @@ def test_fused_record_merge(K, sizes, key_bits, odd):
     assert bytes(host[n * 102: n * 102 + 2]) == b"\xff\xff"
     if key_bits == 3:
         assert fb > 0 and iters > 0
+        assert tree_tiles > 0          # one key per tile: every record lands in one bin -> merge-tree ordering
+    if key_bits == 0:
+        assert tree_tiles == 0         # random keys: every tile is ordered by the key bins
 
 
 @pytest.mark.parametrize("stride", [16, 30, 100, 102, 257])

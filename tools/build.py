@@ -22,7 +22,10 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent
 LIB_DIR = ROOT / "uda_b200" / "lib"
-OBJ_DIR = ROOT / "build" / "obj"
+# UDA_BUILD_TAG=<tag>: an A/B variant of the kernel library (UDA_FR_* / UDA_TP_* defines from the environment) is
+# written to libuda_kernels_<tag>.so with its own object directory; select it with UDA_B200_KERNELS_LIB
+TAG = os.environ.get("UDA_BUILD_TAG", "")
+OBJ_DIR = ROOT / "build" / ("obj_" + TAG if TAG else "obj")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = os.environ.get("CXX", "g++")
 
@@ -89,9 +92,11 @@ def build(verbose: bool = False) -> dict:
         cu_objs = list(ex.map(lambda s: _compile(s, NVCC, NVCC_FLAGS + vflag), cu))
         cc_objs = list(ex.map(lambda s: _compile(s, CXX, CXX_FLAGS + vflag), cc))
     out = {}
-    klib = LIB_DIR / "libuda_kernels.so"
+    klib = LIB_DIR / (f"libuda_kernels_{TAG}.so" if TAG else "libuda_kernels.so")
     _run([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(klib), *map(str, cu_objs)])
     out["kernels"] = klib
+    if TAG:
+        return out
     if cc_objs:
         rlib = LIB_DIR / "libuda.so"
         _run([CXX, "-shared", "-pthread", "-o", str(rlib), *map(str, cc_objs), "-ldl"])

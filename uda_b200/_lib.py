@@ -44,10 +44,11 @@ _PROTOS = {
     "uda_merge_runs_fixed": (c_int, [c_vp, c_vp, c_int, c_ll, c_ll, c_int, c_int, c_int, c_vp, c_vp, c_vp, c_vp]),
     "uda_merge_records_scratch_bytes": (c_ll, [c_ll, c_int]),
     "uda_merge_records_supported": (c_int, [c_int, c_ll, c_int, c_int]),
-    "uda_merge_records_fixed": (c_int, [c_vp, c_int, c_ll, c_ll, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp, c_vp]),
+    "uda_merge_records_stats3": (c_int, [c_vp, c_vp, c_vp]),
+    "uda_merge_records_tile": (c_int, [c_int, c_int, c_vp, c_vp]),
+    "uda_merge_records_fixed": (c_int, [c_vp, c_int, c_ll, c_ll, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp, c_int, c_vp]),
     "uda_sample_splitters": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     "uda_lower_bound_records": (c_int, [c_vp, c_ll, c_int, c_int, c_int, c_vp, c_int, c_vp, c_vp]),
-    "uda_merge_records_set_ctas_per_sm": (c_int, [c_int]),
     "uda_merge_records_stats": (c_int, [c_vp, C.POINTER(c_ull), c_vp]),
     "uda_merge_stats": (c_int, [c_vp, C.POINTER(c_ull), c_vp]),
     "uda_gather_fixed": (c_int, [c_vp, c_ll, c_vp, c_int, c_vp, c_int, c_vp]),
@@ -64,10 +65,9 @@ _PROTOS = {
     "uda_snappy_decode_blocks": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]),
     "uda_push_scratch_bytes": (c_ll, [c_int]),
     "uda_shuffle_push": (c_int, [c_vp, c_int, c_vp, c_int, c_vp]),
-    "uda_shuffle_push_set_interleave": (c_int, [c_int]),
+    "uda_shuffle_push_nway": (c_int, [c_vp, c_int, c_vp, c_int, c_int, c_vp]),
     "uda_push_tma_scratch_bytes": (c_ll, [c_int]),
-    "uda_shuffle_push_tma_set_flush": (c_int, [c_int]),
-    "uda_shuffle_push_tma": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_int, c_vp]),
+    "uda_shuffle_push_tma": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_vp]),
     "uda_wait_flags": (c_int, [c_vp, c_vp, c_int, c_ull, c_vp, c_vp]),
     "uda_barrier_all": (c_int, [c_vp, c_int, c_int, c_ull, c_ull, c_vp, c_vp]),
     "uda_barrier_all_counted": (c_int, [c_vp, c_int, c_int, c_vp, c_ull, c_vp, c_vp]),

@@ -134,7 +134,6 @@ class SortJob:
                                  [self.arena.peer_flag_ptr(p, 0) for p in range(P)], 0), dev)
         self.nseg = self.maps * P
         self.push_scratch = torch.empty(K.push_scratch_bytes(self.nseg), dtype=torch.uint8, device=dev)
-        K.shuffle_push_set_interleave(P)
         lay = self.plan.layout(self.rank)
         data = self.arena.data()
         #: landed segments of this reducer in run order: (tensor view, raw length incl. EOF, exact record count)
@@ -190,12 +189,12 @@ class SortJob:
         if self.world > 1:
             self.arena.barrier()
         self.expect.add_(self.expect_step)
-        K.shuffle_push(self.push_descs_dev, self.nseg, self.push_scratch, self.push_ctas)
+        K.shuffle_push(self.push_descs_dev, self.nseg, self.push_scratch, self.push_ctas, self.world)
         if self.side_index:
             if self.world > 1:
                 self.side_arena.barrier()
             self.side_expect.add_(self.side_expect_step)
-            K.shuffle_push(self.side_descs_dev, self.nseg, self.side_scratch, self.push_ctas)
+            K.shuffle_push(self.side_descs_dev, self.nseg, self.side_scratch, self.push_ctas, self.world)
             K.wait_flags(self.side_arena.flags()[: self.plan.nruns], self.side_expect, self.plan.nruns, self.side_arena.status)
         K.wait_flags(self.arena.flags()[: self.plan.nruns], self.expect, self.plan.nruns, self.arena.status)
         out, _ = self.merger.merge(self.segments, exact_counts=True, rec_offs=self.rec_offs)

@@ -54,7 +54,7 @@ class TeraSortJob:
 
     def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 1234,
                  key_bits: int = 0, group=None, push_ctas: int = 0, subparts: int = 1, merge_ctas_per_sm: int = 0,
-                 push_mode: str = "lsu", local_zero_copy: bool = False):
+                 push_mode: str = "lsu", local_zero_copy: bool = False, tma_flush: int = 0):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -72,6 +72,8 @@ class TeraSortJob:
         #: launch for all sub-partitions on `push_ctas` SMs of its own, the merge keeps the remaining SMs
         assert push_mode in ("lsu", "tma")
         self.push_mode = push_mode
+        #: copy-engine push: chunks between two advances of the landed-byte counters (0 = library default)
+        self.tma_flush = tma_flush
         #: merge this rank's own map outputs where they lie instead of copying them into the arena first (the
         #: reference and Hadoop copy local fetches like remote ones). Off by default: the headline benchmark moves
         #: every segment. Not available on the end-to-end path, whose map outputs alternate between two buffers.
@@ -123,8 +125,6 @@ class TeraSortJob:
         self.push_scratch = [torch.empty(K.push_scratch_bytes(self.nseg), dtype=torch.uint8, device=dev) for _ in range(C)]
         self.push_descs_all = torch.cat(self.push_descs_dev).contiguous()
         self.push_tma_scratch = torch.empty(K.push_tma_scratch_bytes(self.nseg * C), dtype=torch.uint8, device=dev)
-        K.shuffle_push_set_interleave(P)  # local copy and the P-1 remote pushes run concurrently
-        K.merge_records_set_ctas_per_sm(self.merge_ctas_per_sm)
         self.sub_runs, self.sub_n, expect = [], [], []
         max_sub = 1
         for j in range(C):
@@ -143,7 +143,8 @@ class TeraSortJob:
         self.n_out = sum(self.sub_n)
         self.expect_step = torch.from_numpy(np.concatenate(expect)).to(dev)
         self.expect = torch.zeros_like(self.expect_step)
-        self.merger = DeviceMerger(max_sub, nruns, TERA_STRIDE, dev, out_bytes=self.n_out * TERA_STRIDE + 2)
+        self.merger = DeviceMerger(max_sub, nruns, TERA_STRIDE, dev, out_bytes=self.n_out * TERA_STRIDE + 2,
+                                   ctas_per_sm=self.merge_ctas_per_sm)
         snaps = []
         for rd, run_off, run_base in self.sub_runs:
             self.merger.set_runs(rd, run_off, run_base)
@@ -196,19 +197,19 @@ class TeraSortJob:
             all_descs = self.push_descs_all if descs is self.push_descs_dev else torch.cat(descs).contiguous()
         if C == 1:
             if tma:
-                K.shuffle_push_tma(all_descs, self.nseg, 1, self.world, self.push_tma_scratch, self.push_ctas)
+                K.shuffle_push_tma(all_descs, self.nseg, 1, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
             else:
-                K.shuffle_push(descs[0], self.nseg, self.push_scratch[0], self.push_ctas)
+                K.shuffle_push(descs[0], self.nseg, self.push_scratch[0], self.push_ctas, self.world)
             self._merge_sub(0, out)
         else:
             self.ev_go.record(cur)
             with torch.cuda.stream(self.push_stream):
                 self.push_stream.wait_event(self.ev_go)
                 if tma:
-                    K.shuffle_push_tma(all_descs, self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas)
+                    K.shuffle_push_tma(all_descs, self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
                 else:
                     for j in range(C):
-                        K.shuffle_push(descs[j], self.nseg, self.push_scratch[j], self.push_ctas)
+                        K.shuffle_push(descs[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
                 self.ev_pushed.record(self.push_stream)
             for j in range(C):
                 self._merge_sub(j, out)
@@ -244,12 +245,12 @@ class TeraSortJob:
         with torch.cuda.stream(self.push_stream):
             self.push_stream.wait_event(self.ev_go)
             if self.push_mode == "tma":
-                K.shuffle_push_tma(self.push_descs_all, self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas)
+                K.shuffle_push_tma(self.push_descs_all, self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
                 for j in range(C):
                     pushed[j].record(self.push_stream)
             else:
                 for j in range(C):
-                    K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas)
+                    K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
                     pushed[j].record(self.push_stream)
             self.ev_pushed.record(self.push_stream)
         nruns = self.plan.nruns
@@ -275,10 +276,10 @@ class TeraSortJob:
         ev[0].record()
         if self.push_mode == "tma":
             K.shuffle_push_tma(self.push_descs_all, self.nseg * self.subparts, self.subparts, self.world, self.push_tma_scratch,
-                               self.push_ctas)
+                               self.push_ctas, self.tma_flush)
         else:
             for j in range(self.subparts):  # phases are measured un-overlapped, one sub-partition after the other
-                K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas)
+                K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
         ev[1].record()
         nr = self.plan.nruns * self.subparts
         K.wait_flags(self.arena.flags(), self.expect, nr, self.arena.status)

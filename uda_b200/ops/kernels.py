@@ -130,20 +130,33 @@ def merge_records_scratch_bytes(n: int, nruns: int) -> int:
 
 
 def merge_records_fixed(run_descs_dev: torch.Tensor, nruns: int, n: int, max_nrec: int, stride: int, key_off: int, key_len: int,
-                        out: torch.Tensor, scratch: torch.Tensor, write_eof: bool = True, align2: bool = True) -> None:
-    """Fused fixed-stride k-way merge: every record is read once and written once."""
+                        out: torch.Tensor, scratch: torch.Tensor, write_eof: bool = True, align2: bool = True,
+                        ctas_per_sm: int = 0) -> None:
+    """Fused fixed-stride k-way merge: every record is read once and written once. ``ctas_per_sm`` caps the resident
+    merge CTAs per SM (0 = occupancy limit)."""
     check(kernels().uda_merge_records_fixed(run_descs_dev.data_ptr(), nruns, n, max_nrec, stride, key_off, key_len, int(align2),
-                                            out.data_ptr(), int(write_eof), scratch.data_ptr(), _stream()), "uda_merge_records_fixed")
-
-
-def merge_records_set_ctas_per_sm(n: int) -> None:
-    check(kernels().uda_merge_records_set_ctas_per_sm(n), "uda_merge_records_set_ctas_per_sm")
+                                            out.data_ptr(), int(write_eof), scratch.data_ptr(), ctas_per_sm, _stream()),
+          "uda_merge_records_fixed")
 
 
 def merge_records_stats(scratch: torch.Tensor) -> Tuple[int, int]:
     out = (C.c_ulonglong * 2)()
     check(kernels().uda_merge_records_stats(scratch.data_ptr(), out, _stream()), "uda_merge_records_stats")
     return int(out[0]), int(out[1])
+
+
+def merge_records_stats3(scratch: torch.Tensor) -> Tuple[int, int, int]:
+    """(oversize buckets, bisection iterations, tiles ordered by the merge tree) of the last fused merge."""
+    out = (C.c_ulonglong * 3)()
+    check(kernels().uda_merge_records_stats3(scratch.data_ptr(), out, _stream()), "uda_merge_records_stats3")
+    return int(out[0]), int(out[1]), int(out[2])
+
+
+def merge_records_tile(nruns: int, stride: int) -> Tuple[int, int]:
+    """(tile capacity in records, shared memory per CTA) of the fused merge for this shape."""
+    cap, smem = C.c_int(0), C.c_longlong(0)
+    check(kernels().uda_merge_records_tile(nruns, stride, C.byref(cap), C.byref(smem)), "uda_merge_records_tile")
+    return cap.value, smem.value
 
 
 def merge_stats(scratch: torch.Tensor) -> Tuple[int, int]:
@@ -206,23 +219,22 @@ def push_scratch_bytes(nseg: int) -> int:
     return int(kernels().uda_push_scratch_bytes(nseg))
 
 
-def shuffle_push(descs_dev: torch.Tensor, nseg: int, scratch: torch.Tensor, max_ctas: int = 0) -> None:
-    check(kernels().uda_shuffle_push(descs_dev.data_ptr(), nseg, scratch.data_ptr(), max_ctas, _stream()), "uda_shuffle_push")
+def shuffle_push(descs_dev: torch.Tensor, nseg: int, scratch: torch.Tensor, max_ctas: int = 0, nway: int = 1) -> None:
+    """LSU push. ``nway`` = number of destination ranks the chunk order is interleaved over (1 = descriptor order)."""
+    check(kernels().uda_shuffle_push_nway(descs_dev.data_ptr(), nseg, scratch.data_ptr(), max_ctas, nway, _stream()),
+          "uda_shuffle_push_nway")
 
 
 def push_tma_scratch_bytes(nseg: int) -> int:
     return int(kernels().uda_push_tma_scratch_bytes(nseg))
 
 
-def shuffle_push_tma(descs_dev: torch.Tensor, nseg: int, nsub: int, nway: int, scratch: torch.Tensor, num_ctas: int = 0) -> None:
+def shuffle_push_tma(descs_dev: torch.Tensor, nseg: int, nsub: int, nway: int, scratch: torch.Tensor, num_ctas: int = 0,
+                     flush_chunks: int = 0) -> None:
     """Copy-engine push: ``nsub`` equally long descriptor tables, concatenated, pushed in order by ``num_ctas``
     single-warp CTAs that each own an SM (TMA bulk load -> shared-memory ring -> TMA bulk store to the peer)."""
-    check(kernels().uda_shuffle_push_tma(descs_dev.data_ptr(), nseg, nsub, nway, scratch.data_ptr(), num_ctas, _stream()),
-          "uda_shuffle_push_tma")
-
-
-def shuffle_push_set_interleave(nway: int) -> None:
-    check(kernels().uda_shuffle_push_set_interleave(nway), "uda_shuffle_push_set_interleave")
+    check(kernels().uda_shuffle_push_tma(descs_dev.data_ptr(), nseg, nsub, nway, scratch.data_ptr(), num_ctas, flush_chunks,
+                                         _stream()), "uda_shuffle_push_tma")
 
 
 def wait_flags(flags: torch.Tensor, expect: torch.Tensor, n: int, status: torch.Tensor, max_spins: int = 50_000_000) -> None:

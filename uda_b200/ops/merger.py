@@ -20,8 +20,10 @@ from . import kernels as K
 
 class DeviceMerger:
     def __init__(self, max_records: int, max_runs: int, stride: int, device, out_bytes: Optional[int] = None,
-                 fused: Optional[bool] = None, key_len: int = 10):
+                 fused: Optional[bool] = None, key_len: int = 10, ctas_per_sm: int = 0):
         self.device, self.stride, self.max_records, self.max_runs = device, stride, max_records, max_runs
+        #: cap on resident merge CTAs per SM (0 = occupancy limit); lowered when a push kernel runs concurrently
+        self.ctas_per_sm = ctas_per_sm
         # fused record merge (one read + one write per record) when the shape allows it, else the
         # entry pipeline (key normalise -> entry merge -> gather)
         self.fused = K.merge_records_supported(max_runs, max_records, stride, key_len) if fused is None else fused
@@ -63,7 +65,7 @@ class DeviceMerger:
         out = self.out if out is None else out
         if self.fused:
             K.merge_records_fixed(self.run_descs_dev, self.nruns, n, self.max_nrec, self.stride, key_off, key_len, out,
-                                  self.scratch, write_eof=write_eof, align2=self.align2)
+                                  self.scratch, write_eof=write_eof, align2=self.align2, ctas_per_sm=self.ctas_per_sm)
             return out[: n * self.stride + (2 if write_eof else 0)]
         if n:
             K.merge_runs_fixed(self.run_descs_dev, self.run_off_dev, self.nruns, n, self.max_nrec, self.stride, key_off, key_len,
