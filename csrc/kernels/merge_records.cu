@@ -41,7 +41,7 @@ namespace uda {
 #define UDA_FR_VT 2
 #endif
 #ifndef UDA_FR_CTAS
-#define UDA_FR_CTAS 3
+#define UDA_FR_CTAS 2
 #endif
 #ifndef UDA_FR_THREADS
 #define UDA_FR_THREADS 256
@@ -58,7 +58,7 @@ constexpr int FR_TILE = FR_THREADS * FR_VT;  // largest tile capacity in record 
 constexpr int FR_CAP_MIN = 128;              // smallest capacity the host ever picks (bounds the scratch size)
 constexpr int FR_MERGE_THREADS = UDA_FR_MERGE_THREADS;   // threads that run the merge tree (fewer = more items per thread)
 constexpr int FR_MERGE_VT = FR_TILE / FR_MERGE_THREADS;
-constexpr int FR_NBIN = 2 * FR_THREADS;      // key bins per tile: two per thread in the scan
+constexpr int FR_NBIN = 4 * FR_THREADS;      // key bins per tile: four per thread in the scan
 constexpr int FR_BIN_LIMIT = UDA_FR_BIN_LIMIT;
 constexpr int FR_SAMPLE = 8;
 constexpr int FR_NB_LOG = 22;
@@ -263,14 +263,57 @@ __global__ void fr_sizes_kernel(const uint32_t* __restrict__ P, int k, int G, ui
 }
 
 // ------------------------------------------------------------------------------------------- 5
-// Shared memory of one merge CTA (`cap` = tile capacity in record slots):
-//   rec                      staged record bytes of the k slices
-//   work  (cap * 36 bytes)   bin ordering: skey[cap] u64 | sts[cap] u32 | bincnt[NBIN] | binbase[NBIN + 1]
+// The merge kernel is a producer / consumer pipeline inside every CTA:
+//
+//   producer warp (1)   claims the next bucket, reads its split positions and key range, lays the k slices out in one
+//                       of TWO record buffers and issues the TMA bulk copies for it — one tile ahead of the consumers,
+//                       so the bucket's metadata round trips and the DRAM latency of the copies are off the critical
+//                       path (in the single-buffered version they were 40 % of the stall samples, profiles/NCU_SUMMARY.md).
+//   consumer warps (8)  wait on the buffer's `full` mbarrier, order the tile (key bins, see the file header), write the
+//                       records out, and hand the buffer back through its `empty` mbarrier. They synchronise among
+//                       themselves with a named barrier; the producer never takes part.
+//
+// Shared memory of one CTA (`cap` = tile capacity in record slots):
+//   rec x 2                  staged record bytes of the k slices, double buffered
+//   work  (cap * 36 bytes)   bin ordering: skey[cap] u64 | sts[cap] u32 | bincnt[NBIN] | binbase[NBIN + 4]
 //                            tree ordering (fallback): entA[cap] | entB[cap] | slotaddr[cap]      (same bytes)
 //   srcaddr[cap]             byte offset inside rec of the record that goes to output position p
-//   per-run tables           lo, hi, bend, sbase [k]; soff, doff [k + 1]
+//   meta x 2                 per buffer: header, sbase[k], soff[k + 1], lo[k], bend[k]
+//   hi[k], doff[k + 1]       oversize-bucket / merge-tree scratch (consumers only)
+constexpr int FR_CONSUMERS = FR_THREADS;            // threads that order and emit a tile
+constexpr int FR_THREADS_ALL = FR_CONSUMERS + 32;   // + the producer warp
+constexpr uint32_t FR_META_DONE = 0xFFFFFFFFu;
+
+struct FrTileHdr {
+    unsigned long long klo, kspan;   // key bins cover [klo, klo + kspan]
+    uint32_t total;                  // records in the tile; FR_META_DONE: no more work
+    uint32_t obase;                  // first output record of the tile
+    uint32_t big;                    // oversize bucket: lo / bend hold its slice bounds, nothing was staged
+    uint32_t pad;
+};
+struct FrMeta {
+    FrTileHdr* hdr;
+    uint32_t* sbase;   // [k] byte offset of the first record of run r's slice inside rec
+    uint32_t* soff;    // [k+1] slot offsets (list boundaries for the merge tree)
+    uint32_t* lo;      // [k]
+    uint32_t* bend;    // [k]
+};
 struct FrSmem {
-    uint8_t* rec;
+    uint8_t* rec0;       // two record buffers, rec_bytes apart
+    uint8_t* meta0;      // two metadata blocks, meta_bytes apart
+    uint32_t rec_bytes, meta_bytes;
+    int k;
+    __device__ __forceinline__ uint8_t* rec(uint32_t b) const { return rec0 + b * rec_bytes; }
+    __device__ __forceinline__ FrMeta meta(uint32_t b) const {   // computed, not indexed: keeps the struct in registers
+        uint8_t* mp = meta0 + b * meta_bytes;
+        FrMeta m;
+        m.hdr = reinterpret_cast<FrTileHdr*>(mp);
+        m.sbase = reinterpret_cast<uint32_t*>(mp + sizeof(FrTileHdr));
+        m.soff = m.sbase + k;
+        m.lo = m.soff + (k + 1);
+        m.bend = m.lo + k;
+        return m;
+    }
     Entry* entA;
     Entry* entB;
     uint32_t* slotaddr;
@@ -279,151 +322,154 @@ struct FrSmem {
     uint32_t* bincnt;    // all zero between tiles
     uint32_t* binbase;
     uint32_t* srcaddr;
-    uint32_t* lo;
     uint32_t* hi;
-    uint32_t* bend;
-    uint32_t* sbase;     // [k] byte offset of the first record of run r's slice inside rec
-    uint32_t* soff;      // [k+1] slot offsets (list boundaries for the merge tree)
-    uint32_t* doff;      // [k+1]
+    uint32_t* doff;
 };
 
 __host__ __device__ inline size_t fr_rec_bytes(int cap, int k, int stride) {
     return ((size_t)cap * stride + (size_t)FR_SLICE_PAD * k + 64 + 15) & ~(size_t)15;
 }
 __host__ __device__ inline size_t fr_work_bytes(int cap) {
-    const size_t tree = (size_t)cap * 36, bins = (size_t)cap * 12 + ((size_t)2 * FR_NBIN + 2) * 4;
+    const size_t tree = (size_t)cap * 36, bins = (size_t)cap * 12 + ((size_t)2 * FR_NBIN + 4) * 4;
     return ((tree > bins ? tree : bins) + 15) & ~(size_t)15;
 }
+__host__ __device__ inline size_t fr_meta_bytes(int k) { return sizeof(FrTileHdr) + ((size_t)4 * k + 1) * 4 + 4; }   // multiple of 8
 __host__ __device__ inline size_t fr_smem_bytes(int cap, int k, int stride) {
-    return fr_rec_bytes(cap, k, stride) + fr_work_bytes(cap) + (size_t)cap * 4 + ((size_t)4 * k + 2 * ((size_t)k + 1)) * 4 + 16;
+    return 2 * fr_rec_bytes(cap, k, stride) + fr_work_bytes(cap) + (size_t)cap * 4 + 2 * fr_meta_bytes(k) + ((size_t)2 * k + 1) * 4 + 16;
 }
 
 __device__ __forceinline__ void mbar_expect_tx_only(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// barrier among the consumer warps only (the producer warp runs ahead on its own)
+__device__ __forceinline__ void fr_cbar() { asm volatile("bar.sync 1, %0;" ::"n"(FR_CONSUMERS) : "memory"); }
 
-// key range of one tile and the monotone key -> bin map derived from it
-struct FrBinMap {
-    unsigned long long klo, kspan;   // bins cover [klo, klo + kspan]
-};
+// One full warp lays the k slices [lo[r], hi[r]) out in `rec` (slot offsets by a shuffle scan, 32 runs at a time), issues one
+// bulk copy per non-empty slice and arrives on `bar` once; the data (and the tables) are visible to whoever waits on it.
+__device__ __forceinline__ void fr_stage(const UdaRunDesc* __restrict__ runs, int k, int stride, const uint32_t* lo_a,
+                                         const uint32_t* hi_a, uint8_t* rec, uint32_t* sbase, uint32_t* soff, uint32_t total,
+                                         uint64_t* bar) {
+    const int lane = threadIdx.x & 31;
+    fence_proxy_async_smem();  // earlier generic-proxy accesses to `rec` are ordered before the TMA writes
+    uint32_t run_slot = 0;
+    for (int r0 = 0; r0 < k; r0 += 32) {
+        const int r = r0 + lane;
+        const uint32_t lo = r < k ? lo_a[r] : 0u;
+        const uint32_t len = r < k ? hi_a[r] - lo : 0u;
+        uint32_t x = len;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        const uint32_t slot = run_slot + x - len;
+        if (r < k) {
+            soff[r] = slot;
+            const uint32_t B = ((slot * (uint32_t)stride + (uint32_t)FR_SLICE_PAD * r) + 15u) & ~15u;
+            if (len) {
+                const uint8_t* src = (const uint8_t*)runs[r].base + (unsigned long long)lo * stride;
+                const uint32_t mis = (uint32_t)((uintptr_t)src & 15);
+                const uint32_t nbytes = (mis + len * (uint32_t)stride + 15u) & ~15u;
+                sbase[r] = B + mis;
+                mbar_expect_tx_only(bar, nbytes);
+                tma_load_1d(rec + B, src - mis, nbytes, bar);
+            } else {
+                sbase[r] = B;
+            }
+        }
+        run_slot += __shfl_sync(0xffffffffu, x, 31);
+    }
+    if (lane == 0) soff[k] = total;
+    __syncwarp();                      // every expect_tx and table store precedes the single arrival
+    if (lane == 0) mbar_arrive(bar);
+}
 
+// Orders one staged tile and writes its records to `out` (consumer threads only). `release`: mbarrier of the OTHER record
+// buffer, handed back to the producer once every consumer has left the previous tile's output phase (first barrier here).
+// There is no barrier at the end: the next tile's phase A may overlap this tile's output phase (it touches neither
+// srcaddr nor rec of this buffer).
 template <bool ALIGN2, int STRIDE>
-__device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ runs, const FrSmem& sm, int k, int stride_rt,
-                                                int key_off, int key_len, uint32_t total, const FrBinMap bm, int force_tree,
-                                                uint8_t* __restrict__ out, uint64_t* mbar, uint32_t& phase, uint32_t* s_ws,
-                                                uint32_t* s_flag, FrParams* __restrict__ prm) {
+__device__ __forceinline__ void fr_order_emit(const FrSmem& sm, const uint8_t* rec, const FrMeta& mt, int k, int stride_rt, int key_off,
+                                              int key_len, uint32_t total, unsigned long long klo, unsigned long long kspan,
+                                              int force_tree, uint8_t* __restrict__ out, uint64_t* release, uint32_t* s_ws,
+                                              uint32_t* s_flag, FrParams* __restrict__ prm) {
     const int stride = STRIDE > 0 ? STRIDE : stride_rt;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    // ---- stage the k slices: warp 0 lays them out (slot offsets by a shuffle scan, 32 runs at a time) and issues one
-    //      bulk copy per non-empty slice; everybody then waits on the mbarrier. No block-wide barrier in this phase.
-    if (warp == 0) {
-        fence_proxy_async_smem();  // previous tile's generic-proxy accesses to `rec` are ordered before the TMA writes
-        uint32_t run_slot = 0;
-        for (int r0 = 0; r0 < k; r0 += 32) {
-            const int r = r0 + lane;
-            const uint32_t lo = r < k ? sm.lo[r] : 0u;
-            const uint32_t len = r < k ? sm.hi[r] - lo : 0u;
-            uint32_t x = len;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-                if (lane >= o) x += y;
-            }
-            const uint32_t slot = run_slot + x - len;
-            if (r < k) {
-                sm.soff[r] = slot;
-                const uint32_t B = ((slot * (uint32_t)stride + (uint32_t)FR_SLICE_PAD * r) + 15u) & ~15u;
-                if (len) {
-                    const uint8_t* src = (const uint8_t*)runs[r].base + (unsigned long long)lo * stride;
-                    const uint32_t mis = (uint32_t)((uintptr_t)src & 15);
-                    const uint32_t nbytes = (mis + len * (uint32_t)stride + 15u) & ~15u;
-                    sm.sbase[r] = B + mis;
-                    mbar_expect_tx_only(mbar, nbytes);
-                    tma_load_1d(sm.rec + B, src - mis, nbytes, mbar);
-                } else {
-                    sm.sbase[r] = B;
-                }
-            }
-            run_slot += __shfl_sync(0xffffffffu, x, 31);
-        }
-        if (lane == 0) { sm.soff[k] = total; *s_flag = (uint32_t)force_tree; }
-        __syncwarp();                      // every expect_tx and table store precedes the single arrival
-        if (lane == 0) mbar_arrive(mbar);
-    }
-    mbar_wait(mbar, phase);                // acquire: the tables written by warp 0 are visible too
-    phase ^= 1u;
-
     // ---- A: key of every staged record -> bin, position inside the bin by a shared-memory atomic
-    const int bits = 64 - __clzll((long long)bm.kspan);
+    if (tid == 0) *s_flag = (uint32_t)force_tree;
+    const int bits = 64 - __clzll((long long)kspan);
     const int sh = bits > 32 ? bits - 32 : 0;
-    const float scale = (float)FR_NBIN / (__uint2float_rz((uint32_t)(bm.kspan >> sh)) + 1.0f);
+    const float scale = (float)FR_NBIN / (__uint2float_rz((uint32_t)(kspan >> sh)) + 1.0f);
     unsigned long long kw0[FR_VT];
     uint32_t kts[FR_VT], kaddr[FR_VT], kbin[FR_VT];
 #pragma unroll
     for (int v = 0; v < FR_VT; ++v) {
-        const uint32_t j = (uint32_t)tid + (uint32_t)v * FR_THREADS;
+        const uint32_t j = (uint32_t)tid + (uint32_t)v * FR_CONSUMERS;
         kw0[v] = 0; kts[v] = 0; kaddr[v] = 0; kbin[v] = 0;
         if (j < total) {
             int lo = 0, hi = k - 1;  // run owning slot j: last r with soff[r] <= j
             while (lo < hi) {
                 const int mid = (lo + hi + 1) >> 1;
-                if (sm.soff[mid] <= j) lo = mid; else hi = mid - 1;
+                if (mt.soff[mid] <= j) lo = mid; else hi = mid - 1;
             }
-            const uint32_t addr = sm.sbase[lo] + (j - sm.soff[lo]) * (uint32_t)stride;
-            const uint8_t* kp = sm.rec + addr + key_off;
+            const uint32_t addr = mt.sbase[lo] + (j - mt.soff[lo]) * (uint32_t)stride;
+            const uint8_t* kp = rec + addr + key_off;
             unsigned long long w0 = 0;
             uint32_t t = 0;
             if (ALIGN2 && key_len == 10) {
                 const uint16_t* h = reinterpret_cast<const uint16_t*>(kp);
                 const uint32_t h0 = h[0], h1 = h[1], h2 = h[2], h3 = h[3], h4 = h[4];
                 // bytes are big-endian key digits; each little-endian half holds (b0 | b1 << 8)
-                auto sw = [](uint32_t x) { return ((x & 0xFFu) << 8) | (x >> 8); };
-                w0 = ((unsigned long long)sw(h0) << 48) | ((unsigned long long)sw(h1) << 32) | ((unsigned long long)sw(h2) << 16) | sw(h3);
-                t = sw(h4);
+                w0 = ((unsigned long long)__byte_perm(h0, h1, 0x0145) << 32) | __byte_perm(h2, h3, 0x0145);
+                t = __byte_perm(h4, 0, 0x4401);
             } else {
                 key_prefix(kp, key_len, &w0, &t);
             }
-            unsigned long long rel = w0 > bm.klo ? w0 - bm.klo : 0ull;
-            if (rel > bm.kspan) rel = bm.kspan;
+            unsigned long long rel = w0 > klo ? w0 - klo : 0ull;
+            if (rel > kspan) rel = kspan;
             uint32_t b = __float2uint_rz(__uint2float_rz((uint32_t)(rel >> sh)) * scale);   // monotone in the key
             b = b < (uint32_t)FR_NBIN - 1u ? b : (uint32_t)FR_NBIN - 1u;
             const uint32_t o = atomicAdd(&sm.bincnt[b], 1u);
             kw0[v] = w0; kts[v] = (t << 16) | j; kaddr[v] = addr; kbin[v] = b | (o << 16);
         }
     }
-    __syncthreads();
+    fr_cbar();
+    if (release != nullptr && tid == 0) {   // everybody is out of the previous tile: its record buffer may be refilled
+        fence_proxy_async_smem();
+        mbar_arrive(release);
+    }
 
-    // ---- B: exclusive scan of the bin counts (two bins per thread); the counters go back to zero for the next tile
+    // ---- B: exclusive scan of the bin counts (four bins per thread); the counters go back to zero for the next tile
     {
-        const uint2 c = *reinterpret_cast<const uint2*>(&sm.bincnt[2 * tid]);
-        *reinterpret_cast<uint2*>(&sm.bincnt[2 * tid]) = make_uint2(0u, 0u);
-        const uint32_t s2 = c.x + c.y;
-        uint32_t x = s2;
+        const uint4 c = *reinterpret_cast<const uint4*>(&sm.bincnt[4 * tid]);
+        *reinterpret_cast<uint4*>(&sm.bincnt[4 * tid]) = make_uint4(0u, 0u, 0u, 0u);
+        const uint32_t s4 = c.x + c.y + c.z + c.w;
+        uint32_t x = s4;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
             if (lane >= o) x += y;
         }
         if (lane == 31) s_ws[warp] = x;
-        if ((c.x > (uint32_t)FR_BIN_LIMIT) | (c.y > (uint32_t)FR_BIN_LIMIT)) *s_flag = 1u;
-        __syncthreads();
-        uint32_t wp = lane < warp ? s_ws[lane] : 0u;   // FR_THREADS / 32 <= 32 warps
+        const uint32_t mx = max(max(c.x, c.y), max(c.z, c.w));
+        if (mx > (uint32_t)FR_BIN_LIMIT) *s_flag = 1u;
+        fr_cbar();
+        uint32_t wp = lane < warp ? s_ws[lane] : 0u;   // FR_CONSUMERS / 32 <= 32 warps
 #pragma unroll
         for (int o = 16; o; o >>= 1) wp += __shfl_xor_sync(0xffffffffu, wp, o);
-        const uint32_t e = wp + x - s2;
-        sm.binbase[2 * tid] = e;
-        sm.binbase[2 * tid + 1] = e + c.x;
-        if (tid == FR_THREADS - 1) sm.binbase[FR_NBIN] = e + s2;
+        const uint32_t e = wp + x - s4;
+        *reinterpret_cast<uint4*>(&sm.binbase[4 * tid]) = make_uint4(e, e + c.x, e + c.x + c.y, e + c.x + c.y + c.z);
+        if (tid == FR_CONSUMERS - 1) sm.binbase[FR_NBIN] = e + s4;
     }
-    __syncthreads();
+    fr_cbar();
 
     if (*s_flag == 0u) {
         // ---- C: a record alone in its bin knows its output position; the others are staged by bin
         uint32_t b0[FR_VT], cn[FR_VT];
 #pragma unroll
         for (int v = 0; v < FR_VT; ++v) {
-            const uint32_t j = (uint32_t)tid + (uint32_t)v * FR_THREADS;
+            const uint32_t j = (uint32_t)tid + (uint32_t)v * FR_CONSUMERS;
             b0[v] = 0; cn[v] = 0;
             if (j < total) {
                 const uint32_t b = kbin[v] & 0xFFFFu, o = kbin[v] >> 16;
@@ -433,7 +479,7 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
                 else { sm.skey[b0[v] + o] = kw0[v]; sm.sts[b0[v] + o] = kts[v]; }
             }
         }
-        __syncthreads();
+        fr_cbar();
         // ---- D: exact rank among the records of the same bin on (key, tail, slot); slots are run-major, so equal
         //         keys come out in (run, index) order
 #pragma unroll
@@ -448,15 +494,15 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
                 sm.srcaddr[b0[v] + rank] = kaddr[v];
             }
         }
-        __syncthreads();
+        fr_cbar();
     } else {
         // ---- fallback: many records share a key bin (duplicate-heavy keys). Pairwise merge-path tree over 16-byte
         //      entries, one block-wide level per log2 k.
         if (tid == 0) atomicAdd(&prm->tree_tiles, 1ull);
-        __syncthreads();               // nobody reads binbase / bincnt any more: the work area becomes entA | entB | slotaddr
+        fr_cbar();               // nobody reads binbase / bincnt any more: the work area becomes entA | entB | slotaddr
 #pragma unroll
         for (int v = 0; v < FR_VT; ++v) {
-            const uint32_t j = (uint32_t)tid + (uint32_t)v * FR_THREADS;
+            const uint32_t j = (uint32_t)tid + (uint32_t)v * FR_CONSUMERS;
             if (j < total) {
                 Entry e;
                 e.w0 = kw0[v];
@@ -465,27 +511,29 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
                 sm.slotaddr[j] = kaddr[v];
             }
         }
-        __syncthreads();
+        fr_cbar();
         Entry* src = sm.entA; Entry* dst = sm.entB;
-        uint32_t* soff = sm.soff; uint32_t* doff = sm.doff;
+        uint32_t* soff = mt.soff; uint32_t* doff = sm.doff;
         int L = k;
         while (L > 1) {
             if (tid < FR_MERGE_THREADS) merge_level<FR_MERGE_THREADS, FR_MERGE_VT>(src, soff, L, dst, doff, total);
-            __syncthreads();
+            fr_cbar();
             Entry* te = src; src = dst; dst = te;
             uint32_t* tu = soff; soff = doff; doff = tu;
             L = (L + 1) >> 1;
         }
-        for (uint32_t p = tid; p < total; p += FR_THREADS) sm.srcaddr[p] = sm.slotaddr[(uint32_t)src[p].w1 & 0xFFFFu];
-        __syncthreads();
-        for (int b = tid; b < FR_NBIN; b += FR_THREADS) sm.bincnt[b] = 0u;   // restore the invariant the bin path relies on
+        for (uint32_t p = tid; p < total; p += FR_CONSUMERS) sm.srcaddr[p] = sm.slotaddr[(uint32_t)src[p].w1 & 0xFFFFu];
+        fr_cbar();
+        for (int b = tid; b < FR_NBIN; b += FR_CONSUMERS) sm.bincnt[b] = 0u;   // restore the invariant the bin path relies on
+        fr_cbar();
     }
 
-    // ---- E: records leave in merged order. One thread per 16-byte *destination* word (all 32 lanes busy, the
-    // per-record work is amortised over the lanes): the word's bytes come from at most two staged records at
-    // arbitrary (even) shared-memory offsets, each fetched as aligned 32-bit shared loads + funnel shifts.
+    // ---- E: records leave in merged order, one thread per 16-byte *destination* word (all 32 lanes busy, fully coalesced
+    // stores). Words that lie inside one record are a single unaligned 16-byte read of shared memory (aligned 32-bit loads +
+    // funnel shifts); the one word per record boundary that takes bytes from two records is handled in a second, dense
+    // loop over the boundaries, so the two-source path is not paid by every warp of the first loop.
     // Shared-space addresses are explicit so the loads are LDS, not generic LD.
-    const uint32_t rec_s = smem_u32(sm.rec), sa_s = smem_u32(sm.srcaddr);
+    const uint32_t rec_s = smem_u32(rec), sa_s = smem_u32(sm.srcaddr);
     auto slot_addr = [&](uint32_t p) -> uint32_t {  // shared address of merged record p
         uint32_t sa;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sa) : "r"(sa_s + p * 4u));
@@ -507,30 +555,41 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
     const uint32_t span = total * (uint32_t)stride;
     const uint32_t head = (uint32_t)((16u - ((uintptr_t)out & 15u)) & 15u) < span ? (uint32_t)((16u - ((uintptr_t)out & 15u)) & 15u) : span;
     const uint32_t nfull = (span - head) >> 4;
-    auto emit16 = [&](uint32_t w) {
+#pragma unroll 2
+    for (uint32_t w = tid; w < nfull; w += FR_CONSUMERS) {
         const uint32_t rel = head + (w << 4);
         const uint32_t p = rel / (uint32_t)stride;
         const uint32_t o = rel - p * (uint32_t)stride;
-        const uint32_t len0 = (uint32_t)stride - o < 16u ? (uint32_t)stride - o : 16u;
-        uint4 v = lds16(slot_addr(p) + o);
-        if (len0 < 16u) {  // the word straddles two records (stride >= 16: never three)
-            const uint4 u = lds16(slot_addr(p + 1) - len0);
-            // byte k of the word comes from v for k < len0, from u otherwise: one 128-bit mask, 4 LOP3 selects
-            const unsigned long long mlo = len0 >= 8u ? ~0ull : ((1ull << (8u * len0)) - 1ull);
-            const unsigned long long mhi = len0 <= 8u ? 0ull : ((1ull << (8u * (len0 - 8u))) - 1ull);
-            const uint32_t m0 = (uint32_t)mlo, m1 = (uint32_t)(mlo >> 32), m2 = (uint32_t)mhi, m3 = (uint32_t)(mhi >> 32);
-            v.x = (v.x & m0) | (u.x & ~m0); v.y = (v.y & m1) | (u.y & ~m1);
-            v.z = (v.z & m2) | (u.z & ~m2); v.w = (v.w & m3) | (u.w & ~m3);
+        if (o + 16u <= (uint32_t)stride) {   // the word lies inside record p
+            const uint4 v = lds16(slot_addr(p) + o);
+            st_stream(reinterpret_cast<int4*>(out + rel), make_int4((int)v.x, (int)v.y, (int)v.z, (int)v.w));
         }
-        st_stream(reinterpret_cast<int4*>(out + rel), make_int4((int)v.x, (int)v.y, (int)v.z, (int)v.w));
-    };
-#pragma unroll 2
-    for (uint32_t w = tid; w < nfull; w += FR_THREADS) emit16(w);
+    }
+    // the word around the boundary between records i-1 and i (stride >= 16: a word never spans three records)
+    for (uint32_t i = (uint32_t)tid + 1u; i < total; i += FR_CONSUMERS) {
+        const uint32_t rel_b = i * (uint32_t)stride;
+        if (rel_b <= head) continue;                 // inside the unaligned head bytes (byte loop below)
+        const uint32_t d = rel_b - head;
+        if ((d & 15u) == 0u) continue;               // the boundary coincides with a word boundary
+        const uint32_t wrel = head + (d & ~15u);
+        if (wrel + 16u > head + (nfull << 4)) continue;   // inside the unaligned tail bytes
+        const uint32_t len0 = rel_b - wrel;          // bytes of record i-1 in this word (1..15)
+        uint4 v = lds16(slot_addr(i - 1u) + (uint32_t)stride - len0);
+        const uint4 u = lds16(slot_addr(i) - len0);
+        auto msk = [&](int wi) -> uint32_t {         // bytes of 32-bit word wi that still belong to record i-1
+            const int rem = (int)len0 - 4 * wi;
+            return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : (0xFFFFFFFFu >> (32 - 8 * rem)));
+        };
+        const uint32_t m0 = msk(0), m1 = msk(1), m2 = msk(2), m3 = msk(3);
+        v.x = (v.x & m0) | (u.x & ~m0); v.y = (v.y & m1) | (u.y & ~m1);
+        v.z = (v.z & m2) | (u.z & ~m2); v.w = (v.w & m3) | (u.w & ~m3);
+        st_stream(reinterpret_cast<int4*>(out + wrel), make_int4((int)v.x, (int)v.y, (int)v.z, (int)v.w));
+    }
     // unaligned head and tail bytes of the tile's span (< 16 bytes each)
     {
         const uint32_t tail0 = head + (nfull << 4);
         const uint32_t nedge = head + (span - tail0);
-        for (uint32_t e = tid; e < nedge; e += FR_THREADS) {
+        for (uint32_t e = tid; e < nedge; e += FR_CONSUMERS) {
             const uint32_t rel = e < head ? e : tail0 + (e - head);
             const uint32_t p = rel / (uint32_t)stride, o = rel - p * (uint32_t)stride;
             uint32_t v;
@@ -538,22 +597,24 @@ __device__ __forceinline__ void fr_process_tile(const UdaRunDesc* __restrict__ r
             out[rel] = (uint8_t)v;
         }
     }
-    __syncthreads();  // buffers are reused by the next tile
 }
 
 template <bool ALIGN2, int STRIDE>
-__global__ void __launch_bounds__(FR_THREADS, UDA_FR_CTAS)
+__global__ void __launch_bounds__(FR_THREADS_ALL, UDA_FR_CTAS)
 fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int stride_rt, int key_off, int key_len, int force_tree,
                 const uint32_t* __restrict__ P, const uint32_t* __restrict__ outoff, const unsigned long long* __restrict__ bkey,
                 const uint8_t* __restrict__ kind, FrParams* __restrict__ prm, uint8_t* __restrict__ out) {
     const int stride = STRIDE > 0 ? STRIDE : stride_rt;
     extern __shared__ __align__(128) uint8_t fr_smem_raw[];
-    __shared__ __align__(8) uint64_t mbar;
+    __shared__ __align__(8) uint64_t bar_full[2], bar_empty[2], bar_own;
     __shared__ uint32_t s_cnt, s_flag;
     __shared__ uint32_t s_ws[32];
     FrSmem sm;
-    sm.rec = fr_smem_raw;
-    uint8_t* work = fr_smem_raw + fr_rec_bytes(cap, k, stride);
+    const size_t rec_bytes = fr_rec_bytes(cap, k, stride);
+    sm.rec0 = fr_smem_raw;
+    sm.rec_bytes = (uint32_t)rec_bytes;
+    sm.k = k;
+    uint8_t* work = fr_smem_raw + 2 * rec_bytes;
     sm.entA = reinterpret_cast<Entry*>(work);
     sm.entB = sm.entA + cap;
     sm.slotaddr = reinterpret_cast<uint32_t*>(sm.entB + cap);
@@ -562,55 +623,100 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
     sm.bincnt = sm.sts + cap;
     sm.binbase = sm.bincnt + FR_NBIN;
     sm.srcaddr = reinterpret_cast<uint32_t*>(work + fr_work_bytes(cap));
-    sm.lo = sm.srcaddr + cap;
-    sm.hi = sm.lo + k;
-    sm.bend = sm.hi + k;
-    sm.sbase = sm.bend + k;
-    sm.soff = sm.sbase + k;
-    sm.doff = sm.soff + (k + 1);
-    if (threadIdx.x == 0) { mbar_init(&mbar, 1); mbar_fence_init(); }
-    for (int b = threadIdx.x; b < FR_NBIN; b += FR_THREADS) sm.bincnt[b] = 0u;
-    __syncthreads();
-    uint32_t phase = 0;
-    const unsigned long long gmin = prm->kmin, gmax = prm->kmax;
+    uint8_t* mp = reinterpret_cast<uint8_t*>(sm.srcaddr + cap);
+    mp += (8 - ((uintptr_t)mp & 7)) & 7;
+    sm.meta0 = mp;
+    sm.meta_bytes = (uint32_t)fr_meta_bytes(k);
+    mp += 2 * fr_meta_bytes(k);
+    sm.hi = reinterpret_cast<uint32_t*>(mp);
+    sm.doff = sm.hi + k;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar_full[0], 1); mbar_init(&bar_full[1], 1);
+        mbar_init(&bar_empty[0], 1); mbar_init(&bar_empty[1], 1);
+        mbar_init(&bar_own, 1);
+        mbar_fence_init();
+    }
+    for (int b = threadIdx.x; b < FR_NBIN; b += FR_THREADS_ALL) sm.bincnt[b] = 0u;
+    __syncthreads();   // the only block-wide barrier: from here on the two roles run on their own
+    const int lane = threadIdx.x & 31;
 
-    // Buckets are handed out through a counter, not by blockIdx stride: when part of the SMs is held by a
-    // concurrently running push kernel, the CTAs that do get an SM still share the work evenly.
-    __shared__ int s_q;
-    for (;;) {
-        if (threadIdx.x == 0) s_q = (int)atomicAdd(&prm->next_bucket, 1u);
-        __syncthreads();
-        const int q = s_q;
-        __syncthreads();
-        if (q >= G) break;
-        const uint32_t obase = outoff[q];
-        const uint32_t total = outoff[q + 1] - obase;
-        if (total == 0) continue;
-        for (int r = threadIdx.x; r < k; r += FR_THREADS) {
-            sm.lo[r] = P[(long long)q * k + r];
-            sm.bend[r] = P[(long long)(q + 1) * k + r];
-            sm.hi[r] = sm.bend[r];
+    if (threadIdx.x >= FR_CONSUMERS) {
+        // =============================================================== producer warp
+        // Buckets are handed out through a counter, not by blockIdx stride: when part of the SMs is held by a
+        // concurrently running push kernel, the CTAs that do get an SM still share the work evenly.
+        const unsigned long long gmin = prm->kmin, gmax = prm->kmax;
+        for (uint32_t it = 0;; ++it) {
+            int q = 0;
+            uint32_t obase = 0, total = 0;
+            for (;;) {   // next non-empty bucket
+                if (lane == 0) q = (int)atomicAdd(&prm->next_bucket, 1u);
+                q = __shfl_sync(0xffffffffu, q, 0);
+                if (q >= G) break;
+                obase = outoff[q];
+                total = outoff[q + 1] - obase;
+                if (total) break;
+            }
+            const uint32_t b = it & 1u;
+            if (it >= 2) mbar_wait(&bar_empty[b], ((it >> 1) & 1u) ^ 1u);   // the consumers have left this buffer's previous tile
+            const FrMeta mt = sm.meta(b);
+            if (q >= G) {
+                if (lane == 0) { mt.hdr->total = FR_META_DONE; mbar_arrive(&bar_full[b]); }
+                break;
+            }
+            for (int r = lane; r < k; r += 32) {
+                mt.lo[r] = P[(long long)q * k + r];
+                mt.bend[r] = P[(long long)(q + 1) * k + r];
+            }
+            if (lane == 0) {   // the bucket's key range: [first key of the bucket, last key before the next bucket]
+                const unsigned long long klo = kind[q] == 1 ? bkey[q] : gmin;
+                const unsigned long long khi = kind[q + 1] == 1 ? bkey[q + 1] - 1ull : gmax;
+                mt.hdr->klo = klo;
+                mt.hdr->kspan = khi > klo ? khi - klo : 0ull;
+                mt.hdr->total = total;
+                mt.hdr->obase = obase;
+                mt.hdr->big = total > (uint32_t)cap ? 1u : 0u;
+            }
+            __syncwarp();
+            if (total > (uint32_t)cap) {
+                if (lane == 0) mbar_arrive(&bar_full[b]);   // the consumers split and stage an oversize bucket themselves
+            } else {
+                fr_stage(runs, k, stride, mt.lo, mt.bend, sm.rec(b), mt.sbase, mt.soff, total, &bar_full[b]);
+            }
         }
-        FrBinMap bm;   // the bucket's key range: [first key of the bucket, last key before the next bucket]
-        bm.klo = kind[q] == 1 ? bkey[q] : gmin;
-        const unsigned long long khi = kind[q + 1] == 1 ? bkey[q + 1] - 1ull : gmax;
-        bm.kspan = khi > bm.klo ? khi - bm.klo : 0ull;
-        __syncthreads();
-        if (total <= (uint32_t)cap) {
-            fr_process_tile<ALIGN2, STRIDE>(runs, sm, k, stride, key_off, key_len, total, bm, force_tree,
-                                            out + (unsigned long long)obase * stride, &mbar, phase, s_ws, &s_flag, prm);
+        return;
+    }
+
+    // =================================================================== consumer warps
+    uint32_t own_phase = 0;
+    for (uint32_t it = 0;; ++it) {
+        const uint32_t b = it & 1u;
+        mbar_wait(&bar_full[b], (it >> 1) & 1u);     // acquire: tables and records of this tile are visible
+        const FrMeta mt = sm.meta(b);
+        const uint32_t total = mt.hdr->total;
+        if (total == FR_META_DONE) break;
+        const uint32_t obase = mt.hdr->obase;
+        const unsigned long long klo = mt.hdr->klo, kspan = mt.hdr->kspan;
+        uint64_t* release = it > 0 ? &bar_empty[b ^ 1u] : nullptr;
+        if (!mt.hdr->big) {
+            fr_order_emit<ALIGN2, STRIDE>(sm, sm.rec(b), mt, k, stride, key_off, key_len, total, klo, kspan, force_tree,
+                                          out + (unsigned long long)obase * stride, release, s_ws, &s_flag, prm);
             continue;
         }
-        // ---- oversize bucket: split by bisection over the 128-bit value (key80 | run | index)
-        if (threadIdx.x == 0) atomicAdd(&prm->fallback_buckets, 1ull);
+        // ---- oversize bucket: split by bisection over the 128-bit value (key80 | run | index); every piece is staged by
+        //      consumer warp 0 into this buffer and ordered like a regular tile
+        fr_cbar();
+        if (threadIdx.x == 0) {
+            if (release != nullptr) { fence_proxy_async_smem(); mbar_arrive(release); }
+            atomicAdd(&prm->fallback_buckets, 1ull);
+        }
         uint32_t remaining = total, done = 0;
         unsigned __int128 vlo = 0;
         while (remaining > 0) {
             uint32_t cnt;
             if (remaining <= (uint32_t)cap) {
-                for (int r = threadIdx.x; r < k; r += FR_THREADS) sm.hi[r] = sm.bend[r];
+                for (int r = threadIdx.x; r < k; r += FR_CONSUMERS) sm.hi[r] = mt.bend[r];
                 cnt = remaining;
-                __syncthreads();
+                fr_cbar();
             } else {
                 unsigned __int128 lo128 = vlo, hi128 = ~(unsigned __int128)0, best = vlo;
                 uint32_t bestc = 0;
@@ -619,10 +725,10 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
                     const unsigned long long v0 = (unsigned long long)(v >> 64), v1 = (unsigned long long)v;
                     const uint32_t t = (uint32_t)(v1 >> 48), vrun = (uint32_t)(v1 >> 32) & 0xFFFFu, vidx = (uint32_t)v1;
                     const uint8_t* base = (const uint8_t*)runs[r].base;
-                    uint32_t lb = lb_records(base, stride, key_off, key_len, sm.lo[r], sm.bend[r], v0, t);
+                    uint32_t lb = lb_records(base, stride, key_off, key_len, mt.lo[r], mt.bend[r], v0, t);
                     const uint32_t rid = (uint32_t)r;  // slots are laid out run-major, so the run *index* is the tie-break rank
                     if (rid > vrun) return lb;
-                    uint32_t ub = ub_records(base, stride, key_off, key_len, lb, sm.bend[r], v0, t);
+                    uint32_t ub = ub_records(base, stride, key_off, key_len, lb, mt.bend[r], v0, t);
                     if (rid < vrun) return ub;
                     uint32_t x = vidx < lb ? lb : (vidx > ub ? ub : vidx);
                     return x;
@@ -630,13 +736,13 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
                 while (hi128 - lo128 > 1) {
                     unsigned __int128 mid = lo128 + ((hi128 - lo128) >> 1);
                     uint32_t c = 0;
-                    for (int r = threadIdx.x; r < k; r += FR_THREADS) c += split_pos(r, mid) - sm.lo[r];
+                    for (int r = threadIdx.x; r < k; r += FR_CONSUMERS) c += split_pos(r, mid) - mt.lo[r];
                     for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-                    __syncthreads();
+                    fr_cbar();
                     if (threadIdx.x == 0) s_cnt = 0;
-                    __syncthreads();
+                    fr_cbar();
                     if ((threadIdx.x & 31) == 0) atomicAdd(&s_cnt, c);
-                    __syncthreads();
+                    fr_cbar();
                     c = s_cnt;
                     ++iters;
                     if (c > (uint32_t)cap) hi128 = mid;
@@ -646,17 +752,23 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
                     }
                 }
                 if (threadIdx.x == 0) atomicAdd(&prm->fallback_iters, (unsigned long long)iters);
-                for (int r = threadIdx.x; r < k; r += FR_THREADS) sm.hi[r] = split_pos(r, best);
+                for (int r = threadIdx.x; r < k; r += FR_CONSUMERS) sm.hi[r] = split_pos(r, best);
                 cnt = bestc;
                 vlo = best;
-                __syncthreads();
+                fr_cbar();
             }
-            if (cnt) fr_process_tile<ALIGN2, STRIDE>(runs, sm, k, stride, key_off, key_len, cnt, bm, force_tree,
-                                                     out + (unsigned long long)(obase + done) * stride, &mbar, phase, s_ws, &s_flag, prm);
+            if (cnt) {
+                if (threadIdx.x < 32) fr_stage(runs, k, stride, mt.lo, sm.hi, sm.rec(b), mt.sbase, mt.soff, cnt, &bar_own);
+                mbar_wait(&bar_own, own_phase);
+                own_phase ^= 1u;
+                fr_order_emit<ALIGN2, STRIDE>(sm, sm.rec(b), mt, k, stride, key_off, key_len, cnt, klo, kspan, force_tree,
+                                              out + (unsigned long long)(obase + done) * stride, nullptr, s_ws, &s_flag, prm);
+            }
+            fr_cbar();   // the piece has left the record buffer and the tables
             done += cnt;
             remaining -= cnt;
-            for (int r = threadIdx.x; r < k; r += FR_THREADS) sm.lo[r] = sm.hi[r];
-            __syncthreads();
+            for (int r = threadIdx.x; r < k; r += FR_CONSUMERS) mt.lo[r] = sm.hi[r];
+            fr_cbar();
         }
     }
 }
@@ -801,12 +913,12 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
             // remembering it per process, which breaks the second device of a multi-GPU process
             UDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int per_sm = 0;
-            UDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FR_THREADS, smem));
+            UDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FR_THREADS_ALL, smem));
             if (per_sm < 1) return UDA_E_TOO_LARGE;
             if (ctas_per_sm > 0 && per_sm > ctas_per_sm) per_sm = ctas_per_sm;
             int grid = kNumSMs * per_sm;
             if (grid > G) grid = G;
-            kern<<<grid, FR_THREADS, smem, stream>>>(runs_dev, nruns, G, cap, stride, key_off, key_len, fr_env().force_tree, s.P, s.sizes,
+            kern<<<grid, FR_THREADS_ALL, smem, stream>>>(runs_dev, nruns, G, cap, stride, key_off, key_len, fr_env().force_tree, s.P, s.sizes,
                                                      s.bkey, s.kind, s.prm, o);
         }
     }

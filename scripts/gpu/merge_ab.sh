@@ -17,11 +17,13 @@ except Exception as e:
     print(sys.argv[2], "no result", e)
 PY
 }
-C4=uda_b200/lib/libuda_kernels_c4.so
+C3=uda_b200/lib/libuda_kernels_c3.so
 for k in 8 64; do
-  run bins_c3_k$k UDA_X=1 -- --maps-per-gpu $k
-  run tree_c3_k$k UDA_FR_FORCE_TREE=1 -- --maps-per-gpu $k
-  [ -f $C4 ] && run bins_c4_k$k UDA_B200_KERNELS_LIB=$C4 UDA_FR_WANT_CTAS=4 -- --maps-per-gpu $k
+  run bins_c2_k$k UDA_X=1 -- --maps-per-gpu $k
+  [ -f $C3 ] && run bins_c3_k$k UDA_B200_KERNELS_LIB=$C3 -- --maps-per-gpu $k
 done
-run bins_c3_k16 UDA_X=1 -- --maps-per-gpu 16
-run bins_c3_k32 UDA_X=1 -- --maps-per-gpu 32
+run tree_c2_k8 UDA_FR_FORCE_TREE=1 -- --maps-per-gpu 8
+run bins_c2_k16 UDA_X=1 -- --maps-per-gpu 16
+run bins_c2_k32 UDA_X=1 -- --maps-per-gpu 32
+run bins_c2_cap384_k8 UDA_FR_CAP=384 -- --maps-per-gpu 8
+run bins_c2_cap512_k8 UDA_FR_CAP=512 -- --maps-per-gpu 8
