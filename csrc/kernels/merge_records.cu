@@ -197,54 +197,57 @@ __global__ void fr_partition_search_kernel(const UdaRunDesc* __restrict__ runs, 
     }
 }
 
-// Exact split position of every bucket boundary in every run: the k-way merge-path partition.
-//
-// A boundary is a bin edge, so "first record of run r in bucket >= q" can be read off a single pass over
-// the run's keys: record i lies in bucket b_i = cum[bin(key_i)] / (TARGET/SAMPLE) (O(1), the prefix array is
-// L2 resident), b_i is non-decreasing in i, and P[q][r] = i for every q in (b_{i-1}, b_i]. One coalesced,
-// sector-sparse pass (2 ms for 125 M records) replaces (G+1)*k independent binary searches over strided
-// records, which for k = 64 dragged the whole data set through DRAM at 2 TB/s (6.3 ms). Runs that are much
-// shorter than the bucket count keep the per-boundary binary search (their gaps would serialise one thread).
-__global__ void fr_partition_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int per_i, int stride, int key_off, int key_len,
-                                    const uint32_t* __restrict__ cum, const FrParams* __restrict__ prm,
-                                    const unsigned long long* __restrict__ bkey, const uint8_t* __restrict__ kind,
-                                    uint32_t* __restrict__ P) {
-    const int r = blockIdx.y;
-    const UdaRunDesc rd = runs[r];
-    const uint8_t* base = (const uint8_t*)rd.base;
-    const long long n = rd.nrec;
-    const long long nthreads = (long long)gridDim.x * blockDim.x;
-    const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (n * 4 < (long long)G) {  // short run: one binary search per boundary
-        for (long long q = t0; q <= G; q += nthreads) {
+// The k-way merge-path partition for many runs (k > 16), as a walk instead of a search per boundary: bucket boundaries and a run's keys are
+// both sorted, so one thread takes FR_PCHUNK consecutive boundaries of one run, finds the first by binary search and every
+// following one by scanning forward from the previous position (a few records apart on average; gaps are bounded by an
+// exponential probe + binary search). Every key is read about once. (Round 1 used one streaming pass over all keys with a
+// prefix-table look-up per record: 2.4 ms for 125 M records at k = 64; per-boundary binary searches took 5.5 ms.)
+constexpr int FR_PCHUNK = 32;
+__global__ void fr_partition_walk_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride, int key_off, int key_len,
+                                         const unsigned long long* __restrict__ bkey, const uint8_t* __restrict__ kind,
+                                         uint32_t* __restrict__ P) {
+    const long long nchunk = ((long long)G + 1 + FR_PCHUNK - 1) / FR_PCHUNK;
+    const long long total = nchunk * k;
+    for (long long x = (long long)blockIdx.x * blockDim.x + threadIdx.x; x < total; x += (long long)gridDim.x * blockDim.x) {
+        const int r = (int)(x % k);                 // consecutive threads: consecutive runs of the same boundaries (coalesced P stores)
+        const long long c = x / k;
+        const UdaRunDesc rd = runs[r];
+        const uint8_t* base = (const uint8_t*)rd.base;
+        const uint32_t n = (uint32_t)rd.nrec;
+        const int q0 = (int)(c * FR_PCHUNK);
+        const int q1 = min(G, q0 + FR_PCHUNK - 1);
+        uint32_t pos = 0;
+        bool have = false;                           // pos is a valid lower bound for the next boundary
+        for (int q = q0; q <= q1; ++q) {
             const uint8_t kd = kind[q];
-            uint32_t pos = kd == 0 ? 0u : (uint32_t)n;
-            if (kd == 1) pos = lb_records(base, stride, key_off, key_len, 0u, (uint32_t)n, bkey[q], 0u);
-            P[q * k + r] = pos;
-        }
-        return;
-    }
-    const unsigned long long kmin = prm->kmin;
-    const int shift = prm->shift;
-    const uint32_t per = (uint32_t)per_i;
-    auto bucket_of = [&](long long i) -> int {
-        unsigned long long w0;
-        uint32_t t;
-        load_key80(base + i * stride + key_off, key_len, &w0, &t);
-        const uint32_t bq = __ldg(&cum[(w0 - kmin) >> shift]) / per;
-        return (int)(bq < (uint32_t)(G - 1) ? bq : (uint32_t)(G - 1));
-    };
-    const int lane = threadIdx.x & 31;
-    for (long long wi = t0 - lane; wi < n; wi += nthreads) {  // warp-uniform trip count: the shuffle needs every lane
-        const long long i = wi + lane;
-        const bool valid = i < n;
-        const int bi = valid ? bucket_of(i) : G;
-        int bp = __shfl_up_sync(0xffffffffu, bi, 1);
-        if (lane == 0) bp = wi > 0 ? bucket_of(wi - 1) : -1;
-        if (valid) {
-            for (int q = bp + 1; q <= bi; ++q) P[(long long)q * k + r] = (uint32_t)i;
-            if (i == n - 1)
-                for (int q = bi + 1; q <= G; ++q) P[(long long)q * k + r] = (uint32_t)n;
+            uint32_t p;
+            if (kd == 0) p = 0u;
+            else if (kd == 2) p = n;
+            else {
+                const unsigned long long target = bkey[q];
+                auto below = [&](uint32_t i) -> bool {   // key of record i < (target, tail 0)
+                    unsigned long long w0;
+                    uint32_t t;
+                    load_key80(base + (unsigned long long)i * stride + key_off, key_len, &w0, &t);
+                    return w0 < target;
+                };
+                if (!have) {
+                    p = lb_records(base, stride, key_off, key_len, 0u, n, target, 0u);
+                } else {
+                    p = pos;
+                    int lin = 0;
+                    while (p < n && lin < 6 && below(p)) { ++p; ++lin; }
+                    if (p < n && lin == 6 && below(p)) {   // a long gap: exponential probe, then binary search
+                        uint32_t lo = p + 1u, step = 8u;
+                        while (lo + step <= n && below(lo + step - 1u)) { lo += step; step <<= 1; }
+                        const uint32_t hi = lo + step - 1u < n ? lo + step - 1u : n;
+                        p = lb_records(base, stride, key_off, key_len, lo, hi, target, 0u);
+                    }
+                }
+                pos = p;
+                have = true;
+            }
+            P[(long long)q * k + r] = p;
         }
     }
 }
@@ -278,7 +281,7 @@ __global__ void fr_sizes_kernel(const uint32_t* __restrict__ P, int k, int G, ui
 //   work  (cap * 36 bytes)   bin ordering: skey[cap] u64 | sts[cap] u32 | bincnt[NBIN] | binbase[NBIN + 4]
 //                            tree ordering (fallback): entA[cap] | entB[cap] | slotaddr[cap]      (same bytes)
 //   srcaddr[cap]             byte offset inside rec of the record that goes to output position p
-//   meta x 2                 per buffer: header, sbase[k], soff[k + 1], lo[k], bend[k]
+//   meta x 3                 per tile in flight: header, sbase[k], soff[k + 1], lo[k], bend[k]
 //   hi[k], doff[k + 1]       oversize-bucket / merge-tree scratch (consumers only)
 constexpr int FR_CONSUMERS = FR_THREADS;            // threads that order and emit a tile
 constexpr int FR_THREADS_ALL = FR_CONSUMERS + 32;   // + the producer warp
@@ -300,7 +303,7 @@ struct FrMeta {
 };
 struct FrSmem {
     uint8_t* rec0;       // two record buffers, rec_bytes apart
-    uint8_t* meta0;      // two metadata blocks, meta_bytes apart
+    uint8_t* meta0;      // three metadata blocks, meta_bytes apart
     uint32_t rec_bytes, meta_bytes;
     int k;
     __device__ __forceinline__ uint8_t* rec(uint32_t b) const { return rec0 + b * rec_bytes; }
@@ -335,7 +338,7 @@ __host__ __device__ inline size_t fr_work_bytes(int cap) {
 }
 __host__ __device__ inline size_t fr_meta_bytes(int k) { return sizeof(FrTileHdr) + ((size_t)4 * k + 1) * 4 + 4; }   // multiple of 8
 __host__ __device__ inline size_t fr_smem_bytes(int cap, int k, int stride) {
-    return 2 * fr_rec_bytes(cap, k, stride) + fr_work_bytes(cap) + (size_t)cap * 4 + 2 * fr_meta_bytes(k) + ((size_t)2 * k + 1) * 4 + 16;
+    return 2 * fr_rec_bytes(cap, k, stride) + fr_work_bytes(cap) + (size_t)cap * 4 + 3 * fr_meta_bytes(k) + ((size_t)2 * k + 1) * 4 + 16;
 }
 
 __device__ __forceinline__ void mbar_expect_tx_only(uint64_t* bar, uint32_t bytes) {
@@ -392,7 +395,7 @@ template <bool ALIGN2, int STRIDE>
 __device__ __forceinline__ void fr_order_emit(const FrSmem& sm, const uint8_t* rec, const FrMeta& mt, int k, int stride_rt, int key_off,
                                               int key_len, uint32_t total, unsigned long long klo, unsigned long long kspan,
                                               int force_tree, uint8_t* __restrict__ out, uint64_t* release, uint32_t* s_ws,
-                                              uint32_t* s_flag, FrParams* __restrict__ prm) {
+                                              uint32_t* s_flag, const uint4* s_mask, FrParams* __restrict__ prm) {
     const int stride = STRIDE > 0 ? STRIDE : stride_rt;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
@@ -533,7 +536,7 @@ __device__ __forceinline__ void fr_order_emit(const FrSmem& sm, const uint8_t* r
     // funnel shifts); the one word per record boundary that takes bytes from two records is handled in a second, dense
     // loop over the boundaries, so the two-source path is not paid by every warp of the first loop.
     // Shared-space addresses are explicit so the loads are LDS, not generic LD.
-    const uint32_t rec_s = smem_u32(rec), sa_s = smem_u32(sm.srcaddr);
+    const uint32_t rec_s = smem_u32(rec), sa_s = smem_u32(sm.srcaddr), mask_s = smem_u32(s_mask);
     auto slot_addr = [&](uint32_t p) -> uint32_t {  // shared address of merged record p
         uint32_t sa;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sa) : "r"(sa_s + p * 4u));
@@ -576,11 +579,10 @@ __device__ __forceinline__ void fr_order_emit(const FrSmem& sm, const uint8_t* r
         const uint32_t len0 = rel_b - wrel;          // bytes of record i-1 in this word (1..15)
         uint4 v = lds16(slot_addr(i - 1u) + (uint32_t)stride - len0);
         const uint4 u = lds16(slot_addr(i) - len0);
-        auto msk = [&](int wi) -> uint32_t {         // bytes of 32-bit word wi that still belong to record i-1
-            const int rem = (int)len0 - 4 * wi;
-            return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : (0xFFFFFFFFu >> (32 - 8 * rem)));
-        };
-        const uint32_t m0 = msk(0), m1 = msk(1), m2 = msk(2), m3 = msk(3);
+        // byte b of the word comes from record i-1 for b < len0: a 16-entry mask table in shared memory (one LDS.128) instead
+        // of per-word shift arithmetic, which was 12 % of the kernel's instructions
+        uint32_t m0, m1, m2, m3;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(m0), "=r"(m1), "=r"(m2), "=r"(m3) : "r"(mask_s + len0 * 16u));
         v.x = (v.x & m0) | (u.x & ~m0); v.y = (v.y & m1) | (u.y & ~m1);
         v.z = (v.z & m2) | (u.z & ~m2); v.w = (v.w & m3) | (u.w & ~m3);
         st_stream(reinterpret_cast<int4*>(out + wrel), make_int4((int)v.x, (int)v.y, (int)v.z, (int)v.w));
@@ -609,6 +611,12 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
     __shared__ __align__(8) uint64_t bar_full[2], bar_empty[2], bar_own;
     __shared__ uint32_t s_cnt, s_flag;
     __shared__ uint32_t s_ws[32];
+    __shared__ __align__(16) uint4 s_mask[16];   // s_mask[n]: the low n bytes of a 16-byte word set
+    if (threadIdx.x < 16) {
+        const int n = threadIdx.x;
+        auto w = [n](int wi) -> uint32_t { const int rem = n - 4 * wi; return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : (0xFFFFFFFFu >> (32 - 8 * rem))); };
+        s_mask[n] = make_uint4(w(0), w(1), w(2), w(3));
+    }
     FrSmem sm;
     const size_t rec_bytes = fr_rec_bytes(cap, k, stride);
     sm.rec0 = fr_smem_raw;
@@ -627,7 +635,7 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
     mp += (8 - ((uintptr_t)mp & 7)) & 7;
     sm.meta0 = mp;
     sm.meta_bytes = (uint32_t)fr_meta_bytes(k);
-    mp += 2 * fr_meta_bytes(k);
+    mp += 3 * fr_meta_bytes(k);
     sm.hi = reinterpret_cast<uint32_t*>(mp);
     sm.doff = sm.hi + k;
     if (threadIdx.x == 0) {
@@ -645,10 +653,13 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
         // Buckets are handed out through a counter, not by blockIdx stride: when part of the SMs is held by a
         // concurrently running push kernel, the CTAs that do get an SM still share the work evenly.
         const unsigned long long gmin = prm->kmin, gmax = prm->kmax;
-        for (uint32_t it = 0;; ++it) {
+        // Metadata of the next non-empty bucket -> meta block `slot` (three blocks: the consumers may still read the one
+        // of the tile they are on while the next tile's is complete and the one after that is being fetched).
+        auto fetch = [&](uint32_t slot) {
+            const FrMeta mt = sm.meta(slot);
             int q = 0;
             uint32_t obase = 0, total = 0;
-            for (;;) {   // next non-empty bucket
+            for (;;) {
                 if (lane == 0) q = (int)atomicAdd(&prm->next_bucket, 1u);
                 q = __shfl_sync(0xffffffffu, q, 0);
                 if (q >= G) break;
@@ -656,32 +667,41 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
                 total = outoff[q + 1] - obase;
                 if (total) break;
             }
-            const uint32_t b = it & 1u;
-            if (it >= 2) mbar_wait(&bar_empty[b], ((it >> 1) & 1u) ^ 1u);   // the consumers have left this buffer's previous tile
-            const FrMeta mt = sm.meta(b);
             if (q >= G) {
-                if (lane == 0) { mt.hdr->total = FR_META_DONE; mbar_arrive(&bar_full[b]); }
-                break;
-            }
-            for (int r = lane; r < k; r += 32) {
-                mt.lo[r] = P[(long long)q * k + r];
-                mt.bend[r] = P[(long long)(q + 1) * k + r];
-            }
-            if (lane == 0) {   // the bucket's key range: [first key of the bucket, last key before the next bucket]
-                const unsigned long long klo = kind[q] == 1 ? bkey[q] : gmin;
-                const unsigned long long khi = kind[q + 1] == 1 ? bkey[q + 1] - 1ull : gmax;
-                mt.hdr->klo = klo;
-                mt.hdr->kspan = khi > klo ? khi - klo : 0ull;
-                mt.hdr->total = total;
-                mt.hdr->obase = obase;
-                mt.hdr->big = total > (uint32_t)cap ? 1u : 0u;
+                if (lane == 0) mt.hdr->total = FR_META_DONE;
+            } else {
+                for (int r = lane; r < k; r += 32) {
+                    mt.lo[r] = P[(long long)q * k + r];
+                    mt.bend[r] = P[(long long)(q + 1) * k + r];
+                }
+                if (lane == 0) {   // the bucket's key range: [first key of the bucket, last key before the next bucket]
+                    const unsigned long long klo = kind[q] == 1 ? bkey[q] : gmin;
+                    const unsigned long long khi = kind[q + 1] == 1 ? bkey[q + 1] - 1ull : gmax;
+                    mt.hdr->klo = klo;
+                    mt.hdr->kspan = khi > klo ? khi - klo : 0ull;
+                    mt.hdr->total = total;
+                    mt.hdr->obase = obase;
+                    mt.hdr->big = total > (uint32_t)cap ? 1u : 0u;
+                }
             }
             __syncwarp();
+        };
+        fetch(0);
+        for (uint32_t it = 0;; ++it) {
+            const uint32_t b = it & 1u;
+            if (it >= 2) mbar_wait(&bar_empty[b], ((it >> 1) & 1u) ^ 1u);   // the consumers have left this buffer's previous tile
+            const FrMeta mt = sm.meta(it % 3u);
+            const uint32_t total = mt.hdr->total;
+            if (total == FR_META_DONE) {
+                if (lane == 0) mbar_arrive(&bar_full[b]);
+                break;
+            }
             if (total > (uint32_t)cap) {
                 if (lane == 0) mbar_arrive(&bar_full[b]);   // the consumers split and stage an oversize bucket themselves
             } else {
                 fr_stage(runs, k, stride, mt.lo, mt.bend, sm.rec(b), mt.sbase, mt.soff, total, &bar_full[b]);
             }
+            fetch((it + 1u) % 3u);   // its global-memory round trips overlap the consumers' work on tile `it`
         }
         return;
     }
@@ -691,7 +711,7 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
     for (uint32_t it = 0;; ++it) {
         const uint32_t b = it & 1u;
         mbar_wait(&bar_full[b], (it >> 1) & 1u);     // acquire: tables and records of this tile are visible
-        const FrMeta mt = sm.meta(b);
+        const FrMeta mt = sm.meta(it % 3u);
         const uint32_t total = mt.hdr->total;
         if (total == FR_META_DONE) break;
         const uint32_t obase = mt.hdr->obase;
@@ -699,7 +719,7 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
         uint64_t* release = it > 0 ? &bar_empty[b ^ 1u] : nullptr;
         if (!mt.hdr->big) {
             fr_order_emit<ALIGN2, STRIDE>(sm, sm.rec(b), mt, k, stride, key_off, key_len, total, klo, kspan, force_tree,
-                                          out + (unsigned long long)obase * stride, release, s_ws, &s_flag, prm);
+                                          out + (unsigned long long)obase * stride, release, s_ws, &s_flag, s_mask, prm);
             continue;
         }
         // ---- oversize bucket: split by bisection over the 128-bit value (key80 | run | index); every piece is staged by
@@ -762,7 +782,7 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
                 mbar_wait(&bar_own, own_phase);
                 own_phase ^= 1u;
                 fr_order_emit<ALIGN2, STRIDE>(sm, sm.rec(b), mt, k, stride, key_off, key_len, cnt, klo, kspan, force_tree,
-                                              out + (unsigned long long)(obase + done) * stride, nullptr, s_ws, &s_flag, prm);
+                                              out + (unsigned long long)(obase + done) * stride, nullptr, s_ws, &s_flag, s_mask, prm);
             }
             fr_cbar();   // the piece has left the record buffer and the tables
             done += cnt;
@@ -879,19 +899,16 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
             int bq = (G + 1 + 255) / 256;
             if (bq > kNumSMs * 8) bq = kNumSMs * 8;
             fr_bkeys_kernel<<<bq, 256, 0, stream>>>(G, per, s.hist, s.prm, s.bkey, s.kind);
-            if (nruns <= 16) {  // measured: search 0.4 ms vs streaming 2.0 ms at k = 8; search 5.5 ms vs streaming 2.4 ms at k = 64
+            if (nruns <= 16) {  // measured: search 0.5 ms at k = 8 (a boundary falls only every ~50 records of a run)
                 long long t = (long long)(G + 1) * nruns;
                 long long b = (t + 255) / 256;
                 if (b > kNumSMs * 32) b = kNumSMs * 32;
                 fr_partition_search_kernel<<<(int)b, 256, 0, stream>>>(runs_dev, nruns, G, stride, key_off, key_len, s.bkey, s.kind, s.P);
             } else {
-                long long bx = (max_nrec + 255) / 256;
-                long long capb = (kNumSMs * 16 + nruns - 1) / nruns;
-                if (capb < 1) capb = 1;
-                if (bx > capb) bx = capb;
-                if (bx < 1) bx = 1;
-                dim3 grid((unsigned)bx, (unsigned)nruns);
-                fr_partition_kernel<<<grid, 256, 0, stream>>>(runs_dev, nruns, G, per, stride, key_off, key_len, s.hist, s.prm, s.bkey, s.kind, s.P);
+                const long long t = (((long long)G + FR_PCHUNK) / FR_PCHUNK) * nruns;
+                long long b = (t + 127) / 128;
+                if (b > kNumSMs * 64) b = kNumSMs * 64;
+                fr_partition_walk_kernel<<<(int)b, 128, 0, stream>>>(runs_dev, nruns, G, stride, key_off, key_len, s.bkey, s.kind, s.P);
             }
         }
         {
