@@ -34,8 +34,6 @@ jmethodID g_fetchOver, g_dataFromUda, g_getPathUda, g_getConfData, g_logToJava;
 jfieldID g_fidOffset, g_fidRaw, g_fidPart, g_fidPath;
 uda_role_t g_role = nullptr;
 bool g_is_net_merger = false;
-std::mutex g_buf_mu;
-std::map<const void*, jobject> g_direct_buffers;  // staging block address -> global ref of its DirectByteBuffer
 
 #define ENV(fn, ...) ((*env)->fn(env, ##__VA_ARGS__))
 
@@ -65,25 +63,18 @@ void up_fetch_over(void*) {
     if (env) ENV(CallStaticVoidMethod, g_cls, g_fetchOver);
 }
 
+// One block of whole records for Java. The block may live anywhere (the two 1 MiB staging blocks of the CPU merges, an
+// arbitrary offset inside the pinned windows of the device merge, a temporary for a record larger than a block), so the
+// DirectByteBuffer is made for exactly this call — capacity = len, never more than the memory behind it — and dropped
+// afterwards. Nothing is cached by address: a cache keyed on the block address leaks one global reference per distinct
+// address and keeps references to freed temporaries.
 void up_data(void*, const void* buf, int len) {
     JNIEnv* env = thread_env();
-    if (!env) return;
-    jobject jbuf = nullptr;
-    {
-        std::lock_guard<std::mutex> lk(g_buf_mu);
-        auto it = g_direct_buffers.find(buf);
-        if (it == g_direct_buffers.end()) {
-            // register the staging block once as a direct ByteBuffer (1 MiB capacity); Java reads `len` bytes of it
-            jobject local = ENV(NewDirectByteBuffer, const_cast<void*>(buf), (jlong)(1 << 20));
-            if (!local) return;
-            jbuf = ENV(NewGlobalRef, local);
-            ENV(DeleteLocalRef, local);
-            g_direct_buffers[buf] = jbuf;
-        } else {
-            jbuf = it->second;
-        }
-    }
+    if (!env || len < 0) return;
+    jobject jbuf = ENV(NewDirectByteBuffer, const_cast<void*>(buf), (jlong)len);
+    if (!jbuf) return;
     ENV(CallStaticVoidMethod, g_cls, g_dataFromUda, jbuf, (jint)len);
+    ENV(DeleteLocalRef, jbuf);
 }
 
 int up_get_path(void*, const char* job, const char* map, int reduce, long long* off, long long* raw, long long* part,
@@ -186,9 +177,6 @@ JNIEXPORT void JNICALL JNI_OnUnload(JavaVM* vm, void*) {
     JNIEnv* env = nullptr;
     if (g_role) { uda_rt_destroy(g_role); g_role = nullptr; }
     if (vm && (*vm)->GetEnv(vm, (void**)&env, JNI_VERSION_1_4) == JNI_OK) {
-        std::lock_guard<std::mutex> lk(g_buf_mu);
-        for (auto& kv : g_direct_buffers) ENV(DeleteGlobalRef, kv.second);
-        g_direct_buffers.clear();
         if (g_cls_weak) ENV(DeleteWeakGlobalRef, g_cls_weak);
     }
     g_cls_weak = nullptr;

@@ -301,8 +301,9 @@ void FetchSource::send(int slot, const FetchRequest& r) {
             const int other = slot ^ 1;
             {
                 std::lock_guard<std::mutex> lk(mu_);
-                if (!ok || ack.path == kPathTooLong) {
-                    if (ok) UDA_LOG(lsERROR, "Mof path is too long, UDA supports path of max %zu chars", kMaxMofPath);
+                if (!ok || ack.path == kPathTooLong || ack.path == kFetchRejected) {
+                    if (ok && ack.path == kPathTooLong) UDA_LOG(lsERROR, "Mof path is too long, UDA supports path of max %zu chars", kMaxMofPath);
+                    else if (ok) UDA_LOG(lsERROR, "the provider rejected the fetch of map %s", req_.map_id.c_str());
                     failed_ = true;
                     state_[slot] = EMPTY;
                 } else {

@@ -151,7 +151,8 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
         sink(eof, 2);
         return true;
     }
-    if (k > 0xFFFF || n >= (1LL << 31) - 1) { if (why) *why = "partition too large for the device entry format"; return false; }
+    // limits of the kernel library: uda_kway_merge_entries takes at most 4096 runs, the entry format 2^31 - 2 records
+    if (k > 4096 || n >= (1LL << 31) - 1) { if (why) *why = "partition too large for the device merge (runs > 4096 or records >= 2^31 - 1)"; return false; }
     const long long nn = std::max<long long>(n, 1);
     const long long merge_scratch = a.merge_scratch_bytes(nn, k), tb_scratch = a.tiebreak_scratch_bytes(nn), scan_scratch = a.scan64_scratch_bytes(nn);
     if (merge_scratch < 0 || tb_scratch < 0 || scan_scratch < 0) { if (why) *why = "scratch size query failed"; return false; }
@@ -162,6 +163,12 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
         if (why) *why = "partition needs " + std::to_string(need >> 20) + " MiB of device memory, " + std::to_string(free_b >> 20) + " MiB free";
         return false;
     }
+    // Anything that goes wrong before the first block has been handed to the sink (allocation, a copy, a kernel launch, a
+    // limit of the kernel library) leaves the caller free to merge on the CPU: report it through `why` and return false.
+    // Once output has been delivered the stream cannot be restarted, so the error propagates.
+    bool delivered = false;
+    const std::function<void(const uint8_t*, size_t)> deliver = [&](const uint8_t* p, size_t len) { delivered = true; sink(p, len); };
+    try {
     using Clk = std::chrono::steady_clock;
     auto ms_since = [](Clk::time_point t) { return (long long)std::chrono::duration_cast<std::chrono::milliseconds>(Clk::now() - t).count(); };
     const auto t0 = Clk::now();
@@ -278,8 +285,8 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
             size_t len = (size_t)(off[j] - off[i]);
             const bool last = final_window && j == cur.r1;
             if (last && len + 2 <= max_block) len += 2;
-            sink(cur_buf + (off[i] - base), len);
-            if (last && len == (size_t)(off[j] - off[i])) sink(cur_buf + (off[n] - base), 2);
+            deliver(cur_buf + (off[i] - base), len);
+            if (last && len == (size_t)(off[j] - off[i])) deliver(cur_buf + (off[n] - base), 2);
             i = j;
         }
         if (final_window) break;
@@ -289,6 +296,11 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
     }
     UDA_LOG(lsINFO, "device merge phases: alloc %lld ms, H2D + kernels %lld ms, D2H %lld ms, delivery %lld ms (%lld records, %lld bytes, %d runs)",
             ms_alloc, ms_h2d_kernels, ms_d2h, ms_since(t3), n, out_bytes, k);
+    } catch (const UdaError& e) {
+        if (delivered) throw;
+        if (why) *why = e.info();
+        return false;
+    }
     return true;
 }
 

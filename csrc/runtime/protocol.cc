@@ -10,6 +10,7 @@
 namespace uda {
 
 const char* const kPathTooLong = "MOF_PATH_SIZE_TOO_LONG";
+const char* const kFetchRejected = "UDA_FETCH_REJECTED";
 
 // ---------------------------------------------------------------------------------------------- argv
 namespace {

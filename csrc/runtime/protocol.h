@@ -57,6 +57,9 @@ bool parse_init_params(const HadoopCmd& cmd, InitParams* out);
 constexpr size_t kMaxMsgText = 800;   // NETLEV_FETCH_REQSIZE (src/include/NetlevComm.h:30)
 constexpr size_t kMaxMofPath = 600;   // NETLEV_MOF_PATH_MAX_SIZE (src/include/NetlevComm.h:31)
 extern const char* const kPathTooLong;  // "MOF_PATH_SIZE_TOO_LONG"
+// path field of an ack that rejects a malformed or unservable request (no reference counterpart: the reference never
+// answers such a request and the reducer waits for ever)
+extern const char* const kFetchRejected;  // "UDA_FETCH_REJECTED"
 
 struct FetchRequest {
     std::string job_id, map_id;

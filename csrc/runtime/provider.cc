@@ -134,10 +134,22 @@ void Provider::run() {
 void Provider::process(Job j) {
     FetchRequest& rq = j.req;
     IndexRecord rec;
+    // A request that cannot be served is answered with a rejecting ack (path = kFetchRejected, nothing sent): the
+    // reducer fails that fetch at once instead of waiting for a reply that never comes.
+    auto reject = [&](const char* why) {
+        UDA_LOG(lsERROR, "fetch rejected (%s): job=%s map=%s reduce=%d offset=%lld chunk=%d", why, rq.job_id.c_str(), rq.map_id.c_str(),
+                rq.reduce_id, (long long)rq.map_offset, rq.chunk_size);
+        FetchAck nack;
+        nack.path = kFetchRejected;
+        nack.sent = 0;
+        ShuffleServer::reply(j.conn, rq.request_ptr, format_fetch_ack(nack), nullptr, 0);
+    };
+    // the request text comes off a socket: nothing in it is trusted
+    if (rq.chunk_size <= 0 || rq.map_offset < 0) { reject("non-positive chunk size or negative offset"); return; }
     if (rq.path.empty()) {
         // first fetch of this (job, map, reduce): ask the host for the index record
         if (!host_ || !host_->get_path_uda || !host_->get_path_uda(host_->user, rq.job_id.c_str(), rq.map_id.c_str(), rq.reduce_id, &rec)) {
-            UDA_LOG(lsERROR, "getPathUda returned nothing for job=%s map=%s reduce=%d", rq.job_id.c_str(), rq.map_id.c_str(), rq.reduce_id);
+            reject("getPathUda returned nothing");
             return;
         }
     } else {
@@ -146,9 +158,13 @@ void Provider::process(Job j) {
         rec.part_length = rq.part_length;
         rec.path = rq.path;
     }
+    if (rec.offset < 0 || rec.part_length < 0 || rec.raw_length < 0 || rq.map_offset > rec.part_length) {
+        reject("offset beyond the partition or negative index record");
+        return;
+    }
     if (pool_->free_count() == 0) reader_->submit();  // do not sleep on the pool with reads still un-submitted
     Chunk* chunk = pool_->occupy();
-    if (!chunk) return;
+    if (!chunk) return;   // shutting down
     FetchAck ack;
     ack.raw_length = rec.raw_length;
     ack.part_length = rec.part_length;
@@ -161,9 +177,8 @@ void Provider::process(Job j) {
         pool_->release(chunk);
         return;
     }
-    long long remaining = rec.part_length - rq.map_offset;
-    if (remaining < 0) remaining = 0;
-    long long want = remaining < rq.chunk_size ? remaining : rq.chunk_size;
+    long long want = rec.part_length - rq.map_offset;     // >= 0, checked above
+    if (want > rq.chunk_size) want = rq.chunk_size;
     if (want > opt_.buf_size) want = opt_.buf_size;
     if (want == 0) {
         ack.sent = 0;
@@ -171,12 +186,21 @@ void Provider::process(Job j) {
         pool_->release(chunk);
         return;
     }
-    int fd = fds_.acquire(rec.path);
-    if (fd < 0) { pool_->release(chunk); return; }
     const long long file_pos = rec.offset + rq.map_offset;
     const long long aligned = file_pos & ~((long long)kAioAlignment - 1);
     const size_t lead = (size_t)(file_pos - aligned);
-    size_t len = (lead + (size_t)want + kAioAlignment - 1) & ~((size_t)kAioAlignment - 1);
+    const size_t len = (lead + (size_t)want + kAioAlignment - 1) & ~((size_t)kAioAlignment - 1);
+    if (len > chunk->capacity) {   // cannot happen with want <= buf_size; the read must never leave the chunk
+        pool_->release(chunk);
+        reject("read span exceeds the chunk");
+        return;
+    }
+    int fd = fds_.acquire(rec.path);
+    if (fd < 0) {
+        pool_->release(chunk);
+        reject("cannot open the map output file");
+        return;
+    }
     ReadRequest rr;
     rr.fd = fd;
     rr.offset = aligned;
@@ -189,6 +213,10 @@ void Provider::process(Job j) {
     rr.on_done = [this, chunk, lead, want, ack, conn, cookie, path](ssize_t got) mutable {
         if (got < 0 || (size_t)got < lead + (size_t)want) {
             UDA_LOG(lsERROR, "read of %s failed or short: rc=%zd", path.c_str(), got);
+            FetchAck nack;
+            nack.path = kFetchRejected;
+            nack.sent = 0;
+            ShuffleServer::reply(conn, cookie, format_fetch_ack(nack), nullptr, 0);
         } else {
             ack.sent = want;
             if (ShuffleServer::reply(conn, cookie, format_fetch_ack(ack), chunk->data + lead, (size_t)want)) ++served_;

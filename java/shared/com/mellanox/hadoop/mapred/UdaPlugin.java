@@ -95,7 +95,7 @@ class UdaPluginRT<K, V> extends UdaPlugin implements UdaBridge.UdaCallable {
 	private Progress progress = new Progress();
 
 	private static final class KVBuf {
-		final byte[] bytes = new byte[KV_BUF_SIZE];
+		byte[] bytes = new byte[KV_BUF_SIZE];     // grows when a single record is larger than a staging block
 		final DataInputBuffer in = new DataInputBuffer();
 		int len = 0;
 		boolean full = false;   // true: waiting for the reducer, false: waiting for native data
@@ -199,6 +199,7 @@ class UdaPluginRT<K, V> extends UdaPlugin implements UdaBridge.UdaCallable {
 			while (buf.full) buf.wait();
 			ByteBuffer src = (ByteBuffer) directBuffer;
 			src.position(0);
+			if (len > buf.bytes.length) buf.bytes = new byte[len];   // a record larger than 1 MiB arrives as one block
 			src.get(buf.bytes, 0, len);
 			buf.len = len;
 			buf.in.reset(buf.bytes, 0, len);

@@ -44,6 +44,7 @@ static std::string g_thrown_class, g_thrown_msg;
 static std::map<std::string, Obj*> g_methods;
 static std::map<std::string, std::pair<std::string, std::vector<long long>>> g_mofs;  // map id -> (path, off/raw/part per reduce)
 static int g_direct_buffers = 0;
+static bool g_buffer_cap_ok = true;   // every dataFromUda buffer had capacity == len
 
 static Obj* mk(Obj::Kind k, const std::string& s = "") { auto* o = new Obj(); o->kind = k; o->s = s; return o; }
 static void note(const std::string& s) { std::lock_guard<std::mutex> lk(g_mu); g_calls.push_back(s); }
@@ -124,6 +125,7 @@ static void m_CallStaticVoidMethod(JNIEnv*, jclass, jmethodID mid, ...) {
         Obj* b = O(va_arg(ap, jobject));
         int len = va_arg(ap, jint);
         CHECK(b->kind == Obj::BUFFER && len <= b->cap);
+        if (b->cap != len) g_buffer_cap_ok = false;
         std::lock_guard<std::mutex> lk(g_mu);
         g_stream.append((const char*)b->addr, (size_t)len);  // what UdaPluginRT.dataFromUda does with directBuf.get()
     }
@@ -348,7 +350,7 @@ int main(int argc, char** argv) {
     }
     { std::lock_guard<std::mutex> lk(g_mu); CHECK(g_stream == expect); }
     CHECK(g_fetch_over >= 1 && g_failures == 0);
-    CHECK(g_direct_buffers >= 1 && g_direct_buffers <= 2);  // each staging block is registered once, not per call
+    CHECK(g_direct_buffers >= 1 && g_buffer_cap_ok);  // one buffer per delivered block, capacity == delivered length
     rexit(env, cls);
 
     // 5. consumer whose provider is gone: the merge thread's failure arrives as failureInUda()

@@ -447,3 +447,57 @@ def test_example_fake_hadoop_plumbing(built, approach):
     p = subprocess.run([sys.executable, str(root / "examples" / "fake_hadoop_plumbing.py"), "--approach", str(approach)],
                        capture_output=True, text=True, timeout=120)
     assert p.returncode == 0 and p.stdout.strip().endswith("OK"), p.stdout + p.stderr
+
+
+# ------------------------------------------------------------------------------------------ hostile fetch requests
+def test_provider_rejects_malformed_fetch_requests(built, tmp_path):
+    """The request text comes off a socket: a negative chunk size / offset or an offset past the partition must be
+    answered with a rejecting ack (nothing read, nothing sent), not turned into a wrapped read length; an unknown map
+    is rejected too instead of leaving the reducer waiting (the reference never answers such a request)."""
+    import socket
+
+    mofs, _truth = _make_mofs(str(tmp_path), 1, 1, 50, seed=3)
+    (mapid, (path, idx)), = mofs.items()
+
+    def get_path(job, m, reduce):
+        if m != mapid:
+            return None
+        r = idx[reduce]
+        return r.start_offset, r.raw_length, r.part_length, path
+
+    prov = bridge.NativeRole(False, bridge.build_argv(port=0, buf_kb=8, provider=True), get_path=get_path)
+    try:
+        assert not prov.failed and prov.port > 0
+        part_len = idx[0].part_length
+
+        def ask(text):
+            with socket.create_connection(("127.0.0.1", prov.port), timeout=10) as s:
+                s.sendall(struct.pack("<BBHIQQ", 0x02, 0, 0, len(text), 0, 0) + text.encode())
+                hdr = b""
+                while len(hdr) < 24:
+                    chunk = s.recv(24 - len(hdr))
+                    assert chunk, "provider closed the connection without an ack"
+                    hdr += chunk
+                _t, _c, _p, tot, _cookie, plen = struct.unpack("<BBHIQQ", hdr)
+                body = b""
+                while len(body) < tot + plen:
+                    chunk = s.recv(tot + plen - len(body))
+                    assert chunk
+                    body += chunk
+                return body[:tot].decode(), plen
+
+        # job:map:map_offset:reduce:addr:cookie:chunk_size:file_offset:path:raw:part
+        good, plen = ask(f"job_1:{mapid}:0:0:0:7:4096:0::0:0")
+        assert "UDA_FETCH_REJECTED" not in good and plen == min(4096, part_len)
+        for bad in (f"job_1:{mapid}:0:0:0:7:-5:0::0:0",                       # negative chunk size
+                    f"job_1:{mapid}:-4096:0:0:7:4096:0::0:0",                 # negative offset
+                    f"job_1:{mapid}:{part_len + 1}:0:0:7:4096:0::0:0",        # offset past the partition
+                    f"job_1:{mapid}:0:0:0:7:4096:-8:{path}:10:10",            # negative file offset in a follow-up request
+                    "job_1:attempt_unknown:0:0:0:7:4096:0::0:0"):             # no such map output
+            text, plen = ask(bad)
+            assert "UDA_FETCH_REJECTED" in text and plen == 0, (bad, text)
+        good, plen = ask(f"job_1:{mapid}:0:0:0:7:4096:0::0:0")              # the provider is still serving
+        assert plen == min(4096, part_len)
+    finally:
+        prov.command(bridge.form_cmd(bridge.EXIT, []))
+        prov.close()
