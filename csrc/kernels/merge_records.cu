@@ -76,7 +76,22 @@ struct FrParams {
     unsigned int next_bucket, pad2;   // dynamic bucket scheduler of fr_merge_kernel (reset by fr_range_kernel)
 };
 
+// Key prefix of a record in global memory. A 10-byte key at an even address (TeraSort; any 2-byte aligned layout) is read
+// with two aligned 8-byte loads and shifted into place: the byte-wise path issues ten scattered one-byte loads per key,
+// which made the partition pre-passes L1-throughput bound (every lane of a warp touches a different cache line).
+// The aligned window starts at most 6 bytes before the key (never before an 8-byte aligned allocation start) and ends at
+// most 16 bytes after its first byte (inside the 32 readable bytes every run has after its last record).
 __device__ __forceinline__ void load_key80(const uint8_t* p, int key_len, unsigned long long* w0, uint32_t* t) {
+    if (key_len == 10 && ((uintptr_t)p & 1u) == 0) {
+        const unsigned long long* a = reinterpret_cast<const unsigned long long*>((uintptr_t)p & ~(uintptr_t)7);
+        const uint32_t sh = (uint32_t)((uintptr_t)p & 7u) * 8u;   // 0, 16, 32, 48
+        const unsigned long long q0 = __ldg(a), q1 = __ldg(a + 1);
+        const unsigned long long le = sh ? (q0 >> sh) | (q1 << (64u - sh)) : q0;   // key bytes 0..7, little-endian
+        *w0 = bswap64(le);
+        const uint32_t tl = (uint32_t)(q1 >> sh) & 0xFFFFu;                          // key bytes 8..9
+        *t = ((tl & 0xFFu) << 8) | (tl >> 8);
+        return;
+    }
     key_prefix(p, key_len, w0, t);
 }
 
@@ -197,57 +212,57 @@ __global__ void fr_partition_search_kernel(const UdaRunDesc* __restrict__ runs, 
     }
 }
 
-// The k-way merge-path partition for many runs (k > 16), as a walk instead of a search per boundary: bucket boundaries and a run's keys are
-// both sorted, so one thread takes FR_PCHUNK consecutive boundaries of one run, finds the first by binary search and every
-// following one by scanning forward from the previous position (a few records apart on average; gaps are bounded by an
-// exponential probe + binary search). Every key is read about once. (Round 1 used one streaming pass over all keys with a
-// prefix-table look-up per record: 2.4 ms for 125 M records at k = 64; per-boundary binary searches took 5.5 ms.)
-constexpr int FR_PCHUNK = 32;
-__global__ void fr_partition_walk_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int stride, int key_off, int key_len,
-                                         const unsigned long long* __restrict__ bkey, const uint8_t* __restrict__ kind,
-                                         uint32_t* __restrict__ P) {
-    const long long nchunk = ((long long)G + 1 + FR_PCHUNK - 1) / FR_PCHUNK;
-    const long long total = nchunk * k;
-    for (long long x = (long long)blockIdx.x * blockDim.x + threadIdx.x; x < total; x += (long long)gridDim.x * blockDim.x) {
-        const int r = (int)(x % k);                 // consecutive threads: consecutive runs of the same boundaries (coalesced P stores)
-        const long long c = x / k;
-        const UdaRunDesc rd = runs[r];
-        const uint8_t* base = (const uint8_t*)rd.base;
-        const uint32_t n = (uint32_t)rd.nrec;
-        const int q0 = (int)(c * FR_PCHUNK);
-        const int q1 = min(G, q0 + FR_PCHUNK - 1);
-        uint32_t pos = 0;
-        bool have = false;                           // pos is a valid lower bound for the next boundary
-        for (int q = q0; q <= q1; ++q) {
+// Exact split position of every bucket boundary in every run: the k-way merge-path partition.
+//
+// A boundary is a bin edge, so "first record of run r in bucket >= q" can be read off a single pass over
+// the run's keys: record i lies in bucket b_i = cum[bin(key_i)] / (TARGET/SAMPLE) (O(1), the prefix array is
+// L2 resident), b_i is non-decreasing in i, and P[q][r] = i for every q in (b_{i-1}, b_i]. One coalesced,
+// sector-sparse pass (2.2 ms for 125 M records) replaces (G+1)*k independent binary searches over strided
+// records, which for k = 64 dragged the whole data set through DRAM at 2 TB/s (6.3 ms). Runs that are much
+// shorter than the bucket count keep the per-boundary binary search (their gaps would serialise one thread).
+// The pass is DRAM bound, not latency bound: one key per 102-byte record touches 62 % of the 64-byte DRAM atoms, so
+// no key pass can take less than ~1.4 ms here. Two walking variants that avoid the prefix-table look-up (a thread per
+// 32 boundaries: 4.9 ms; a warp per run with shared-memory key windows: 2.8 ms) measured slower and were dropped.
+__global__ void fr_partition_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int per_i, int stride, int key_off, int key_len,
+                                    const uint32_t* __restrict__ cum, const FrParams* __restrict__ prm,
+                                    const unsigned long long* __restrict__ bkey, const uint8_t* __restrict__ kind,
+                                    uint32_t* __restrict__ P) {
+    const int r = blockIdx.y;
+    const UdaRunDesc rd = runs[r];
+    const uint8_t* base = (const uint8_t*)rd.base;
+    const long long n = rd.nrec;
+    const long long nthreads = (long long)gridDim.x * blockDim.x;
+    const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n * 4 < (long long)G) {  // short run: one binary search per boundary
+        for (long long q = t0; q <= G; q += nthreads) {
             const uint8_t kd = kind[q];
-            uint32_t p;
-            if (kd == 0) p = 0u;
-            else if (kd == 2) p = n;
-            else {
-                const unsigned long long target = bkey[q];
-                auto below = [&](uint32_t i) -> bool {   // key of record i < (target, tail 0)
-                    unsigned long long w0;
-                    uint32_t t;
-                    load_key80(base + (unsigned long long)i * stride + key_off, key_len, &w0, &t);
-                    return w0 < target;
-                };
-                if (!have) {
-                    p = lb_records(base, stride, key_off, key_len, 0u, n, target, 0u);
-                } else {
-                    p = pos;
-                    int lin = 0;
-                    while (p < n && lin < 6 && below(p)) { ++p; ++lin; }
-                    if (p < n && lin == 6 && below(p)) {   // a long gap: exponential probe, then binary search
-                        uint32_t lo = p + 1u, step = 8u;
-                        while (lo + step <= n && below(lo + step - 1u)) { lo += step; step <<= 1; }
-                        const uint32_t hi = lo + step - 1u < n ? lo + step - 1u : n;
-                        p = lb_records(base, stride, key_off, key_len, lo, hi, target, 0u);
-                    }
-                }
-                pos = p;
-                have = true;
-            }
-            P[(long long)q * k + r] = p;
+            uint32_t pos = kd == 0 ? 0u : (uint32_t)n;
+            if (kd == 1) pos = lb_records(base, stride, key_off, key_len, 0u, (uint32_t)n, bkey[q], 0u);
+            P[q * k + r] = pos;
+        }
+        return;
+    }
+    const unsigned long long kmin = prm->kmin;
+    const int shift = prm->shift;
+    const uint32_t per = (uint32_t)per_i;
+    auto bucket_of = [&](long long i) -> int {
+        unsigned long long w0;
+        uint32_t t;
+        load_key80(base + i * stride + key_off, key_len, &w0, &t);
+        const uint32_t bq = __ldg(&cum[(w0 - kmin) >> shift]) / per;
+        return (int)(bq < (uint32_t)(G - 1) ? bq : (uint32_t)(G - 1));
+    };
+    const int lane = threadIdx.x & 31;
+    for (long long wi = t0 - lane; wi < n; wi += nthreads) {  // warp-uniform trip count: the shuffle needs every lane
+        const long long i = wi + lane;
+        const bool valid = i < n;
+        const int bi = valid ? bucket_of(i) : G;
+        int bp = __shfl_up_sync(0xffffffffu, bi, 1);
+        if (lane == 0) bp = wi > 0 ? bucket_of(wi - 1) : -1;
+        if (valid) {
+            for (int q = bp + 1; q <= bi; ++q) P[(long long)q * k + r] = (uint32_t)i;
+            if (i == n - 1)
+                for (int q = bi + 1; q <= G; ++q) P[(long long)q * k + r] = (uint32_t)n;
         }
     }
 }
@@ -905,10 +920,13 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
                 if (b > kNumSMs * 32) b = kNumSMs * 32;
                 fr_partition_search_kernel<<<(int)b, 256, 0, stream>>>(runs_dev, nruns, G, stride, key_off, key_len, s.bkey, s.kind, s.P);
             } else {
-                const long long t = (((long long)G + FR_PCHUNK) / FR_PCHUNK) * nruns;
-                long long b = (t + 127) / 128;
-                if (b > kNumSMs * 64) b = kNumSMs * 64;
-                fr_partition_walk_kernel<<<(int)b, 128, 0, stream>>>(runs_dev, nruns, G, stride, key_off, key_len, s.bkey, s.kind, s.P);
+                long long bx = (max_nrec + 255) / 256;
+                long long capb = (kNumSMs * 16 + nruns - 1) / nruns;
+                if (capb < 1) capb = 1;
+                if (bx > capb) bx = capb;
+                if (bx < 1) bx = 1;
+                dim3 grid((unsigned)bx, (unsigned)nruns);
+                fr_partition_kernel<<<grid, 256, 0, stream>>>(runs_dev, nruns, G, per, stride, key_off, key_len, s.hist, s.prm, s.bkey, s.kind, s.P);
             }
         }
         {
