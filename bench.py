@@ -57,6 +57,9 @@ def parse_args():
     ap.add_argument("--graph", action="store_true", help="time replays of the step captured as a CUDA graph (one GPU, no pipelining)")
     ap.add_argument("--local-zero-copy", action="store_true",
                     help="merge this rank's own map outputs in place instead of copying them into its arena (implies --no-e2e)")
+    ap.add_argument("--local-copy", default="auto", choices=["auto", "push", "ce"],
+                    help="a rank's own map outputs reach its arena through the push kernel or through the copy engines "
+                         "(auto: copy engines when the step is pipelined over several GPUs)")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to the CPUs local to its GPU")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-check", action="store_true")
@@ -262,7 +265,7 @@ def main():
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev).setup()
     else:
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev, subparts=a.subparts, push_ctas=a.push_ctas,
-                  merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode, local_zero_copy=a.local_zero_copy, tma_flush=a.tma_flush).setup()
+                  merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode, local_zero_copy=a.local_zero_copy, tma_flush=a.tma_flush, local_copy=a.local_copy).setup()
     total_bytes = float(a.records_per_gpu) * RECORD_BYTES * world
 
     def timed(fn, steps, warmup, sample_clocks):
@@ -335,7 +338,7 @@ def main():
                 "model": "TeraSort 100 GB/8 GPUs (12.5 GB per GPU), 100-byte teragen records, IFile-framed sorted MOFs in HBM",
                 "global_batch": a.records_per_gpu * world, "seq_len": RECORD_BYTES,
                 "records_per_gpu": a.records_per_gpu, "maps_per_gpu": a.maps_per_gpu, "runs_per_reducer": a.maps_per_gpu * world,
-                "subparts": a.subparts, "push_mode": a.push_mode, "local_zero_copy": a.local_zero_copy, "cuda_graph": bool(a.graph), "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
+                "subparts": a.subparts, "push_mode": a.push_mode, "local_zero_copy": a.local_zero_copy, "local_copy": getattr(job, "local_copy", None), "cuda_graph": bool(a.graph), "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
                 "parallelism": f"partition-parallel a2a x{world} (one reducer per GPU)",
                 "l2_policy": "inputs (12.75 GB/GPU) larger than the 126 MB L2; no flush needed",
                 "timed_region": "shuffle push + flag acquire + key normalise + k-way merge + record gather (map-side sort is set-up)",

@@ -5,6 +5,9 @@
 // Run:   build/bin/tma_copy_micro            (prints one line per configuration: GB/s of payload moved)
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <ctime>
+#include <unistd.h>
 #include <cuda_runtime.h>
 
 #include "../csrc/kernels/common.cuh"
@@ -97,10 +100,79 @@ void run(const uint8_t* src, uint8_t* dst, long long bytes, int ctas, int mode) 
            e == cudaSuccess ? "" : cudaGetErrorString(e));
 }
 
+// Bidirectional mode ("b <start epoch>"): two processes, started with swapped CUDA_VISIBLE_DEVICES, write to each other at the
+// same time; every case starts at an agreed wall-clock second so that the two directions overlap.
+static void wait_until(double t) {
+    timespec ts;
+    for (;;) {
+        clock_gettime(CLOCK_REALTIME, &ts);
+        if ((double)ts.tv_sec + 1e-9 * ts.tv_nsec >= t) return;
+        usleep(200);
+    }
+}
+template <int CHUNK, int STAGES, int AHEAD, int WARPS>
+void run_at(double t, const uint8_t* src, uint8_t* dst, long long bytes, int ctas) {
+    auto k = copy_kernel<CHUNK, STAGES, AHEAD, WARPS>;
+    const int smem = CHUNK * STAGES * WARPS;
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const long long nchunks = bytes / CHUNK;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    k<<<ctas, 32 * WARPS, smem>>>(src, dst, nchunks, 0);
+    cudaDeviceSynchronize();
+    wait_until(t);
+    cudaEventRecord(a);
+    for (int i = 0; i < 20; ++i) k<<<ctas, 32 * WARPS, smem>>>(src, dst, nchunks, 0);
+    cudaEventRecord(b);
+    cudaEventSynchronize(b);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    printf("bidirectional tma chunk=%6d stages=%2d ahead=%d warps=%d ctas=%3d : %8.1f GB/s per direction (%.1f GB/s per CTA)\n", CHUNK, STAGES,
+           AHEAD, WARPS, ctas, nchunks * (double)CHUNK * 20 / ms / 1e6, nchunks * (double)CHUNK * 20 / ms / 1e6 / ctas);
+}
+void run_lsu_at(double t, const uint8_t* src, uint8_t* dst, long long bytes, int ctas) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    lsu_copy_kernel<<<ctas, 1024>>>((const int4*)src, (int4*)dst, bytes / 16);
+    cudaDeviceSynchronize();
+    wait_until(t);
+    cudaEventRecord(a);
+    for (int i = 0; i < 20; ++i) lsu_copy_kernel<<<ctas, 1024>>>((const int4*)src, (int4*)dst, bytes / 16);
+    cudaEventRecord(b);
+    cudaEventSynchronize(b);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    printf("bidirectional lsu ctas=%3d : %8.1f GB/s per direction\n", ctas, bytes * 20.0 / ms / 1e6);
+}
+
 int main(int argc, char** argv) {
     const long long bytes = 2LL << 30;
     uint8_t *src, *dst;
     cudaMalloc(&src, bytes);
+    if (argc > 2 && argv[1][0] == 'b') {
+        double t = atof(argv[2]);
+        int can = 0;
+        cudaDeviceCanAccessPeer(&can, 0, 1);
+        if (!can) { printf("no peer access 0->1\n"); return 1; }
+        cudaDeviceEnablePeerAccess(1, 0);
+        cudaSetDevice(1);
+        cudaMalloc(&dst, bytes);
+        cudaMemset(dst, 2, bytes);
+        cudaDeviceSynchronize();
+        cudaSetDevice(0);
+        cudaMemset(src, 1, bytes);
+        cudaDeviceSynchronize();
+        run_at<16384, 3, 2, 4>(t, src, dst, bytes, 16); t += 1.0;
+        run_at<16384, 3, 2, 4>(t, src, dst, bytes, 32); t += 1.0;
+        run_at<16384, 3, 2, 4>(t, src, dst, bytes, 64); t += 1.0;
+        run_at<32768, 6, 4, 1>(t, src, dst, bytes, 32); t += 1.0;
+        run_at<8192, 6, 4, 4>(t, src, dst, bytes, 32); t += 1.0;
+        run_lsu_at(t, src, dst, bytes, 148); t += 1.0;
+        run_lsu_at(t, src, dst, bytes, 296);
+        return 0;
+    }
     const bool peer = argc > 1 && argv[1][0] == 'p';
     if (peer) {   // destination on GPU 1, written from GPU 0 over NVLink
         int can = 0;

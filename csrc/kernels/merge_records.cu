@@ -670,34 +670,54 @@ fr_merge_kernel(const UdaRunDesc* __restrict__ runs, int k, int G, int cap, int 
         const unsigned long long gmin = prm->kmin, gmax = prm->kmax;
         // Metadata of the next non-empty bucket -> meta block `slot` (three blocks: the consumers may still read the one
         // of the tile they are on while the next tile's is complete and the one after that is being fetched).
+        // The bucket counter is read one fetch ahead (qn), and everything that depends only on the bucket number (output
+        // range, split positions, key range) is loaded at once: one global round trip per fetch instead of three.
+        int qn = 0;
+        if (lane == 0) qn = (int)atomicAdd(&prm->next_bucket, 1u);
+        qn = __shfl_sync(0xffffffffu, qn, 0);
         auto fetch = [&](uint32_t slot) {
             const FrMeta mt = sm.meta(slot);
-            int q = 0;
-            uint32_t obase = 0, total = 0;
             for (;;) {
-                if (lane == 0) q = (int)atomicAdd(&prm->next_bucket, 1u);
-                q = __shfl_sync(0xffffffffu, q, 0);
-                if (q >= G) break;
-                obase = outoff[q];
-                total = outoff[q + 1] - obase;
-                if (total) break;
-            }
-            if (q >= G) {
-                if (lane == 0) mt.hdr->total = FR_META_DONE;
-            } else {
-                for (int r = lane; r < k; r += 32) {
+                const int q = qn;
+                if (q >= G) {
+                    if (lane == 0) mt.hdr->total = FR_META_DONE;
+                    break;
+                }
+                int q2 = 0;
+                if (lane == 0) q2 = (int)atomicAdd(&prm->next_bucket, 1u);   // for the next fetch; in flight with the loads below
+                const uint32_t obase = outoff[q];
+                const uint32_t total = outoff[q + 1] - obase;
+                uint32_t plo[4], phi[4];   // k <= 128 in registers; larger k in a second loop
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int r = c * 32 + lane;
+                    plo[c] = r < k ? P[(long long)q * k + r] : 0u;
+                    phi[c] = r < k ? P[(long long)(q + 1) * k + r] : 0u;
+                }
+                unsigned long long klo = 0, khi = 0;
+                if (lane == 0) {   // the bucket's key range: [first key of the bucket, last key before the next bucket]
+                    klo = kind[q] == 1 ? bkey[q] : gmin;
+                    khi = kind[q + 1] == 1 ? bkey[q + 1] - 1ull : gmax;
+                }
+                qn = __shfl_sync(0xffffffffu, q2, 0);
+                if (total == 0) continue;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int r = c * 32 + lane;
+                    if (r < k) { mt.lo[r] = plo[c]; mt.bend[r] = phi[c]; }
+                }
+                for (int r = 128 + lane; r < k; r += 32) {
                     mt.lo[r] = P[(long long)q * k + r];
                     mt.bend[r] = P[(long long)(q + 1) * k + r];
                 }
-                if (lane == 0) {   // the bucket's key range: [first key of the bucket, last key before the next bucket]
-                    const unsigned long long klo = kind[q] == 1 ? bkey[q] : gmin;
-                    const unsigned long long khi = kind[q + 1] == 1 ? bkey[q + 1] - 1ull : gmax;
+                if (lane == 0) {
                     mt.hdr->klo = klo;
                     mt.hdr->kspan = khi > klo ? khi - klo : 0ull;
                     mt.hdr->total = total;
                     mt.hdr->obase = obase;
                     mt.hdr->big = total > (uint32_t)cap ? 1u : 0u;
                 }
+                break;
             }
             __syncwarp();
         };

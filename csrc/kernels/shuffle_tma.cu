@@ -21,10 +21,23 @@
 namespace uda {
 namespace {
 
-constexpr int TP_WARPS = 4;      // independent copy pipelines per CTA (one warp each): hides the per-chunk bookkeeping
-constexpr int TP_CHUNK = 16 * 1024;
-constexpr int TP_STAGES = 3;     // per warp; TP_WARPS * TP_STAGES * TP_CHUNK = 192 KiB per CTA
-constexpr int TP_AHEAD = 2;      // loads run this many chunks ahead of the stores
+#ifndef UDA_TP_WARPS
+#define UDA_TP_WARPS 4
+#endif
+#ifndef UDA_TP_CHUNK_KB
+#define UDA_TP_CHUNK_KB 16
+#endif
+#ifndef UDA_TP_STAGES
+#define UDA_TP_STAGES 3
+#endif
+#ifndef UDA_TP_AHEAD
+#define UDA_TP_AHEAD 2
+#endif
+constexpr int TP_WARPS = UDA_TP_WARPS;      // independent copy pipelines per CTA (one warp each): hides the per-chunk bookkeeping
+constexpr int TP_CHUNK = UDA_TP_CHUNK_KB * 1024;
+constexpr int TP_STAGES = UDA_TP_STAGES;    // per warp; TP_WARPS * TP_STAGES * TP_CHUNK = 192 KiB per CTA
+constexpr int TP_AHEAD = UDA_TP_AHEAD;      // loads run this many chunks ahead of the stores: AHEAD chunks of loads and
+                                            // STAGES - AHEAD chunks of stores are in flight per warp
 constexpr int TP_MAXSUB = 16;
 constexpr int TP_CACHE = 2048;   // chunk_prefix entries kept in shared memory
 constexpr int TP_DCACHE = 256;   // descriptors kept in shared memory

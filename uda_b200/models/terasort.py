@@ -54,7 +54,7 @@ class TeraSortJob:
 
     def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 1234,
                  key_bits: int = 0, group=None, push_ctas: int = 0, subparts: int = 1, merge_ctas_per_sm: int = 0,
-                 push_mode: str = "lsu", local_zero_copy: bool = False, tma_flush: int = 0):
+                 push_mode: str = "lsu", local_zero_copy: bool = False, tma_flush: int = 0, local_copy: str = "auto"):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -78,6 +78,12 @@ class TeraSortJob:
         #: reference and Hadoop copy local fetches like remote ones). Off by default: the headline benchmark moves
         #: every segment. Not available on the end-to-end path, whose map outputs alternate between two buffers.
         self.local_zero_copy = local_zero_copy
+        #: how a rank's OWN map outputs reach its arena. "push": through the push kernel like the remote ones. "ce": with
+        #: the GPU's copy engines (one device-to-device cudaMemcpyAsync per segment on a stream of its own, then one
+        #: atomic add of the landed bytes per sub-partition), so the SMs reserved for the push move only what must cross
+        #: NVLink. "auto": "ce" when the step is pipelined over several GPUs, "push" otherwise.
+        assert local_copy in ("auto", "push", "ce")
+        self.local_copy = local_copy
         #: polls of the landed-byte counters before the wait kernel gives up and records a time-out in the arena's
         #: status word (the watchdog that turns a lost push into a failure up-call instead of a hang)
         self.wait_max_spins = 50_000_000
@@ -120,10 +126,17 @@ class TeraSortJob:
 
         # ---- arena + tables (one push table and one run table per sub-partition)
         self.arena = SymmetricArena(self.plan.max_arena_bytes(), nruns * C, dev, self.group)
-        self.push_descs_dev = self._push_tables([m.data.data_ptr() for m in self.mofs])
+        if self.local_copy == "auto":
+            self.local_copy = "ce" if (P > 1 and C > 1 and not self.local_zero_copy) else "push"
+        if self.local_zero_copy:
+            self.local_copy = "push"
+        self.local_stream = torch.cuda.Stream(dev) if self.local_copy == "ce" else None
+        self.ev_local = torch.cuda.Event()
+        self.push_set = self._push_tables([m.data for m in self.mofs])
+        self.push_descs_dev = self.push_set["tables"]
         self.nseg = self.maps * P
         self.push_scratch = [torch.empty(K.push_scratch_bytes(self.nseg), dtype=torch.uint8, device=dev) for _ in range(C)]
-        self.push_descs_all = torch.cat(self.push_descs_dev).contiguous()
+        self.push_descs_all = self.push_set["all"]
         self.push_tma_scratch = torch.empty(K.push_tma_scratch_bytes(self.nseg * C), dtype=torch.uint8, device=dev)
         self.sub_runs, self.sub_n, expect = [], [], []
         max_sub = 1
@@ -160,16 +173,48 @@ class TeraSortJob:
         return self
 
     # ------------------------------------------------------------------------------------ step
-    def _push_tables(self, mof_ptrs) -> List[torch.Tensor]:
-        P = self.world
-        tables = []
-        for j in range(self.subparts):
+    def _push_tables(self, mof_data: List[torch.Tensor]) -> dict:
+        """Everything one set of map-output buffers needs for a step: the push descriptor table of every sub-partition
+        (``tables``, and ``all`` = their concatenation for the one-launch copy-engine push) and, with ``local_copy ==
+        "ce"``, the device-to-device copies of this rank's own segments (``local[j]`` = list of (dst view, src view),
+        ``local_idx[j]`` / ``local_bytes[j]`` = counter slots and landed bytes)."""
+        P, C = self.world, self.subparts
+        mof_ptrs = [t.data_ptr() for t in mof_data]
+        tables, local, local_idx, local_bytes = [], [], [], []
+        arena = self.arena.data()
+        for j in range(C):
             d = self.plan.push_descs(self.rank, mof_ptrs, [self.arena.peer_data_ptr(p) for p in range(P)],
                                      [self.arena.peer_flag_ptr(p, 0) for p in range(P)], j)
-            if self.local_zero_copy:
+            if self.local_zero_copy or self.local_copy == "ce":
                 d["bytes"][(P - 1) * self.maps:] = 0      # the last `maps` descriptors are the ones addressed to this rank
             tables.append(K.to_device_struct(d, self.device))
-        return tables
+            if self.local_copy == "ce":
+                lay = self.plan.layout(self.rank, j)
+                jobs, idx, nb = [], [], []
+                for m in range(self.maps):
+                    start, _raw, part = (int(x) for x in self.plan.index[self.rank, m, self.rank * C + j])
+                    rid = self.plan.run_id(self.rank, m)
+                    if part > 0:
+                        off = int(lay.run_offsets[rid])
+                        jobs.append((arena[off:off + part], mof_data[m][start:start + part]))
+                    idx.append(j * self.plan.nruns + rid)
+                    nb.append(part)
+                local.append(jobs)
+                local_idx.append(torch.tensor(idx, dtype=torch.int64, device=self.device))
+                local_bytes.append(torch.tensor(nb, dtype=torch.int64, device=self.device))
+        return {"tables": tables, "all": torch.cat(tables).contiguous(), "local": local, "local_idx": local_idx, "local_bytes": local_bytes}
+
+    def _local_copies(self, pset: dict, cur) -> None:
+        """Queues this rank's own segments on the copy engines (stream of their own), sub-partition by sub-partition; the
+        landed-byte counters of a sub-partition advance after its copies (stream order), with atomics on those slots only."""
+        flags = self.arena.flags()
+        with torch.cuda.stream(self.local_stream):
+            self.local_stream.wait_event(self.ev_go)
+            for j in range(self.subparts):
+                for dst, src in pset["local"][j]:
+                    dst.copy_(src, non_blocking=True)
+                flags.index_add_(0, pset["local_idx"][j], pset["local_bytes"][j])
+            self.ev_local.record(self.local_stream)
 
     def _merge_sub(self, j: int, out: torch.Tensor) -> None:
         C, nruns = self.subparts, self.plan.nruns
@@ -179,13 +224,15 @@ class TeraSortJob:
         off = sum(self.sub_n[:j]) * TERA_STRIDE
         self.merger.merge_fixed(out=out[off:], write_eof=(j == C - 1))
 
-    def step(self, descs: Optional[List[torch.Tensor]] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def step(self, pset: Optional[dict] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One shuffle + merge. Flags are cumulative counters, so step ``i`` waits for ``i * bytes``; the
         all-rank barrier at the top keeps a fast rank from overwriting an arena that is still being merged.
         With ``subparts > 1`` the pushes of all sub-partitions are queued on a side stream and the merge of
-        sub-partition j starts as soon as its runs have landed, i.e. while sub-partition j+1 is still in flight."""
+        sub-partition j starts as soon as its runs have landed, i.e. while sub-partition j+1 is still in flight.
+        ``pset``: the tables of another set of map-output buffers (:meth:`_push_tables`), default the job's own."""
         self.steps_run += 1
-        descs = self.push_descs_dev if descs is None else descs
+        pset = self.push_set if pset is None else pset
+        descs = pset["tables"]
         out = self.merger.out if out is None else out
         C = self.subparts
         cur = torch.cuda.current_stream(self.device)
@@ -193,20 +240,26 @@ class TeraSortJob:
             self.arena.barrier()
         self.expect.add_(self.expect_step)
         tma = self.push_mode == "tma"
-        if tma:
-            all_descs = self.push_descs_all if descs is self.push_descs_dev else torch.cat(descs).contiguous()
+        ce = self.local_copy == "ce"
         if C == 1:
+            if ce:
+                self.ev_go.record(cur)
+                self._local_copies(pset, cur)
             if tma:
-                K.shuffle_push_tma(all_descs, self.nseg, 1, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
+                K.shuffle_push_tma(pset["all"], self.nseg, 1, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
             else:
                 K.shuffle_push(descs[0], self.nseg, self.push_scratch[0], self.push_ctas, self.world)
             self._merge_sub(0, out)
+            if ce:
+                cur.wait_event(self.ev_local)
         else:
             self.ev_go.record(cur)
+            if ce:
+                self._local_copies(pset, cur)
             with torch.cuda.stream(self.push_stream):
                 self.push_stream.wait_event(self.ev_go)
                 if tma:
-                    K.shuffle_push_tma(all_descs, self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
+                    K.shuffle_push_tma(pset["all"], self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
                 else:
                     for j in range(C):
                         K.shuffle_push(descs[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
@@ -214,6 +267,8 @@ class TeraSortJob:
             for j in range(C):
                 self._merge_sub(j, out)
             cur.wait_event(self.ev_pushed)  # the step is over only when this rank's own pushes have retired
+            if ce:
+                cur.wait_event(self.ev_local)
         return out[: self.n_out * TERA_STRIDE + 2]
 
     def capture(self):
@@ -242,6 +297,8 @@ class TeraSortJob:
         self.expect.add_(self.expect_step)
         t0.record(cur)
         self.ev_go.record(cur)
+        if self.local_copy == "ce":
+            self._local_copies(self.push_set, cur)
         with torch.cuda.stream(self.push_stream):
             self.push_stream.wait_event(self.ev_go)
             if self.push_mode == "tma":
@@ -262,6 +319,8 @@ class TeraSortJob:
             self.merger.merge_fixed(out=self.merger.out[sum(self.sub_n[:j]) * TERA_STRIDE:], write_eof=(j == C - 1))
             m1[j].record(cur)
         cur.wait_event(self.ev_pushed)
+        if self.local_copy == "ce":
+            cur.wait_event(self.ev_local)
         torch.cuda.synchronize(self.device)
         self.steps_run += 1
         return {"pushed_ms": [t0.elapsed_time(e) for e in pushed], "merge_start_ms": [t0.elapsed_time(e) for e in m0],
@@ -274,12 +333,18 @@ class TeraSortJob:
             self.arena.barrier()
         self.expect.add_(self.expect_step)
         ev[0].record()
+        if self.local_copy == "ce":   # on the copy engines, concurrently with the push kernel below
+            cur = torch.cuda.current_stream(self.device)
+            self.ev_go.record(cur)
+            self._local_copies(self.push_set, cur)
         if self.push_mode == "tma":
             K.shuffle_push_tma(self.push_descs_all, self.nseg * self.subparts, self.subparts, self.world, self.push_tma_scratch,
                                self.push_ctas, self.tma_flush)
         else:
             for j in range(self.subparts):  # phases are measured un-overlapped, one sub-partition after the other
                 K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
+        if self.local_copy == "ce":
+            torch.cuda.current_stream(self.device).wait_event(self.ev_local)
         ev[1].record()
         nr = self.plan.nruns * self.subparts
         K.wait_flags(self.arena.flags(), self.expect, nr, self.arena.status)
@@ -319,7 +384,7 @@ class TeraSortJob:
         self.h_ring = [torch.empty(self.E2E_RING_BYTES, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
         # second device buffer set
         self.d_mofs = [[m.data for m in self.mofs], [torch.empty_like(m.data) for m in self.mofs]]
-        self.d_descs = [self.push_descs_dev, self._push_tables([t.data_ptr() for t in self.d_mofs[1]])]
+        self.d_descs = [self.push_set, self._push_tables(self.d_mofs[1])]
         self.d_out = [self.merger.out, torch.empty_like(self.merger.out)]
         self.s_h2d, self.s_d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
         self.ev_h2d = [torch.cuda.Event(), torch.cuda.Event()]
