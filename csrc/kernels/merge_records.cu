@@ -123,7 +123,7 @@ __device__ __forceinline__ uint32_t ub_records(const uint8_t* __restrict__ base,
 }
 
 // ------------------------------------------------------------------------------------------- 0
-__global__ void fr_range_kernel(const UdaRunDesc* __restrict__ runs, int k, int stride, int key_off, int key_len,
+__global__ void fr_range_kernel(const UdaRunDesc* __restrict__ runs, int k, int stride, int key_off, int key_len, int nb,
                                 FrParams* __restrict__ prm) {
     __shared__ unsigned long long smin, smax;
     if (threadIdx.x == 0) { smin = ~0ull; smax = 0ull; }
@@ -146,7 +146,7 @@ __global__ void fr_range_kernel(const UdaRunDesc* __restrict__ runs, int k, int 
         if (lo > hi) { lo = 0; hi = 0; }
         unsigned long long range = hi - lo;
         int shift = 0;
-        while (shift < 64 && (range >> shift) >= (unsigned long long)FR_NB) ++shift;
+        while (shift < 64 && (range >> shift) >= (unsigned long long)nb) ++shift;
         prm->kmin = lo; prm->kmax = hi; prm->shift = shift;
         prm->fallback_buckets = 0; prm->fallback_iters = 0; prm->tree_tiles = 0;
         prm->next_bucket = 0;
@@ -174,11 +174,11 @@ __global__ void fr_sample_hist_kernel(const UdaRunDesc* __restrict__ runs, int s
 // ------------------------------------------------------------------------------------------- 3
 // boundary key of every bucket: bkey[q] = first key of bucket q (w0 only, tail 0); kind[q]: 0 = start of the
 // run (q == 0), 1 = search for bkey[q], 2 = end of the run (past the last sample / q == G)
-__global__ void fr_bkeys_kernel(int G, int per, const uint32_t* __restrict__ cum, const FrParams* __restrict__ prm,
+__global__ void fr_bkeys_kernel(int G, int per, int nb, const uint32_t* __restrict__ cum, const FrParams* __restrict__ prm,
                                 unsigned long long* __restrict__ bkey, uint8_t* __restrict__ kind) {
     for (int q = blockIdx.x * blockDim.x + threadIdx.x; q <= G; q += gridDim.x * blockDim.x) {
         const unsigned long long want = (unsigned long long)q * (unsigned long long)per;
-        int lo = 0, hi = FR_NB;
+        int lo = 0, hi = nb;
         while (lo < hi) {
             int mid = (lo + hi) >> 1;
             if ((unsigned long long)__ldg(&cum[mid]) < want) lo = mid + 1; else hi = mid;
@@ -186,7 +186,7 @@ __global__ void fr_bkeys_kernel(int G, int per, const uint32_t* __restrict__ cum
         uint8_t kd = 1;
         unsigned long long key = 0;
         if (q == 0) kd = 0;
-        else if (lo >= FR_NB || q == G) kd = 2;
+        else if (lo >= nb || q == G) kd = 2;
         else {
             key = prm->kmin + ((unsigned long long)lo << prm->shift);
             if (key < prm->kmin) kd = 2;  // wrapped past the top of the key space
@@ -916,8 +916,12 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
         const int per = fr_target(cap) / FR_SAMPLE;     // samples per bucket
         FrScratch s = fr_layout(scratch, n, nruns, cap);
         const int G = fr_num_buckets(n, cap);
-        fr_range_kernel<<<1, 256, 0, stream>>>(runs_dev, nruns, stride, key_off, key_len, s.prm);
-        UDA_CUDA(cudaMemsetAsync(s.hist, 0, (size_t)(FR_NB + 1) * 4, stream));
+        // histogram bins: ~10 per bucket is plenty; a sub-partition of a pipelined step (10 M records) then clears and scans
+        // 2 MB instead of 16 MB
+        int nb = 1 << 16;
+        while (nb < FR_NB && (long long)nb * 32 < n) nb <<= 1;
+        fr_range_kernel<<<1, 256, 0, stream>>>(runs_dev, nruns, stride, key_off, key_len, nb, s.prm);
+        UDA_CUDA(cudaMemsetAsync(s.hist, 0, (size_t)(nb + 1) * 4, stream));
         {
             long long ns = max_nrec / FR_SAMPLE;
             long long bx = (ns + 255) / 256;
@@ -928,12 +932,12 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
             dim3 grid((unsigned)bx, (unsigned)nruns);
             fr_sample_hist_kernel<<<grid, 256, 0, stream>>>(runs_dev, stride, key_off, key_len, s.prm, s.hist);
         }
-        int rc = scan4::exclusive(s.hist, FR_NB, s.hist, s.sums, stream);
+        int rc = scan4::exclusive(s.hist, nb, s.hist, s.sums, stream);
         if (rc) return rc;
         {
             int bq = (G + 1 + 255) / 256;
             if (bq > kNumSMs * 8) bq = kNumSMs * 8;
-            fr_bkeys_kernel<<<bq, 256, 0, stream>>>(G, per, s.hist, s.prm, s.bkey, s.kind);
+            fr_bkeys_kernel<<<bq, 256, 0, stream>>>(G, per, nb, s.hist, s.prm, s.bkey, s.kind);
             if (nruns <= 16) {  // measured: search 0.5 ms at k = 8 (a boundary falls only every ~50 records of a run)
                 long long t = (long long)(G + 1) * nruns;
                 long long b = (t + 255) / 256;

@@ -81,7 +81,7 @@ class TeraSortJob:
         #: how a rank's OWN map outputs reach its arena. "push": through the push kernel like the remote ones. "ce": with
         #: the GPU's copy engines (one device-to-device cudaMemcpyAsync per segment on a stream of its own, then one
         #: atomic add of the landed bytes per sub-partition), so the SMs reserved for the push move only what must cross
-        #: NVLink. "auto": "ce" when the step is pipelined over several GPUs, "push" otherwise.
+        #: NVLink. "auto": "ce" when the step is pipelined (several sub-partitions), "push" otherwise.
         assert local_copy in ("auto", "push", "ce")
         self.local_copy = local_copy
         #: polls of the landed-byte counters before the wait kernel gives up and records a time-out in the arena's
@@ -127,7 +127,7 @@ class TeraSortJob:
         # ---- arena + tables (one push table and one run table per sub-partition)
         self.arena = SymmetricArena(self.plan.max_arena_bytes(), nruns * C, dev, self.group)
         if self.local_copy == "auto":
-            self.local_copy = "ce" if (P > 1 and C > 1 and not self.local_zero_copy) else "push"
+            self.local_copy = "ce" if (C > 1 and not self.local_zero_copy) else "push"
         if self.local_zero_copy:
             self.local_copy = "push"
         self.local_stream = torch.cuda.Stream(dev) if self.local_copy == "ce" else None
@@ -241,11 +241,14 @@ class TeraSortJob:
         self.expect.add_(self.expect_step)
         tma = self.push_mode == "tma"
         ce = self.local_copy == "ce"
+        nothing_remote = ce and self.world == 1       # one GPU, copy engines: the push kernel would find only empty descriptors
         if C == 1:
             if ce:
                 self.ev_go.record(cur)
                 self._local_copies(pset, cur)
-            if tma:
+            if nothing_remote:
+                pass
+            elif tma:
                 K.shuffle_push_tma(pset["all"], self.nseg, 1, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
             else:
                 K.shuffle_push(descs[0], self.nseg, self.push_scratch[0], self.push_ctas, self.world)
@@ -258,7 +261,9 @@ class TeraSortJob:
                 self._local_copies(pset, cur)
             with torch.cuda.stream(self.push_stream):
                 self.push_stream.wait_event(self.ev_go)
-                if tma:
+                if nothing_remote:
+                    pass
+                elif tma:
                     K.shuffle_push_tma(pset["all"], self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
                 else:
                     for j in range(C):
@@ -433,6 +438,8 @@ class TeraSortJob:
     @property
     def launches_per_step(self) -> int:
         push = 2 if self.push_mode == "tma" else 2 * self.subparts     # plan + push: one pair for all sub-partitions with tma
+        if self.local_copy == "ce" and self.world == 1:
+            push = 0                                                   # everything travels on the copy engines
         return (1 if self.world > 1 else 0) + push + self.subparts * (1 + DeviceMerger.LAUNCHES_PER_MERGE)
 
     # ------------------------------------------------------------------------------------ check

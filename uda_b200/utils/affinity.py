@@ -68,7 +68,10 @@ def bind_to_gpu_numa(index: int) -> dict:
         cpus = local & allowed
         info["local_cpus"], info["allowed_cpus"] = len(local), len(allowed)
         if not cpus or cpus == allowed:
-            return info           # nothing to narrow (single node, or a cpuset that excludes the local CPUs)
+            # nothing to narrow: the GPU's local CPU list is the whole allowed set (a single-NUMA-node host or VM, where
+            # numa_node reads -1), or the cpuset excludes the local CPUs
+            info["reason"] = "local CPU list equals the allowed set (single NUMA node)" if cpus else "cpuset excludes the GPU's local CPUs"
+            return info
         os.sched_setaffinity(0, cpus)
         info["bound"], info["cpus"] = True, len(cpus)
     except Exception as e:  # noqa: BLE001 - affinity is an optimisation
