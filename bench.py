@@ -60,6 +60,9 @@ def parse_args():
     ap.add_argument("--local-copy", default="auto", choices=["auto", "push", "ce"],
                     help="a rank's own map outputs reach its arena through the push kernel or through the copy engines "
                          "(auto: copy engines when the step is pipelined over sub-partitions)")
+    ap.add_argument("--arena-slots", type=int, default=0,
+                    help="receive slots per reducer (0 = one per sub-partition: the arena holds the whole partition; fewer = a ring "
+                         "with credit-based back-pressure, receive memory = slots / subparts of the partition)")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to the CPUs local to its GPU")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-check", action="store_true")
@@ -267,7 +270,8 @@ def main():
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev).setup()
     else:
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev, subparts=a.subparts, push_ctas=a.push_ctas,
-                  merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode, local_zero_copy=a.local_zero_copy, tma_flush=a.tma_flush, local_copy=a.local_copy).setup()
+                  merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode, local_zero_copy=a.local_zero_copy, tma_flush=a.tma_flush, local_copy=a.local_copy,
+                  arena_slots=a.arena_slots).setup()
     total_bytes = float(a.records_per_gpu) * RECORD_BYTES * world
 
     def timed(fn, steps, warmup, sample_clocks):
@@ -340,7 +344,9 @@ def main():
                 "model": "TeraSort 100 GB/8 GPUs (12.5 GB per GPU), 100-byte teragen records, IFile-framed sorted MOFs in HBM",
                 "global_batch": a.records_per_gpu * world, "seq_len": RECORD_BYTES,
                 "records_per_gpu": a.records_per_gpu, "maps_per_gpu": a.maps_per_gpu, "runs_per_reducer": a.maps_per_gpu * world,
-                "subparts": a.subparts, "push_mode": a.push_mode, "local_zero_copy": a.local_zero_copy, "local_copy": getattr(job, "local_copy", None), "cuda_graph": bool(a.graph), "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
+                "subparts": a.subparts, "push_mode": a.push_mode, "local_zero_copy": a.local_zero_copy, "local_copy": getattr(job, "local_copy", None),
+                "arena_slots": (job.plan.slots if hasattr(job, "plan") else None), "arena_bytes": (int(job.plan.max_arena_bytes()) if hasattr(job, "plan") else None),
+                "cuda_graph": bool(a.graph), "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
                 "parallelism": f"partition-parallel a2a x{world} (one reducer per GPU)",
                 "l2_policy": "inputs (12.75 GB/GPU) larger than the 126 MB L2; no flush needed",
                 "timed_region": "shuffle push + flag acquire + key normalise + k-way merge + record gather (map-side sort is set-up)",

@@ -140,8 +140,15 @@ struct TpDesc {
 };
 constexpr int TP_BATCH = 32;  // chunks resolved at once, one per lane
 
+// Receive ring (credit != nullptr): the destination arenas hold only `slots` sub-partitions. Before a warp touches
+// sub-partition j it finishes and publishes everything it has in flight (a reducer may be waiting for exactly those bytes
+// before it can merge and hand out the credit this warp is about to wait for), then waits until every reducer has merged
+// the sub-partition that used the slot before: credit[p] >= need0 + j, written by reducer p with a system-scope release
+// (uda_credit_publish). All ranks push in sub-partition order, so the oldest outstanding sub-partition can always complete.
 __global__ void __launch_bounds__(32 * TP_WARPS, 1) push_tma_kernel(const UdaPushDesc* __restrict__ d, int nseg, int nsub, unsigned nway,
-                                                         const unsigned* __restrict__ chunk_prefix, const TpSub* __restrict__ subg, int flush) {
+                                                         const unsigned* __restrict__ chunk_prefix, const TpSub* __restrict__ subg, int flush,
+                                                         const unsigned long long* __restrict__ credit, int world, long long need0,
+                                                         unsigned long long max_spins, unsigned* __restrict__ status) {
     extern __shared__ __align__(128) uint8_t tp_smem[];
     __shared__ __align__(8) uint64_t mbar_all[TP_WARPS][TP_STAGES];
     __shared__ TpStage stage_all[TP_WARPS][TP_STAGES];
@@ -176,82 +183,108 @@ __global__ void __launch_bounds__(32 * TP_WARPS, 1) push_tma_kernel(const UdaPus
     const int n_my = vfirst < vtotal ? (int)((vtotal - vfirst + vstride - 1) / vstride) : 0;
     int published = 0;  // lane 0 only: chunks [0, published) of this warp have had their counters advanced
 
-    for (int base = 0; base < n_my + TP_AHEAD; base += TP_BATCH) {
-        // ---- all lanes: resolve chunk base+lane (which bytes is virtual chunk v?) and copy its unaligned fringes
-        const int it_l = base + lane;
-        {
-            unsigned body = 0, len = 0;
-            unsigned long long* flag = nullptr;
-            uint8_t* dst_body = nullptr;
-            const uint8_t* src_body = nullptr;
-            if (it_l < n_my) {
-                const unsigned v = vfirst + (unsigned)it_l * vstride;
-                int j = 0;
-                while (j + 1 < nsub && v >= sub.vstart[j + 1]) ++j;
-                const unsigned li = v - sub.vstart[j];
-                const unsigned rel = (li % nway) * sub.per[j] + li / nway;
-                const unsigned cnt = sub.cstart[j + 1] - sub.cstart[j];
-                if (rel < cnt) {
-                    const unsigned c = sub.cstart[j] + rel;
-                    int lo = 0, hi = nseg - 1;  // last segment with chunk_prefix[seg] <= c
-                    while (lo < hi) {
-                        int mid = (lo + hi + 1) >> 1;
-                        if (cp[mid] <= c) lo = mid; else hi = mid - 1;
+    int it_begin = 0;
+    for (int js = 0; js < nsub; ++js) {
+        // this warp's chunks of sub-partition js: `it` in [it_begin, it_end)
+        const unsigned ve = sub.vstart[js + 1];
+        const int it_end = ve > vfirst ? (int)((ve - vfirst + vstride - 1) / vstride) : 0;
+        if (credit != nullptr) {
+            int ok = 1;
+            if (lane == 0) {
+                tma_store_wait<0>();                       // everything issued so far has landed ...
+                tp_publish(hist, published, it_begin);     // ... and is visible to its reducer
+                const long long need = need0 + js;
+                if (need > 0) {
+                    for (int p = 0; p < world && ok; ++p) {
+                        unsigned long long spins = 0;
+                        while ((long long)ld_acquire_sys(credit + p) < need) {
+                            if (++spins > max_spins) { ok = 0; atomicExch(status, 3u); break; }
+                            __nanosleep(500);
+                        }
                     }
-                    const UdaPushDesc sd = dd[lo];
-                    const long long off = (long long)(c - cp[lo]) * TP_CHUNK;
-                    len = (unsigned)(sd.bytes - off < TP_CHUNK ? sd.bytes - off : TP_CHUNK);
-                    const uint8_t* src = (const uint8_t*)sd.src + off;
-                    uint8_t* dst = (uint8_t*)sd.dst + off;
-                    flag = (unsigned long long*)sd.flag;
-                    if ((((uintptr_t)src ^ (uintptr_t)dst) & 15) != 0) {
-                        for (unsigned i = 0; i < len; ++i) dst[i] = src[i];  // incompatible phases (not produced by our layouts)
-                    } else {
-                        unsigned head = (unsigned)((16 - ((uintptr_t)src & 15)) & 15);
-                        if (head > len) head = len;
-                        body = (len - head) & ~15u;
-                        for (unsigned i = 0; i < head; ++i) dst[i] = src[i];
-                        for (unsigned i = head + body; i < len; ++i) dst[i] = src[i];
-                        src_body = src + head;
-                        dst_body = dst + head;
-                    }
-                }
-                hist.flag[it_l % TP_HIST] = flag;
-                hist.len[it_l % TP_HIST] = len;
-            }
-            tab[lane].src_body = src_body;
-            tab[lane].dst_body = dst_body;
-            tab[lane].body = body;
-        }
-        __syncwarp();
-        // ---- lane 0: the copy pipeline over this batch
-        if (lane == 0) {
-            const int end = base + TP_BATCH < n_my + TP_AHEAD ? base + TP_BATCH : n_my + TP_AHEAD;
-            for (int it = base; it < end; ++it) {
-                if (it < n_my) {
-                    const int s = it % TP_STAGES;
-                    // the stage is free again once the store that used it has READ it; landing is tracked separately
-                    if (it >= TP_STAGES) tma_store_wait_read<TP_STAGES - 1 - TP_AHEAD>();
-                    if (it % flush == 0 && it - TP_AHEAD - TP_LAG > published) {
-                        tma_store_wait<TP_LAG>();   // groups committed so far: chunks [0, it - TP_AHEAD)
-                        tp_publish(hist, published, it - TP_AHEAD - TP_LAG);
-                    }
-                    const TpDesc t = tab[it - base];
-                    stage[s].body = t.body;
-                    stage[s].dst_body = t.dst_body;
-                    mbar_expect_tx(&mbar[s], t.body);
-                    if (t.body) tma_load_1d(ring + (size_t)s * TP_CHUNK, t.src_body, t.body, &mbar[s]);
-                }
-                const int jt = it - TP_AHEAD;
-                if (jt >= 0 && jt < n_my) {
-                    const int s2 = jt % TP_STAGES;
-                    mbar_wait(&mbar[s2], (uint32_t)(jt / TP_STAGES) & 1u);
-                    if (stage[s2].body) tma_store_1d(stage[s2].dst_body, ring + (size_t)s2 * TP_CHUNK, stage[s2].body);
-                    tma_store_commit();  // one group per chunk, empty or not, so that wait_group counts chunks
                 }
             }
+            ok = __shfl_sync(0xffffffffu, ok, 0);
+            if (!ok) return;                               // a reducer never freed its slot: give up (status word = 3)
         }
-        __syncwarp();
+        for (int base = it_begin; base < it_end + TP_AHEAD; base += TP_BATCH) {
+            // ---- all lanes: resolve chunk base+lane (which bytes is virtual chunk v?) and copy its unaligned fringes
+            const int it_l = base + lane;
+            {
+                unsigned body = 0, len = 0;
+                unsigned long long* flag = nullptr;
+                uint8_t* dst_body = nullptr;
+                const uint8_t* src_body = nullptr;
+                if (it_l < it_end) {
+                    const unsigned v = vfirst + (unsigned)it_l * vstride;
+                    int j = 0;
+                    while (j + 1 < nsub && v >= sub.vstart[j + 1]) ++j;
+                    const unsigned li = v - sub.vstart[j];
+                    const unsigned rel = (li % nway) * sub.per[j] + li / nway;
+                    const unsigned cnt = sub.cstart[j + 1] - sub.cstart[j];
+                    if (rel < cnt) {
+                        const unsigned c = sub.cstart[j] + rel;
+                        int lo = 0, hi = nseg - 1;  // last segment with chunk_prefix[seg] <= c
+                        while (lo < hi) {
+                            int mid = (lo + hi + 1) >> 1;
+                            if (cp[mid] <= c) lo = mid; else hi = mid - 1;
+                        }
+                        const UdaPushDesc sd = dd[lo];
+                        const long long off = (long long)(c - cp[lo]) * TP_CHUNK;
+                        len = (unsigned)(sd.bytes - off < TP_CHUNK ? sd.bytes - off : TP_CHUNK);
+                        const uint8_t* src = (const uint8_t*)sd.src + off;
+                        uint8_t* dst = (uint8_t*)sd.dst + off;
+                        flag = (unsigned long long*)sd.flag;
+                        if ((((uintptr_t)src ^ (uintptr_t)dst) & 15) != 0) {
+                            for (unsigned i = 0; i < len; ++i) dst[i] = src[i];  // incompatible phases (not produced by our layouts)
+                        } else {
+                            unsigned head = (unsigned)((16 - ((uintptr_t)src & 15)) & 15);
+                            if (head > len) head = len;
+                            body = (len - head) & ~15u;
+                            for (unsigned i = 0; i < head; ++i) dst[i] = src[i];
+                            for (unsigned i = head + body; i < len; ++i) dst[i] = src[i];
+                            src_body = src + head;
+                            dst_body = dst + head;
+                        }
+                    }
+                    hist.flag[it_l % TP_HIST] = flag;
+                    hist.len[it_l % TP_HIST] = len;
+                }
+                tab[lane].src_body = src_body;
+                tab[lane].dst_body = dst_body;
+                tab[lane].body = body;
+            }
+            __syncwarp();
+            // ---- lane 0: the copy pipeline over this batch
+            if (lane == 0) {
+                const int end = base + TP_BATCH < it_end + TP_AHEAD ? base + TP_BATCH : it_end + TP_AHEAD;
+                for (int it = base; it < end; ++it) {
+                    if (it < it_end) {
+                        const int s = it % TP_STAGES;
+                        // the stage is free again once the store that used it has READ it; landing is tracked separately
+                        if (it >= TP_STAGES) tma_store_wait_read<TP_STAGES - 1 - TP_AHEAD>();
+                        if (it % flush == 0 && it - TP_AHEAD - TP_LAG > published) {
+                            tma_store_wait<TP_LAG>();   // groups committed so far: chunks [0, it - TP_AHEAD)
+                            tp_publish(hist, published, it - TP_AHEAD - TP_LAG);
+                        }
+                        const TpDesc t = tab[it - base];
+                        stage[s].body = t.body;
+                        stage[s].dst_body = t.dst_body;
+                        mbar_expect_tx(&mbar[s], t.body);
+                        if (t.body) tma_load_1d(ring + (size_t)s * TP_CHUNK, t.src_body, t.body, &mbar[s]);
+                    }
+                    const int jt = it - TP_AHEAD;
+                    if (jt >= it_begin && jt < it_end) {
+                        const int s2 = jt % TP_STAGES;
+                        mbar_wait(&mbar[s2], (uint32_t)(jt / TP_STAGES) & 1u);
+                        if (stage[s2].body) tma_store_1d(stage[s2].dst_body, ring + (size_t)s2 * TP_CHUNK, stage[s2].body);
+                        tma_store_commit();  // one group per chunk, empty or not, so that wait_group counts chunks
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        it_begin = it_end;
     }
     if (lane == 0) {
         tma_store_wait<0>();
@@ -267,8 +300,9 @@ extern "C" long long uda_push_tma_scratch_bytes(int nseg) {
     return ((long long)(nseg + 1) * 4 + 15) / 16 * 16 + (long long)sizeof(uda::TpSub) + 64;
 }
 
-extern "C" int uda_shuffle_push_tma(const UdaPushDesc* descs_dev, int nseg, int nsub, int nway, void* scratch, int num_ctas,
-                                    int flush_chunks, cudaStream_t stream) {
+static int push_tma_launch(const UdaPushDesc* descs_dev, int nseg, int nsub, int nway, void* scratch, int num_ctas, int flush_chunks,
+                           const unsigned long long* credit, int world, long long need0, unsigned long long max_spins, unsigned* status,
+                           cudaStream_t stream) {
     using namespace uda;
     if (flush_chunks == 0) flush_chunks = 8;
     if (flush_chunks < 1 || flush_chunks > TP_FLUSH_MAX) return UDA_E_INVALID;
@@ -279,15 +313,40 @@ extern "C" int uda_shuffle_push_tma(const UdaPushDesc* descs_dev, int nseg, int 
     unsigned* chunk_prefix = (unsigned*)scratch;
     TpSub* sub = (TpSub*)((uint8_t*)scratch + ((size_t)(nseg + 1) * 4 + 15) / 16 * 16);
     const int smem = TP_WARPS * TP_STAGES * TP_CHUNK;
-    static bool attr_set[64] = {};
-    int dev = 0;
-    UDA_CUDA(cudaGetDevice(&dev));
-    if (dev < 64 && !attr_set[dev]) {
-        UDA_CUDA(cudaFuncSetAttribute(push_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr_set[dev] = true;
-    }
+    // the opt-in is a per-device attribute of the function
+    UDA_CUDA(cudaFuncSetAttribute(push_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     tp_plan_kernel<<<1, 1024, 0, stream>>>(descs_dev, nseg, nsub, (unsigned)nway, chunk_prefix, sub);
-    push_tma_kernel<<<num_ctas, 32 * TP_WARPS, smem, stream>>>(descs_dev, nseg, nsub, (unsigned)nway, chunk_prefix, sub, flush_chunks);
+    push_tma_kernel<<<num_ctas, 32 * TP_WARPS, smem, stream>>>(descs_dev, nseg, nsub, (unsigned)nway, chunk_prefix, sub, flush_chunks, credit, world,
+                                                              need0, max_spins, status);
+    UDA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int uda_shuffle_push_tma(const UdaPushDesc* descs_dev, int nseg, int nsub, int nway, void* scratch, int num_ctas,
+                                    int flush_chunks, cudaStream_t stream) {
+    return push_tma_launch(descs_dev, nseg, nsub, nway, scratch, num_ctas, flush_chunks, nullptr, 0, 0, 0, nullptr, stream);
+}
+
+extern "C" int uda_shuffle_push_tma_ring(const UdaPushDesc* descs_dev, int nseg, int nsub, int nway, void* scratch, int num_ctas,
+                                         int flush_chunks, const unsigned long long* credits_dev, int world, long long need0,
+                                         unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream) {
+    if (!credits_dev || !status_dev || world < 1 || world > 64) return UDA_E_INVALID;
+    return push_tma_launch(descs_dev, nseg, nsub, nway, scratch, num_ctas, flush_chunks, credits_dev, world, need0, max_spins, status_dev, stream);
+}
+
+namespace uda {
+// reducer side of the ring: one more sub-partition merged -> the new count goes to every sender's credit slot
+__global__ void credit_publish_kernel(unsigned long long* const* __restrict__ slots, int world, unsigned long long* __restrict__ counter) {
+    __shared__ unsigned long long v;
+    if (threadIdx.x == 0) { v = *counter + 1ull; *counter = v; }
+    __syncthreads();
+    if ((int)threadIdx.x < world) st_release_sys(slots[threadIdx.x], v);
+}
+}  // namespace uda
+
+extern "C" int uda_credit_publish(unsigned long long* const* credit_slots_dev, int world, unsigned long long* counter_dev, cudaStream_t stream) {
+    if (world < 1 || world > 64 || !credit_slots_dev || !counter_dev) return UDA_E_INVALID;
+    uda::credit_publish_kernel<<<1, 64, 0, stream>>>(credit_slots_dev, world, counter_dev);
     UDA_CHECK_LAUNCH();
     return 0;
 }

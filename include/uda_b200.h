@@ -149,6 +149,17 @@ long long uda_push_tma_scratch_bytes(int nseg);
  * (1..64, 0 = default 8): each advance costs one system-scope fence. */
 int uda_shuffle_push_tma(const UdaPushDesc* descs_dev, int nseg, int nsub, int nway, void* scratch, int num_ctas,
                          int flush_chunks, cudaStream_t stream);
+/* Receive ring with credits (reference: two 1 MiB buffers per map refilled on consumption, src/Merger/StreamRW.cc:462-486,
+ * sender throttled by credits, src/DataNet/RDMAServer.cc:44-136). The destination arenas hold fewer sub-partitions than the
+ * step has; before a copy warp touches sub-partition j it publishes what it has in flight and waits until
+ * credits_dev[p] >= need0 + j for every rank p < world (credits_dev: this rank's credit slots, written by the reducers).
+ * A wait that exceeds max_spins polls sets *status_dev = 3 and the warp stops pushing. */
+int uda_shuffle_push_tma_ring(const UdaPushDesc* descs_dev, int nseg, int nsub, int nway, void* scratch, int num_ctas,
+                              int flush_chunks, const unsigned long long* credits_dev, int world, long long need0,
+                              unsigned long long max_spins, unsigned* status_dev, cudaStream_t stream);
+/* reducer side: ++*counter_dev, then the new count is stored (system-scope release) to credit_slots_dev[p] for p < world */
+int uda_credit_publish(unsigned long long* const* credit_slots_dev, int world, unsigned long long* counter_dev,
+                       cudaStream_t stream);
 /* No counterpart in the reference (it has no device code and nothing that must avoid allocation).
  * Same push as uda_shuffle_push (chunks in descriptor order), but the chunk-prefix scratch is a fixed array inside the library,
  * so the call never allocates: for providers embedded in a process that does not own the GPU's free

@@ -563,6 +563,30 @@ def test_sort_job_single_gpu(built, kind, n, maps, side):
     job.close()
 
 
+@pytest.mark.parametrize("subparts,slots,local_copy", [(8, 2, "ce"), (6, 2, "push"), (5, 1, "ce")])
+def test_terasort_receive_ring_single_gpu(built, subparts, slots, local_copy):
+    """Receive ring on one GPU: the arena holds `slots` sub-partitions; a slot is refilled only after its merge."""
+    from uda_b200.models.terasort import TeraSortJob
+
+    n = 1_500_000
+    full = TeraSortJob(n, 3, device=_dev(), subparts=subparts, push_mode="tma", push_ctas=8, local_copy=local_copy)
+    ring = TeraSortJob(n, 3, device=_dev(), subparts=subparts, push_mode="tma", push_ctas=8, local_copy=local_copy, arena_slots=slots).setup()
+    try:
+        for _ in range(3):
+            out = ring.step()
+        res = ring.check(out)
+        assert res["ok"], res
+        assert ring.plan.slots == slots
+        full.setup()
+        assert ring.plan.max_arena_bytes() < 0.75 * full.plan.max_arena_bytes() * (slots + 1) / subparts + (1 << 20)
+        ref = full.step()
+        torch.cuda.synchronize()
+        assert torch.equal(ref, out)
+    finally:
+        ring.close()
+        full.close()
+
+
 # ------------------------------------------------------------------------------------------- fault injection
 def test_fault_lost_push_times_out_and_falls_back(built):
     """A push that sends fewer bytes than planned trips the wait kernel's watchdog; the controller raises the
@@ -578,7 +602,8 @@ def test_fault_lost_push_times_out_and_falls_back(built):
     calls = []
     fc = FallbackController(on_failure=calls.append)
     with fc.guard("shuffle"):
-        job.step(descs=bad)
+        pset = dict(job.push_set, tables=bad, all=torch.cat(bad).contiguous())
+        job.step(pset=pset)
         job.raise_on_failure()
     assert fc.failed and len(calls) == 1 and isinstance(calls[0], ShuffleTimeout)
     with fc.guard("merge") as active:

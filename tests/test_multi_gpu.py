@@ -32,6 +32,20 @@ def test_terasort_multi_rank(built, world, subparts, mode):
     assert text.count("MPRESULT") == world and text.count('"ok": true') == world, text[-6000:]
 
 
+@pytest.mark.parametrize("world,subparts,slots,local_copy", [(2, 8, 2, "ce"), (2, 8, 2, "push"), (2, 12, 3, "ce"), (8, 12, 3, "ce")])
+def test_terasort_receive_ring(built, world, subparts, slots, local_copy):
+    """Bounded receive memory: the arena holds `slots` of the `subparts` sub-partitions (a quarter of the partition),
+    senders wait for credits before they refill a slot. Several steps, so slots and credits are reused across steps; the
+    output must be the full sorted partition on every rank."""
+    if _ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    p = _torchrun(world, "mp_terasort.py", 2_000_000, 3, 4, subparts, "tma", 0, slots, local_copy)
+    text = p.stdout + "\n" + p.stderr
+    assert p.returncode == 0, text[-6000:]
+    assert text.count("MPRESULT") == world and text.count('"ok": true') == world, text[-6000:]
+    assert text.count(f'"slots": {slots}') == world
+
+
 def test_terasort_local_zero_copy_two_ranks(built):
     if _ngpu() < 2:
         pytest.skip("needs 2 GPUs")

@@ -68,6 +68,8 @@ _PROTOS = {
     "uda_shuffle_push_nway": (c_int, [c_vp, c_int, c_vp, c_int, c_int, c_vp]),
     "uda_push_tma_scratch_bytes": (c_ll, [c_int]),
     "uda_shuffle_push_tma": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_vp]),
+    "uda_shuffle_push_tma_ring": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_vp, c_int, c_ll, c_ull, c_vp, c_vp]),
+    "uda_credit_publish": (c_int, [c_vp, c_int, c_vp, c_vp]),
     "uda_wait_flags": (c_int, [c_vp, c_vp, c_int, c_ull, c_vp, c_vp]),
     "uda_barrier_all": (c_int, [c_vp, c_int, c_int, c_ull, c_ull, c_vp, c_vp]),
     "uda_barrier_all_counted": (c_int, [c_vp, c_int, c_int, c_vp, c_ull, c_vp, c_vp]),

@@ -14,6 +14,7 @@ One reducer per rank, one process per GPU (the reference has the same limit:
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional
 
 import numpy as np
@@ -54,7 +55,7 @@ class TeraSortJob:
 
     def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 1234,
                  key_bits: int = 0, group=None, push_ctas: int = 0, subparts: int = 1, merge_ctas_per_sm: int = 0,
-                 push_mode: str = "lsu", local_zero_copy: bool = False, tma_flush: int = 0, local_copy: str = "auto"):
+                 push_mode: str = "lsu", local_zero_copy: bool = False, tma_flush: int = 0, local_copy: str = "auto", arena_slots: int = 0):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -84,6 +85,11 @@ class TeraSortJob:
         #: NVLink. "auto": "ce" when the step is pipelined (several sub-partitions), "push" otherwise.
         assert local_copy in ("auto", "push", "ce")
         self.local_copy = local_copy
+        #: receive slots of the arena (0 = one per sub-partition: the arena holds the whole partition). Fewer slots than
+        #: sub-partitions make the arena a ring with credit-based back-pressure: receive memory = slots / subparts of the
+        #: partition (copy-engine push only).
+        self.arena_slots = arena_slots
+        self.ring_steps = 0
         #: polls of the landed-byte counters before the wait kernel gives up and records a time-out in the arena's
         #: status word (the watchdog that turns a lost push into a failure up-call instead of a hang)
         self.wait_max_spins = 50_000_000
@@ -121,7 +127,9 @@ class TeraSortJob:
             index = allt.cpu().numpy()
         else:
             index = local_idx[None]
-        self.plan = ShufflePlan(index, record_stride=TERA_STRIDE, subparts=C)
+        self.plan = ShufflePlan(index, record_stride=TERA_STRIDE, subparts=C, slots=self.arena_slots)
+        if self.plan.slots < C:
+            assert self.push_mode == "tma" and not self.local_zero_copy, "the receive ring needs the copy-engine push"
         nruns = self.plan.nruns
 
         # ---- arena + tables (one push table and one run table per sub-partition)
@@ -131,7 +139,7 @@ class TeraSortJob:
         if self.local_zero_copy:
             self.local_copy = "push"
         self.local_stream = torch.cuda.Stream(dev) if self.local_copy == "ce" else None
-        self.ev_local = torch.cuda.Event()
+        self.ev_local, self.ev_merged = torch.cuda.Event(), torch.cuda.Event()
         self.push_set = self._push_tables([m.data for m in self.mofs])
         self.push_descs_dev = self.push_set["tables"]
         self.nseg = self.maps * P
@@ -167,10 +175,54 @@ class TeraSortJob:
         self.ev_go, self.ev_pushed = torch.cuda.Event(), torch.cuda.Event()
         self.bytes_in = int(sum(int(m.index[:, 2].sum()) for m in self.mofs))
         self.record_bytes_local = self.n_local * 100
+        self._warm_up()
         torch.cuda.synchronize(dev)
         if P > 1:
             dist.barrier(group=self.group)
         return self
+
+    def _warm_up(self) -> None:
+        """Runs every kernel a step launches once, on an idle device. Kernels are loaded lazily at their first launch, and
+        that load waits for the kernels already running: inside a step some of those spin on the progress of kernels that are
+        launched later (the flag wait on the push, the push on the ring credits, which come from the merges), so a first
+        launch in the middle of a step blocks until a watchdog gives up. (Measured: the first ring step took 590 ms and
+        ended with a push time-out; the following steps 1.5 ms.) Nothing here touches the arena, counters or credits."""
+        dev, P, C = self.device, self.world, self.subparts
+        k = self.plan.nruns
+        # a tiny merge with the job's run count (selects the same partition kernel) over throw-away records
+        nrec = 4
+        recs = K.teragen(nrec * k, self.seed + 99, first_row=0, framed=True, key_bits=self.key_bits, device=dev)
+        pad = torch.zeros(recs.numel() + 256, dtype=torch.uint8, device=dev)
+        pad[64:64 + recs.numel()] = recs          # unsorted runs are fine: only the launches matter
+        desc, _off = K.make_run_descs([pad.data_ptr() + 64 + r * nrec * TERA_STRIDE for r in range(k)], [nrec] * k)
+        tmp_out = torch.empty(nrec * k * TERA_STRIDE + 66, dtype=torch.uint8, device=dev)
+        scratch = torch.empty(K.merge_records_scratch_bytes(nrec * k, k), dtype=torch.uint8, device=dev)
+        if self.merger.fused:
+            K.merge_records_fixed(K.to_device_struct(desc, dev), k, nrec * k, nrec, TERA_STRIDE, 2, 10, tmp_out, scratch, write_eof=True,
+                                  align2=True, ctas_per_sm=self.merge_ctas_per_sm)
+        # push kernels over a table of empty descriptors
+        empty = self.push_descs_all.clone()
+        host = empty.cpu().numpy().view(K.PUSH_DESC_DTYPE).copy()
+        host["bytes"][:] = 0
+        empty.copy_(torch.from_numpy(host.view(np.uint8).reshape(-1)))
+        dummy = torch.zeros(128, dtype=torch.int64, device=dev)
+        status = torch.zeros(4, dtype=torch.int32, device=dev)
+        if self.push_mode == "tma":
+            K.shuffle_push_tma(empty, self.nseg * C, C, P, self.push_tma_scratch, max(1, self.push_ctas), self.tma_flush)
+            if self.plan.slots < C:
+                K.shuffle_push_tma_ring(empty, self.nseg * C, C, P, self.push_tma_scratch, max(1, self.push_ctas), self.tma_flush, dummy, P, -C,
+                                        status, 1000)
+        K.shuffle_push(empty[: self.push_descs_dev[0].numel()], self.nseg, self.push_scratch[0], 8, P)
+        # flag wait (already satisfied), credit publication into a dummy table, the torch kernels of the copy-engine path
+        K.wait_flags(dummy[:4], dummy[4:8], 4, status, 10)
+        slots = torch.tensor([dummy.data_ptr() + 8 * (16 + p) for p in range(P)], dtype=torch.int64, device=dev)
+        K.credit_publish(slots, P, dummy[8:9])
+        dummy.index_add_(0, torch.tensor([40, 41], dtype=torch.int64, device=dev), torch.tensor([0, 0], dtype=torch.int64, device=dev))
+        dummy[64:96].add_(dummy[96:128])
+        tmp_out[:64].copy_(pad[:64], non_blocking=True)
+        if P > 1:
+            self.arena.barrier()      # collective: every rank calls setup()
+        torch.cuda.synchronize(dev)
 
     # ------------------------------------------------------------------------------------ step
     def _push_tables(self, mof_data: List[torch.Tensor]) -> dict:
@@ -204,76 +256,94 @@ class TeraSortJob:
                 local_bytes.append(torch.tensor(nb, dtype=torch.int64, device=self.device))
         return {"tables": tables, "all": torch.cat(tables).contiguous(), "local": local, "local_idx": local_idx, "local_bytes": local_bytes}
 
-    def _local_copies(self, pset: dict, cur) -> None:
-        """Queues this rank's own segments on the copy engines (stream of their own), sub-partition by sub-partition; the
+    def _local_copies(self, pset: dict, subs) -> None:
+        """Queues this rank's own segments of sub-partitions ``subs`` on the copy engines (stream of their own); the
         landed-byte counters of a sub-partition advance after its copies (stream order), with atomics on those slots only."""
         flags = self.arena.flags()
         with torch.cuda.stream(self.local_stream):
-            self.local_stream.wait_event(self.ev_go)
-            for j in range(self.subparts):
+            for j in subs:
                 for dst, src in pset["local"][j]:
                     dst.copy_(src, non_blocking=True)
                 flags.index_add_(0, pset["local_idx"][j], pset["local_bytes"][j])
             self.ev_local.record(self.local_stream)
 
-    def _merge_sub(self, j: int, out: torch.Tensor) -> None:
+    def _merge_sub(self, j: int, out: torch.Tensor, tl: Optional[dict] = None) -> None:
         C, nruns = self.subparts, self.plan.nruns
         K.wait_flags(self.arena.flags()[j * nruns:(j + 1) * nruns], self.expect[j * nruns:(j + 1) * nruns], nruns, self.arena.status,
                      self.wait_max_spins)
+        if tl is not None:
+            tl["m0"][j].record(torch.cuda.current_stream(self.device))
         self.merger.use_runs(self.sub_runs[j])
         off = sum(self.sub_n[:j]) * TERA_STRIDE
         self.merger.merge_fixed(out=out[off:], write_eof=(j == C - 1))
+        if tl is not None:
+            tl["m1"][j].record(torch.cuda.current_stream(self.device))
 
-    def step(self, pset: Optional[dict] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def step(self, pset: Optional[dict] = None, out: Optional[torch.Tensor] = None, _timeline: Optional[dict] = None) -> torch.Tensor:
         """One shuffle + merge. Flags are cumulative counters, so step ``i`` waits for ``i * bytes``; the
         all-rank barrier at the top keeps a fast rank from overwriting an arena that is still being merged.
         With ``subparts > 1`` the pushes of all sub-partitions are queued on a side stream and the merge of
         sub-partition j starts as soon as its runs have landed, i.e. while sub-partition j+1 is still in flight.
+        With ``arena_slots < subparts`` the arena is a ring: sub-partition j lands in slot ``j % slots`` after the
+        merge of sub-partition ``j - slots`` (credits for the remote senders, stream order for the local copies).
         ``pset``: the tables of another set of map-output buffers (:meth:`_push_tables`), default the job's own."""
         self.steps_run += 1
         pset = self.push_set if pset is None else pset
         descs = pset["tables"]
         out = self.merger.out if out is None else out
-        C = self.subparts
+        C, S = self.subparts, self.plan.slots
+        ring = S < C
         cur = torch.cuda.current_stream(self.device)
         if self.world > 1:
             self.arena.barrier()
         self.expect.add_(self.expect_step)
         tma = self.push_mode == "tma"
         ce = self.local_copy == "ce"
-        nothing_remote = ce and self.world == 1       # one GPU, copy engines: the push kernel would find only empty descriptors
-        if C == 1:
-            if ce:
-                self.ev_go.record(cur)
-                self._local_copies(pset, cur)
+        # one GPU, copy engines: the push kernel would find only empty descriptors (UDA_FORCE_PUSH_KERNEL=1 launches it anyway: tests)
+        nothing_remote = ce and self.world == 1 and not os.environ.get("UDA_FORCE_PUSH_KERNEL")
+        tl = _timeline
+        if tl is not None:
+            tl["t0"].record(cur)
+        self.ev_go.record(cur)
+        if ce:
+            self.local_stream.wait_event(self.ev_go)
+            self._local_copies(pset, range(min(S, C)))
+        push_stream = self.push_stream if C > 1 else cur
+        with torch.cuda.stream(push_stream):
+            if C > 1:
+                push_stream.wait_event(self.ev_go)
             if nothing_remote:
                 pass
+            elif tma and ring:
+                # cumulative sub-partitions merged before this step = ring_steps * C; sub-partition j needs j + 1 - S more
+                K.shuffle_push_tma_ring(pset["all"], self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush,
+                                        self.arena.credits, self.world, self.ring_steps * C + 1 - S, self.arena.status, self.wait_max_spins)
             elif tma:
-                K.shuffle_push_tma(pset["all"], self.nseg, 1, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
+                K.shuffle_push_tma(pset["all"], self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
             else:
-                K.shuffle_push(descs[0], self.nseg, self.push_scratch[0], self.push_ctas, self.world)
-            self._merge_sub(0, out)
-            if ce:
-                cur.wait_event(self.ev_local)
-        else:
-            self.ev_go.record(cur)
-            if ce:
-                self._local_copies(pset, cur)
-            with torch.cuda.stream(self.push_stream):
-                self.push_stream.wait_event(self.ev_go)
-                if nothing_remote:
-                    pass
-                elif tma:
-                    K.shuffle_push_tma(pset["all"], self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
-                else:
-                    for j in range(C):
-                        K.shuffle_push(descs[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
-                self.ev_pushed.record(self.push_stream)
-            for j in range(C):
-                self._merge_sub(j, out)
+                for j in range(C):
+                    K.shuffle_push(descs[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
+                    if tl is not None:
+                        tl["pushed"][j].record(push_stream)
+            if tl is not None and tma:
+                for j in range(C):
+                    tl["pushed"][j].record(push_stream)
+            if C > 1:
+                self.ev_pushed.record(push_stream)
+        for j in range(C):
+            self._merge_sub(j, out, tl)
+            if ring:
+                self.arena.publish_credit()            # slot j % S is free: remote senders may refill it ...
+                if ce and j + S < C:                   # ... and so may the local copies of sub-partition j + S
+                    self.ev_merged.record(cur)
+                    self.local_stream.wait_event(self.ev_merged)
+                    self._local_copies(pset, [j + S])
+        if ring:
+            self.ring_steps += 1
+        if C > 1:
             cur.wait_event(self.ev_pushed)  # the step is over only when this rank's own pushes have retired
-            if ce:
-                cur.wait_event(self.ev_local)
+        if ce:
+            cur.wait_event(self.ev_local)
         return out[: self.n_out * TERA_STRIDE + 2]
 
     def capture(self):
@@ -294,62 +364,44 @@ class TeraSortJob:
         C = self.subparts
         if C == 1:
             return {}
-        cur = torch.cuda.current_stream(self.device)
         mk = lambda: torch.cuda.Event(enable_timing=True)
-        t0, pushed, m0, m1 = mk(), [mk() for _ in range(C)], [mk() for _ in range(C)], [mk() for _ in range(C)]
-        if self.world > 1:
-            self.arena.barrier()
-        self.expect.add_(self.expect_step)
-        t0.record(cur)
-        self.ev_go.record(cur)
-        if self.local_copy == "ce":
-            self._local_copies(self.push_set, cur)
-        with torch.cuda.stream(self.push_stream):
-            self.push_stream.wait_event(self.ev_go)
-            if self.push_mode == "tma":
-                K.shuffle_push_tma(self.push_descs_all, self.nseg * C, C, self.world, self.push_tma_scratch, self.push_ctas, self.tma_flush)
-                for j in range(C):
-                    pushed[j].record(self.push_stream)
-            else:
-                for j in range(C):
-                    K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
-                    pushed[j].record(self.push_stream)
-            self.ev_pushed.record(self.push_stream)
-        nruns = self.plan.nruns
-        for j in range(C):
-            K.wait_flags(self.arena.flags()[j * nruns:(j + 1) * nruns], self.expect[j * nruns:(j + 1) * nruns], nruns, self.arena.status,
-                         self.wait_max_spins)
-            m0[j].record(cur)
-            self.merger.use_runs(self.sub_runs[j])
-            self.merger.merge_fixed(out=self.merger.out[sum(self.sub_n[:j]) * TERA_STRIDE:], write_eof=(j == C - 1))
-            m1[j].record(cur)
-        cur.wait_event(self.ev_pushed)
-        if self.local_copy == "ce":
-            cur.wait_event(self.ev_local)
+        tl = {"t0": mk(), "pushed": [mk() for _ in range(C)], "m0": [mk() for _ in range(C)], "m1": [mk() for _ in range(C)]}
+        self.step(_timeline=tl)
         torch.cuda.synchronize(self.device)
-        self.steps_run += 1
-        return {"pushed_ms": [t0.elapsed_time(e) for e in pushed], "merge_start_ms": [t0.elapsed_time(e) for e in m0],
-                "merge_end_ms": [t0.elapsed_time(e) for e in m1]}
+        t0 = tl["t0"]
+        return {"pushed_ms": [t0.elapsed_time(e) for e in tl["pushed"]], "merge_start_ms": [t0.elapsed_time(e) for e in tl["m0"]],
+                "merge_end_ms": [t0.elapsed_time(e) for e in tl["m1"]]}
 
     def step_phases(self) -> dict:
-        """One step with CUDA events between the phases (diagnostics; not used for the headline number)."""
+        """One step with CUDA events between the phases, run one after the other: everything pushed, then everything
+        waited for, then everything merged (diagnostics; not used for the headline number). With a receive ring the phases
+        cannot be separated (a push waits for merges): only the whole step is timed."""
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        if self.plan.slots < self.subparts:
+            ev[0].record()
+            self.step()
+            ev[3].record()
+            torch.cuda.synchronize(self.device)
+            return {"step_ms": ev[0].elapsed_time(ev[3])}
+        cur = torch.cuda.current_stream(self.device)
         if self.world > 1:
             self.arena.barrier()
         self.expect.add_(self.expect_step)
         ev[0].record()
         if self.local_copy == "ce":   # on the copy engines, concurrently with the push kernel below
-            cur = torch.cuda.current_stream(self.device)
             self.ev_go.record(cur)
-            self._local_copies(self.push_set, cur)
-        if self.push_mode == "tma":
+            self.local_stream.wait_event(self.ev_go)
+            self._local_copies(self.push_set, range(self.subparts))
+        if self.local_copy == "ce" and self.world == 1:
+            pass
+        elif self.push_mode == "tma":
             K.shuffle_push_tma(self.push_descs_all, self.nseg * self.subparts, self.subparts, self.world, self.push_tma_scratch,
                                self.push_ctas, self.tma_flush)
         else:
             for j in range(self.subparts):  # phases are measured un-overlapped, one sub-partition after the other
                 K.shuffle_push(self.push_descs_dev[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
         if self.local_copy == "ce":
-            torch.cuda.current_stream(self.device).wait_event(self.ev_local)
+            cur.wait_event(self.ev_local)
         ev[1].record()
         nr = self.plan.nruns * self.subparts
         K.wait_flags(self.arena.flags(), self.expect, nr, self.arena.status)

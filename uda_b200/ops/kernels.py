@@ -237,6 +237,19 @@ def shuffle_push_tma(descs_dev: torch.Tensor, nseg: int, nsub: int, nway: int, s
                                          _stream()), "uda_shuffle_push_tma")
 
 
+def shuffle_push_tma_ring(descs_dev: torch.Tensor, nseg: int, nsub: int, nway: int, scratch: torch.Tensor, num_ctas: int, flush_chunks: int,
+                          credits: torch.Tensor, world: int, need0: int, status: torch.Tensor, max_spins: int = 50_000_000) -> None:
+    """The copy-engine push into a receive RING: before a warp touches sub-partition ``j`` it waits until every
+    ``credits[p] >= need0 + j`` (reducer p has merged the sub-partition that used the slot before)."""
+    check(kernels().uda_shuffle_push_tma_ring(descs_dev.data_ptr(), nseg, nsub, nway, scratch.data_ptr(), num_ctas, flush_chunks,
+                                              credits.data_ptr(), world, need0, max_spins, status.data_ptr(), _stream()),
+          "uda_shuffle_push_tma_ring")
+
+
+def credit_publish(credit_slots_dev: torch.Tensor, world: int, counter_dev: torch.Tensor) -> None:
+    check(kernels().uda_credit_publish(credit_slots_dev.data_ptr(), world, counter_dev.data_ptr(), _stream()), "uda_credit_publish")
+
+
 def wait_flags(flags: torch.Tensor, expect: torch.Tensor, n: int, status: torch.Tensor, max_spins: int = 50_000_000) -> None:
     check(kernels().uda_wait_flags(flags.data_ptr(), expect.data_ptr(), n, max_spins, status.data_ptr(), _stream()),
           "uda_wait_flags")

@@ -12,7 +12,10 @@ into it over NVLink and publish flags that live in the same arena.
 Arena layout (offsets in bytes)::
 
     0      barrier pad   64 x u64   slot[r] written by rank r (uda_barrier_all)
-    512    status words  16 x u32, then the barrier epoch counter (u64 at 576)
+    512    status words  16 x u32, then the barrier epoch counter (u64 at 576) and this rank's count of merged
+                         sub-partitions (u64 at 640)
+    1024   credits       64 x u64   slot[r] = sub-partitions reducer r has merged so far (written by rank r into
+                         every peer's arena: uda_credit_publish; read by the push kernel before it refills a ring slot)
     4096   flags         max_runs x u64  "bytes landed" counter per incoming run
     D      data          receive segments (D = 4096-aligned)
 """
@@ -28,6 +31,7 @@ from .._lib import check, kernels
 
 BARRIER_OFF = 0
 STATUS_OFF = 512
+CREDIT_OFF = 1024
 FLAGS_OFF = 4096
 
 
@@ -103,6 +107,10 @@ class SymmetricArena:
         self.status = self.local_tensor()[STATUS_OFF:STATUS_OFF + 8].view(torch.int32)
         #: barrier epoch, kept on the device so that a barrier launch carries no host state (CUDA-graph replay)
         self.epoch_dev = self.local_tensor()[STATUS_OFF + 64:STATUS_OFF + 72].view(torch.int64)
+        #: receive-ring flow control: credits[r] = sub-partitions reducer r has merged (r writes it here), merged_dev = my own count
+        self.credits = self.local_tensor()[CREDIT_OFF:CREDIT_OFF + 8 * 64].view(torch.int64)
+        self.merged_dev = self.local_tensor()[STATUS_OFF + 128:STATUS_OFF + 136].view(torch.int64)
+        self.credit_slots_dev = torch.tensor([p + CREDIT_OFF + 8 * self.rank for p in self.peer_ptrs], dtype=torch.int64, device=device)
 
     # ---- views -------------------------------------------------------------------------------
     def local_tensor(self) -> torch.Tensor:
@@ -129,6 +137,12 @@ class SymmetricArena:
         from ..ops.kernels import barrier_all_counted
 
         barrier_all_counted(self.pads_dev, self.rank, self.world, self.epoch_dev, self.status)
+
+    def publish_credit(self) -> None:
+        """One more sub-partition of this reducer has been merged (its ring slot is free): tell every sender. Current stream."""
+        from ..ops.kernels import credit_publish
+
+        credit_publish(self.credit_slots_dev, self.world, self.merged_dev)
 
     def close(self) -> None:
         for p in self.peers:

@@ -46,7 +46,7 @@ class ShufflePlan:
     """``index[s][m][p] = (startOffset, rawLength, partLength)`` for every rank ``s``, local map ``m``,
     partition ``p``; all ranks hold the same array. ``record_stride`` > 0 marks a fixed-stride job."""
 
-    def __init__(self, index: np.ndarray, record_stride: int = 0, subparts: int = 1):
+    def __init__(self, index: np.ndarray, record_stride: int = 0, subparts: int = 1, slots: int = 0):
         index = np.asarray(index, dtype=np.int64)
         assert index.ndim == 4 and index.shape[3] == 3, "index must be [world, maps, P*subparts, 3]"
         self.index = index
@@ -56,16 +56,31 @@ class ShufflePlan:
         assert self.P == self.world and self.P * subparts == index.shape[2], "one reducer per rank (reference: src/Merger/reducer.h:137)"
         self.stride = record_stride
         self.nruns = self.world * self.maps
-        #: flat list over (reducer r, sub-partition j): self.layouts[r * subparts + j]; sub-partitions of one
-        #: reducer share one arena and are laid out one after the other
+        #: receive slots per reducer. ``slots == subparts`` (default): the arena holds the whole partition, every
+        #: sub-partition has a place of its own and a push never waits. ``slots < subparts``: a ring — sub-partition j
+        #: lands in slot ``j % slots`` and may only be pushed once the reducer has merged sub-partition ``j - slots``
+        #: (credits in peer memory, see uda_credit_publish), so receive memory is ``slots / subparts`` of the partition.
+        #: This is the counterpart of the reference's two 1 MiB buffers per map with credit-based flow control
+        #: (src/Merger/StreamRW.cc:462-486, src/DataNet/RDMAServer.cc:44-136).
+        self.slots = subparts if slots <= 0 or slots > subparts else slots
+        #: flat list over (reducer r, sub-partition j): self.layouts[r * subparts + j]
         self.layouts: List[ReducerLayout] = []
         self.arena_bytes: List[int] = []
         for r in range(self.P):
-            cur = _align(GATHER_SLACK)
-            for j in range(subparts):
-                lay, cur = self._layout(r, j, cur)
-                self.layouts.append(lay)
-            self.arena_bytes.append(_align(cur + GATHER_SLACK))
+            base = _align(GATHER_SLACK)
+            if self.slots == subparts:
+                cur = base
+                for j in range(subparts):   # one after the other
+                    lay, cur = self._layout(r, j, cur)
+                    self.layouts.append(lay)
+                self.arena_bytes.append(_align(cur + GATHER_SLACK))
+            else:
+                # every slot is as large as the largest sub-partition of this reducer
+                slot_bytes = _align(max(self._layout(r, j, 0)[1] for j in range(subparts)), 256)
+                for j in range(subparts):
+                    lay, _ = self._layout(r, j, base + (j % self.slots) * slot_bytes)
+                    self.layouts.append(lay)
+                self.arena_bytes.append(_align(base + self.slots * slot_bytes + GATHER_SLACK))
 
     def run_id(self, src_rank: int, m: int) -> int:
         return src_rank * self.maps + m
