@@ -63,6 +63,9 @@ def parse_args():
     ap.add_argument("--arena-slots", type=int, default=0,
                     help="receive slots per reducer (0 = one per sub-partition: the arena holds the whole partition; fewer = a ring "
                          "with credit-based back-pressure, receive memory = slots / subparts of the partition)")
+    ap.add_argument("--device-cuts", action="store_true",
+                    help="map outputs keep Hadoop's P partitions; the sub-partitions of the pipeline are cut on the device with "
+                         "splitters sampled from the sorted segments")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the rank to the CPUs local to its GPU")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-check", action="store_true")
@@ -271,7 +274,7 @@ def main():
     else:
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev, subparts=a.subparts, push_ctas=a.push_ctas,
                   merge_ctas_per_sm=a.merge_ctas_per_sm, push_mode=a.push_mode, local_zero_copy=a.local_zero_copy, tma_flush=a.tma_flush, local_copy=a.local_copy,
-                  arena_slots=a.arena_slots).setup()
+                  arena_slots=a.arena_slots, device_cuts=a.device_cuts).setup()
     total_bytes = float(a.records_per_gpu) * RECORD_BYTES * world
 
     def timed(fn, steps, warmup, sample_clocks):
@@ -346,6 +349,8 @@ def main():
                 "records_per_gpu": a.records_per_gpu, "maps_per_gpu": a.maps_per_gpu, "runs_per_reducer": a.maps_per_gpu * world,
                 "subparts": a.subparts, "push_mode": a.push_mode, "local_zero_copy": a.local_zero_copy, "local_copy": getattr(job, "local_copy", None),
                 "arena_slots": (job.plan.slots if hasattr(job, "plan") else None), "arena_bytes": (int(job.plan.max_arena_bytes()) if hasattr(job, "plan") else None),
+                "device_cuts": bool(a.device_cuts),
+                "subpart_balance_max_over_mean": (round(max(job.sub_n) * len(job.sub_n) / max(1, sum(job.sub_n)), 3) if getattr(job, "sub_n", None) else None),
                 "cuda_graph": bool(a.graph), "push_ctas": a.push_ctas, "merge_ctas_per_sm": a.merge_ctas_per_sm,
                 "parallelism": f"partition-parallel a2a x{world} (one reducer per GPU)",
                 "l2_policy": "inputs (12.75 GB/GPU) larger than the 126 MB L2; no flush needed",

@@ -587,6 +587,29 @@ def test_terasort_receive_ring_single_gpu(built, subparts, slots, local_copy):
         full.close()
 
 
+@pytest.mark.parametrize("key_bits", [0, 9])
+def test_terasort_device_cut_subpartitions(built, key_bits):
+    """Map outputs with Hadoop's P partitions; the sub-partitions of the pipelined step are cut on the device with sampled
+    splitters. Same records -> the merged stream must equal the one of the job whose maps wrote the sub-partitions."""
+    from uda_b200.models.terasort import TeraSortJob
+
+    n = 900_000
+    a = TeraSortJob(n, 4, device=_dev(), subparts=6, push_mode="tma", push_ctas=8, key_bits=key_bits, device_cuts=True).setup()
+    b = TeraSortJob(n, 4, device=_dev(), subparts=6, push_mode="tma", push_ctas=8, key_bits=key_bits).setup()
+    try:
+        assert a.mofs[0].num_partitions == 1 and b.mofs[0].num_partitions == 6
+        for _ in range(2):
+            oa, ob = a.step(), b.step()
+        assert a.check(oa)["ok"] and b.check(ob)["ok"]
+        torch.cuda.synchronize()
+        assert torch.equal(oa, ob)
+        if key_bits == 0:   # sampled equi-depth splitters: balanced sub-partitions
+            assert max(a.sub_n) <= 1.3 * sum(a.sub_n) / len(a.sub_n)
+    finally:
+        a.close()
+        b.close()
+
+
 # ------------------------------------------------------------------------------------------- fault injection
 def test_fault_lost_push_times_out_and_falls_back(built):
     """A push that sends fewer bytes than planned trips the wait kernel's watchdog; the controller raises the

@@ -55,7 +55,8 @@ class TeraSortJob:
 
     def __init__(self, records_per_rank: int, maps_per_rank: int, device: Optional[torch.device] = None, seed: int = 1234,
                  key_bits: int = 0, group=None, push_ctas: int = 0, subparts: int = 1, merge_ctas_per_sm: int = 0,
-                 push_mode: str = "lsu", local_zero_copy: bool = False, tma_flush: int = 0, local_copy: str = "auto", arena_slots: int = 0):
+                 push_mode: str = "lsu", local_zero_copy: bool = False, tma_flush: int = 0, local_copy: str = "auto", arena_slots: int = 0,
+                 device_cuts: bool = False):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -90,6 +91,11 @@ class TeraSortJob:
         #: partition (copy-engine push only).
         self.arena_slots = arena_slots
         self.ring_steps = 0
+        #: False: the map side writes P x subparts partitions (uniform sub-ranges), one segment per sub-partition.
+        #: True: the map outputs have the P partitions Hadoop writes (what src/MOFServer/IndexInfo.cc:237-335 serves) and the
+        #: sub-partitions are cut on the device: splitters sampled from the sorted segments of all ranks (equi-depth, so skewed
+        #: keys still give balanced sub-partitions), then one lower-bound search per (segment, splitter).
+        self.device_cuts = device_cuts
         #: polls of the landed-byte counters before the wait kernel gives up and records a time-out in the arena's
         #: status word (the watchdog that turns a lost push into a failure up-call instead of a hang)
         self.wait_max_spins = 50_000_000
@@ -102,8 +108,9 @@ class TeraSortJob:
         dev, P = self.device, self.world
         per_map = [self.n_local // self.maps + (1 if i < self.n_local % self.maps else 0) for i in range(self.maps)]
         C = self.subparts
-        splitters = uniform_splitters_w0(P * C)
-        task = MapTask(max(per_map), P * C, dev)
+        cmap = 1 if self.device_cuts else C
+        splitters = uniform_splitters_w0(P * cmap)
+        task = MapTask(max(per_map), P * cmap, dev)
         row0 = self.rank * self.n_local
         fp = 0
         for m, nm in enumerate(per_map):
@@ -119,7 +126,7 @@ class TeraSortJob:
         torch.cuda.synchronize(dev)
 
         # ---- index exchange (plumbing over the process group)
-        local_idx = np.stack([m.index for m in self.mofs])  # [maps, P, 3]
+        local_idx = self._device_cut_index() if (self.device_cuts and C > 1) else np.stack([m.index for m in self.mofs])  # [maps, P*C, 3]
         if P > 1:
             t = torch.from_numpy(local_idx).to(dev)
             allt = torch.empty((P,) + tuple(t.shape), dtype=torch.int64, device=dev)
@@ -180,6 +187,58 @@ class TeraSortJob:
         if P > 1:
             dist.barrier(group=self.group)
         return self
+
+    def _device_cut_index(self, samples_per_segment: int = 64) -> np.ndarray:
+        """Index ``[maps, P * subparts, 3]`` of sub-segments cut on the device out of P-partition map outputs.
+
+        Every rank samples ``samples_per_segment`` equi-depth keys from each of its sorted segments; the samples (and segment
+        sizes) are all-gathered, and every rank derives the same ``subparts - 1`` splitters per reducer as weighted quantiles of
+        that reducer's samples. The cut positions are lower bounds of the splitters inside each segment
+        (uda_lower_bound_records). A sub-segment is a slice of its parent: body bytes only, no EOF marker or checksum of its own."""
+        dev, P, C, q = self.device, self.world, self.subparts, samples_per_segment
+        maps = len(self.mofs)
+        samples = torch.zeros((maps, P, q), dtype=torch.int64, device=dev)
+        nrec = np.zeros((maps, P), dtype=np.int64)
+        for m, mof in enumerate(self.mofs):
+            for p in range(P):
+                start, raw, _part = (int(x) for x in mof.index[p])
+                nrec[m, p] = (raw - 2) // TERA_STRIDE
+                if nrec[m, p] > 0:
+                    samples[m, p] = K.sample_splitters(mof.data[start:], int(nrec[m, p]), TERA_STRIDE, 2, 10, q)
+        nrec_dev = torch.from_numpy(nrec).to(dev)
+        if P > 1:
+            all_s = torch.empty((P,) + tuple(samples.shape), dtype=torch.int64, device=dev)
+            all_n = torch.empty((P,) + tuple(nrec_dev.shape), dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(all_s, samples.contiguous(), group=self.group)
+            dist.all_gather_into_tensor(all_n, nrec_dev, group=self.group)
+        else:
+            all_s, all_n = samples[None], nrec_dev[None]
+        hs = all_s.cpu().numpy().view(np.uint64)          # [world, maps, P, q]
+        hn = all_n.cpu().numpy().astype(np.float64)       # [world, maps, P]
+        split = np.zeros((P, C - 1), dtype=np.uint64)
+        for p in range(P):
+            keys = hs[:, :, p, :].reshape(-1)
+            w = np.repeat(hn[:, :, p].reshape(-1) / q, q)
+            order = np.argsort(keys, kind="stable")
+            cum = np.cumsum(w[order])
+            total = cum[-1] if len(cum) else 0.0
+            for j in range(1, C):
+                i = int(np.searchsorted(cum, total * j / C, side="left")) if total > 0 else 0
+                split[p, j - 1] = keys[order][min(i, len(keys) - 1)] if len(keys) else 0
+            split[p] = np.maximum.accumulate(split[p])
+        self.sub_splitters = split
+        split_dev = torch.from_numpy(split.view(np.int64)).to(dev)
+        index = np.zeros((maps, P * C, 3), dtype=np.int64)
+        for m, mof in enumerate(self.mofs):
+            for p in range(P):
+                start, _raw, _part = (int(x) for x in mof.index[p])
+                n = int(nrec[m, p])
+                cuts = K.lower_bound_records(mof.data[start:], n, TERA_STRIDE, 2, 10, split_dev[p]).cpu().numpy() if n > 0 else np.zeros(C - 1, np.int64)
+                b = np.concatenate([[0], np.minimum(np.maximum.accumulate(cuts), n), [n]]).astype(np.int64)
+                for j in range(C):
+                    body = int(b[j + 1] - b[j]) * TERA_STRIDE
+                    index[m, p * C + j] = (start + int(b[j]) * TERA_STRIDE, body + 2, body)
+        return index
 
     def _warm_up(self) -> None:
         """Runs every kernel a step launches once, on an idle device. Kernels are loaded lazily at their first launch, and
@@ -533,6 +592,8 @@ class TeraSortJob:
 
     def landed_segments(self):
         """``(tensor at segment start, rawLength)`` of every run of every sub-partition landed in this rank's arena."""
+        if self.device_cuts and self.subparts > 1:
+            raise RuntimeError("sub-segments cut on the device are slices of their parent segment: they carry no checksum of their own")
         data, segs = self.arena.data(), []
         for j in range(self.subparts):
             lay = self.plan.layout(self.rank, j)
