@@ -384,7 +384,7 @@ class TeraSortJob:
                     K.shuffle_push(descs[j], self.nseg, self.push_scratch[j], self.push_ctas, self.world)
                     if tl is not None:
                         tl["pushed"][j].record(push_stream)
-            if tl is not None and tma:
+            if tl is not None and (tma or nothing_remote):
                 for j in range(C):
                     tl["pushed"][j].record(push_stream)
             if C > 1:
