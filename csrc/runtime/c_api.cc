@@ -15,6 +15,7 @@
 #include "threads.h"
 #include "../../include/uda_rt_api.h"
 #include "consumer.h"
+#include "device_merge.h"
 #include "provider.h"
 #include "protocol.h"
 #include "uda_rt.h"
@@ -151,6 +152,7 @@ long long uda_rt_stat(uda_role_t h, const char* what) {
         if (w == "records_emitted") return (long long)r->consumer->records_emitted();
         if (w == "lpqs_spilled") return r->consumer->lpqs_spilled();
         if (w == "device_merges") return r->consumer->device_merges();
+        if (w == "device_fused_merges") return DeviceMerge::fused_merges();   // process-wide: merges that took the fused record merge
         if (w == "fetch_ms") return r->consumer->fetch_ms();
         if (w == "device_ms") return r->consumer->device_ms();
     }

@@ -50,7 +50,64 @@ struct DeviceMerge::Api {
     int (*write_eof_at)(void*, const unsigned long long*, void*);
     const char* (*error_string)(int);
     int (*host_alloc_pinned)(void**, long long);
+    // fused fixed-stride record merge (one read + one write per record)
+    int (*merge_records_supported)(int, long long, int, int);
+    long long (*merge_records_scratch_bytes)(long long, int);
+    int (*merge_records_fixed)(const void*, int, long long, long long, int, int, int, int, void*, int, void*, int, void*);
 };
+
+namespace {
+// the kernel library's run descriptor (include/uda_b200.h: UdaRunDesc)
+struct RunDesc {
+    const void* base;
+    long long nrec;
+    long long out_off;
+    unsigned run_id;
+    unsigned idx0;
+};
+static_assert(sizeof(RunDesc) == 32, "UdaRunDesc layout");
+
+// Do all records of all segments have the same serialized shape (same VInt headers, hence the same key and value lengths),
+// with a compared key part of at most 10 bytes? Then the fused record merge orders them exactly on its own (no entry
+// pipeline, no tie-break) and every record is `stride` bytes.
+struct FixedShape { int stride, key_off, key_len; };
+bool fixed_shape(const std::vector<HostSegment>& segs, KeyKind kind, FixedShape* out) {
+    const HostSegment* first = nullptr;
+    for (const auto& sg : segs) if (sg.records() > 0) { first = &sg; break; }
+    if (!first) return false;
+    const uint8_t* p = first->bytes.data();
+    const uint8_t* end = p + first->bytes.size();
+    int64_t kl = 0, vl = 0;
+    const int n1 = vint_decode(p, end, &kl);
+    const int n2 = n1 ? vint_decode(p + n1, end, &vl) : 0;
+    if (!n1 || !n2 || kl < 1 || vl < 0) return false;
+    const int hdr = n1 + n2;
+    const long long stride = hdr + kl + vl;
+    int skip = 0;
+    if (kind == KeyKind::TEXT) skip = vint_size_from_first((int8_t)p[hdr]);
+    else if (kind == KeyKind::BYTES_WRITABLE) skip = 4;
+    const long long key_len = kl - skip;
+    if (stride < 16 || stride > 128 || key_len < 1 || key_len > 10 || hdr > 8) return false;
+    uint8_t tmpl[9];
+    memcpy(tmpl, p, (size_t)hdr);
+    const uint8_t kfirst = p[hdr];    // Text: the key's own length prefix must be the same everywhere too
+    for (const auto& sg : segs) {
+        const long long n = sg.records();
+        if (n == 0) continue;
+        if (sg.rec_off[(size_t)n] != n * stride) return false;
+        const uint8_t* b = sg.bytes.data();
+        for (long long i = 0; i < n; ++i) {
+            const uint8_t* r = b + i * stride;
+            if (memcmp(r, tmpl, (size_t)hdr) != 0) return false;
+            if (kind == KeyKind::TEXT && r[hdr] != kfirst) return false;
+        }
+    }
+    out->stride = (int)stride;
+    out->key_off = hdr + skip;
+    out->key_len = (int)key_len;
+    return true;
+}
+}  // namespace
 
 namespace {
 std::string dir_of_this_library() {
@@ -63,6 +120,9 @@ std::string dir_of_this_library() {
     return ".";
 }
 }  // namespace
+
+static std::atomic<long long> g_fused_merges{0};
+long long DeviceMerge::fused_merges() { return g_fused_merges.load(); }
 
 DeviceMerge& DeviceMerge::instance() {
     static DeviceMerge d;
@@ -102,6 +162,9 @@ DeviceMerge::DeviceMerge() {
     UDA_SYM(write_eof_at, "uda_write_eof_at");
     UDA_SYM(error_string, "uda_error_string");
     UDA_SYM(host_alloc_pinned, "uda_host_alloc_pinned");
+    UDA_SYM(merge_records_supported, "uda_merge_records_supported");
+    UDA_SYM(merge_records_scratch_bytes, "uda_merge_records_scratch_bytes");
+    UDA_SYM(merge_records_fixed, "uda_merge_records_fixed");
 #undef UDA_SYM
     if (!all) return;
     int n = 0;
@@ -126,6 +189,146 @@ struct DeviceArena {
 };
 inline long long align_up(long long x, long long a) { return (x + a - 1) / a * a; }
 }  // namespace
+
+// The merged stream `d_out` (device) with record offsets `off[0..n]` (off[n] = position of the EOF marker) -> `deliver`.
+void DeviceMerge::stream_out(const uint8_t* d_out, const std::vector<unsigned long long>& off, size_t n, size_t max_block,
+                             const std::function<void(const uint8_t*, size_t)>& deliver) {
+    // The merged stream comes back window by window through two pinned staging buffers: the copy of window w+1 is
+    // in flight while window w is delivered in blocks of whole records; the EOF marker rides with the last block
+    // (or alone when it does not fit). A record larger than a window travels through a one-off pageable buffer.
+    const Api& a = *api_;
+    void* const stream = nullptr;
+    auto ck = [&](int rc, const char* what) { if (rc != 0) throw UdaError(std::string(what) + ": " + a.error_string(rc)); };
+    std::lock_guard<std::mutex> stage_lock(stage_mu_);
+    if (!stage_[0]) {
+        for (int b = 0; b < 2; ++b) {
+            void* p = nullptr;
+            if (a.host_alloc_pinned(&p, (long long)kStageBytes) != 0 || !p) throw UdaError("pinned staging buffer allocation failed");
+            stage_[b] = (uint8_t*)p;
+        }
+    }
+    struct Window { size_t r0, r1; };            // records [r0, r1)
+    auto next_window = [&](size_t r0) {
+        size_t r1 = r0 + 1;
+        // largest r1 with off[r1] - off[r0] (+2 for the EOF marker at the very end) <= kStageBytes, found by bisection
+        size_t lo = r0 + 1, hi = n;
+        while (lo < hi) {
+            size_t mid = lo + (hi - lo + 1) / 2;
+            if (off[mid] - off[r0] + (mid == n ? 2 : 0) <= kStageBytes) lo = mid; else hi = mid - 1;
+        }
+        r1 = std::max(r1, lo);
+        return Window{r0, r1};
+    };
+    std::vector<uint8_t> big[2];                 // only for a record that does not fit a staging buffer (one per slot)
+    auto start_copy = [&](const Window& w, int slot) -> uint8_t* {
+        const size_t bytes = (size_t)(off[w.r1] - off[w.r0]) + (w.r1 == n ? 2 : 0);
+        uint8_t* dst = stage_[slot];
+        if (bytes > kStageBytes) { big[slot].resize(bytes); dst = big[slot].data(); }
+        ck(a.d2h(dst, d_out + off[w.r0], (long long)bytes, stream), "copy of the merged stream to the host");
+        return dst;
+    };
+    Window cur = next_window(0);
+    uint8_t* cur_buf = start_copy(cur, 0);
+    int slot = 0;
+    while (true) {
+        ck(a.sync(stream), "stream synchronize");
+        const bool final_window = cur.r1 == n;
+        Window nxt{0, 0};
+        uint8_t* nxt_buf = nullptr;
+        if (!final_window) {
+            nxt = next_window(cur.r1);
+            nxt_buf = start_copy(nxt, slot ^ 1);
+        }
+        const unsigned long long base = off[cur.r0];
+        size_t i = cur.r0;
+        while (i < cur.r1) {
+            size_t j = i + 1;
+            while (j < cur.r1 && off[j + 1] - off[i] <= max_block) ++j;
+            size_t len = (size_t)(off[j] - off[i]);
+            const bool last = final_window && j == cur.r1;
+            if (last && len + 2 <= max_block) len += 2;
+            deliver(cur_buf + (off[i] - base), len);
+            if (last && len == (size_t)(off[j] - off[i])) deliver(cur_buf + (off[n] - base), 2);
+            i = j;
+        }
+        if (final_window) break;
+        cur = nxt;
+        cur_buf = nxt_buf;
+        slot ^= 1;
+    }
+}
+
+// Fixed-shape records: H2D of the segments, the fused record merge (uda_merge_records_fixed: every record is read once and
+// written once on the device), D2H window by window. Returns false with *why set when nothing has been delivered yet.
+bool DeviceMerge::merge_fixed(const std::vector<HostSegment>& segs, int stride, int key_off, int key_len, long long n, size_t max_block,
+                              const std::function<void(const uint8_t*, size_t)>& sink, std::string* why) {
+    const Api& a = *api_;
+    const int k = (int)segs.size();
+    bool delivered = false;
+    const std::function<void(const uint8_t*, size_t)> deliver = [&](const uint8_t* p, size_t len) { delivered = true; sink(p, len); };
+    try {
+        using Clk = std::chrono::steady_clock;
+        const auto t0 = Clk::now();
+        auto ms_since = [](Clk::time_point t) { return (long long)std::chrono::duration_cast<std::chrono::milliseconds>(Clk::now() - t).count(); };
+        std::vector<long long> seg_pos(k, 0);
+        long long data_bytes = 64, max_nrec = 0;
+        for (int r = 0; r < k; ++r) {
+            seg_pos[r] = data_bytes;
+            data_bytes = align_up(data_bytes + segs[r].records() * stride + 64, 16);
+            max_nrec = std::max(max_nrec, segs[r].records());
+        }
+        const long long out_bytes = n * stride + 2;
+        const long long scratch_bytes = a.merge_records_scratch_bytes(n, k);
+        if (scratch_bytes < 0) { *why = "scratch size query failed"; return false; }
+        const long long need = data_bytes + out_bytes + scratch_bytes + (long long)k * 32 + 4096;
+        long long free_b = 0, total_b = 0;
+        if (a.mem_info(&free_b, &total_b) != 0 || need > (long long)(0.9 * (double)free_b)) {
+            *why = "partition needs " + std::to_string(need >> 20) + " MiB of device memory, " + std::to_string(free_b >> 20) + " MiB free";
+            return false;
+        }
+        DeviceArena arena{this, a.dev_free, {}};
+        auto dmalloc = [&](long long bytes) -> uint8_t* {
+            void* p = nullptr;
+            int rc = a.dev_malloc(&p, std::max<long long>(bytes, 16));
+            if (rc != 0 || !p) throw UdaError(std::string("device allocation failed: ") + a.error_string(rc));
+            arena.ptrs.push_back(p);
+            return (uint8_t*)p;
+        };
+        auto ck = [&](int rc, const char* what) { if (rc != 0) throw UdaError(std::string(what) + ": " + a.error_string(rc)); };
+        void* const stream = nullptr;
+        uint8_t* d_data = dmalloc(data_bytes + 64);
+        uint8_t* d_out = dmalloc(out_bytes + 64);
+        uint8_t* d_scr = dmalloc(scratch_bytes);
+        uint8_t* d_runs = dmalloc((long long)k * 32);
+        std::vector<RunDesc> runs((size_t)k);
+        long long at = 0;
+        const bool even = (stride % 2) == 0 && (key_off % 2) == 0;
+        for (int r = 0; r < k; ++r) {
+            const long long nr = segs[r].records();
+            if (nr) ck(a.h2d(d_data + seg_pos[r], segs[r].bytes.data(), nr * stride, stream), "copy of a segment to the device");
+            runs[(size_t)r] = RunDesc{d_data + seg_pos[r], nr, at, (unsigned)r, 0u};
+            at += nr;
+        }
+        ck(a.h2d(d_runs, runs.data(), (long long)k * 32, stream), "run table upload");
+        const long long ms_h2d = ms_since(t0);
+        const auto t1 = Clk::now();
+        ck(a.merge_records_fixed(d_runs, k, n, max_nrec, stride, key_off, key_len, even ? 1 : 0, d_out, 1, d_scr, 0, stream), "uda_merge_records_fixed");
+        ck(a.sync(stream), "stream synchronize");
+        const long long ms_merge = ms_since(t1);
+        const auto t2 = Clk::now();
+        std::vector<unsigned long long> off((size_t)n + 1);
+        for (long long i = 0; i <= n; ++i) off[(size_t)i] = (unsigned long long)i * (unsigned long long)stride;
+        stream_out(d_out, off, (size_t)n, max_block, deliver);
+        ++g_fused_merges;
+        UDA_LOG(lsINFO, "device merge (fused fixed-stride path): H2D %lld ms, merge %lld ms, D2H + delivery %lld ms (%lld records of %d bytes, %d runs)",
+                ms_h2d, ms_merge, ms_since(t2), n, stride, k);
+    } catch (const UdaError& e) {
+        if (delivered) throw;
+        *why = e.info();
+        return false;
+    }
+    return true;
+}
 
 bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size_t max_block,
                         const std::function<void(const uint8_t*, size_t)>& sink, long long* records_out, std::string* why) {
@@ -153,6 +356,13 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
     }
     // limits of the kernel library: uda_kway_merge_entries takes at most 4096 runs, the entry format 2^31 - 2 records
     if (k > 4096 || n >= (1LL << 31) - 1) { if (why) *why = "partition too large for the device merge (runs > 4096 or records >= 2^31 - 1)"; return false; }
+    // ---- fast path: records of one fixed shape go through the fused record merge (the kernel of the TeraSort headline)
+    FixedShape fs{0, 0, 0};
+    if (fixed_shape(segs, kind, &fs) && a.merge_records_supported(k, n, fs.stride, fs.key_len)) {
+        std::string why_fixed;
+        if (merge_fixed(segs, fs.stride, fs.key_off, fs.key_len, n, max_block, sink, &why_fixed)) return true;
+        UDA_LOG(lsWARN, "fused record merge not used (%s): general device path", why_fixed.c_str());
+    }
     const long long nn = std::max<long long>(n, 1);
     const long long merge_scratch = a.merge_scratch_bytes(nn, k), tb_scratch = a.tiebreak_scratch_bytes(nn), scan_scratch = a.scan64_scratch_bytes(nn);
     if (merge_scratch < 0 || tb_scratch < 0 || scan_scratch < 0) { if (why) *why = "scratch size query failed"; return false; }
@@ -234,66 +444,7 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
     const long long ms_d2h = ms_since(t2);
     const auto t3 = Clk::now();
 
-    // The merged stream comes back window by window through two pinned staging buffers: the copy of window w+1 is
-    // in flight while window w is delivered in blocks of whole records; the EOF marker rides with the last block
-    // (or alone when it does not fit). A record larger than a window travels through a one-off pageable buffer.
-    std::lock_guard<std::mutex> stage_lock(stage_mu_);
-    if (!stage_[0]) {
-        for (int b = 0; b < 2; ++b) {
-            void* p = nullptr;
-            if (a.host_alloc_pinned(&p, (long long)kStageBytes) != 0 || !p) throw UdaError("pinned staging buffer allocation failed");
-            stage_[b] = (uint8_t*)p;
-        }
-    }
-    struct Window { size_t r0, r1; };            // records [r0, r1)
-    auto next_window = [&](size_t r0) {
-        size_t r1 = r0 + 1;
-        // largest r1 with off[r1] - off[r0] (+2 for the EOF marker at the very end) <= kStageBytes, found by bisection
-        size_t lo = r0 + 1, hi = (size_t)n;
-        while (lo < hi) {
-            size_t mid = lo + (hi - lo + 1) / 2;
-            if (off[mid] - off[r0] + (mid == (size_t)n ? 2 : 0) <= kStageBytes) lo = mid; else hi = mid - 1;
-        }
-        r1 = std::max(r1, lo);
-        return Window{r0, r1};
-    };
-    std::vector<uint8_t> big[2];                 // only for a record that does not fit a staging buffer (one per slot)
-    auto start_copy = [&](const Window& w, int slot) -> uint8_t* {
-        const size_t bytes = (size_t)(off[w.r1] - off[w.r0]) + (w.r1 == (size_t)n ? 2 : 0);
-        uint8_t* dst = stage_[slot];
-        if (bytes > kStageBytes) { big[slot].resize(bytes); dst = big[slot].data(); }
-        ck(a.d2h(dst, d_out + off[w.r0], (long long)bytes, stream), "copy of the merged stream to the host");
-        return dst;
-    };
-    Window cur = next_window(0);
-    uint8_t* cur_buf = start_copy(cur, 0);
-    int slot = 0;
-    while (true) {
-        ck(a.sync(stream), "stream synchronize");
-        const bool final_window = cur.r1 == (size_t)n;
-        Window nxt{0, 0};
-        uint8_t* nxt_buf = nullptr;
-        if (!final_window) {
-            nxt = next_window(cur.r1);
-            nxt_buf = start_copy(nxt, slot ^ 1);
-        }
-        const unsigned long long base = off[cur.r0];
-        size_t i = cur.r0;
-        while (i < cur.r1) {
-            size_t j = i + 1;
-            while (j < cur.r1 && off[j + 1] - off[i] <= max_block) ++j;
-            size_t len = (size_t)(off[j] - off[i]);
-            const bool last = final_window && j == cur.r1;
-            if (last && len + 2 <= max_block) len += 2;
-            deliver(cur_buf + (off[i] - base), len);
-            if (last && len == (size_t)(off[j] - off[i])) deliver(cur_buf + (off[n] - base), 2);
-            i = j;
-        }
-        if (final_window) break;
-        cur = nxt;
-        cur_buf = nxt_buf;
-        slot ^= 1;
-    }
+    stream_out(d_out, off, (size_t)n, max_block, deliver);
     UDA_LOG(lsINFO, "device merge phases: alloc %lld ms, H2D + kernels %lld ms, D2H %lld ms, delivery %lld ms (%lld records, %lld bytes, %d runs)",
             ms_alloc, ms_h2d_kernels, ms_d2h, ms_since(t3), n, out_bytes, k);
     } catch (const UdaError& e) {

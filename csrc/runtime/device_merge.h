@@ -4,7 +4,9 @@
 // :202-288 hybrid; selected with `-a` / mapred.netmerger.merge.approach). Approach 3 has no counterpart there: the
 // consumer fetches every map output of its partition into host memory (same fetch protocol, same buffers), hops
 // over the record headers once to build the record-offset tables, and hands the segments to the sm_100a kernels of
-// libuda_kernels.so: key normalise -> k-way merge of entries -> exact-comparator tie-break -> record gather. The
+// libuda_kernels.so. Records of one fixed shape with a compared key of at most 10 bytes (TeraSort, fixed-width keys) go
+// through the fused record merge — the kernel behind the headline benchmark, one read and one write per record; every
+// other shape takes key normalise -> k-way merge of entries -> exact-comparator tie-break -> record gather. The
 // merged stream comes back to the host and is delivered through dataFromUda in blocks of whole records, exactly
 // like the CPU merges deliver it.
 //
@@ -13,6 +15,7 @@
 // not fit the HBM budget, `available()` / `merge()` say so and the consumer falls back to its CPU heap merge over
 // the segments it already holds.
 #pragma once
+#include <atomic>
 #include <cstdint>
 #include <functional>
 #include <mutex>
@@ -41,6 +44,8 @@ public:
     // Creates the CUDA context now (call it from a helper thread while the fetches are still running)
     void warm_up();
     const std::string& why_not() const { return why_; }
+    // merges of this process that took the fused fixed-stride record merge
+    static long long fused_merges();
 
     // Merges the segments (each sorted by `kind`'s comparator) and calls `sink` with consecutive blocks of the merged
     // stream, every block <= max_block bytes and made of whole records (a single larger record travels alone); the
@@ -51,6 +56,10 @@ public:
 
 private:
     DeviceMerge();
+    bool merge_fixed(const std::vector<HostSegment>& segs, int stride, int key_off, int key_len, long long n, size_t max_block,
+                     const std::function<void(const uint8_t*, size_t)>& sink, std::string* why);
+    void stream_out(const uint8_t* d_out, const std::vector<unsigned long long>& off, size_t n, size_t max_block,
+                    const std::function<void(const uint8_t*, size_t)>& deliver);
     bool ok_ = false;
     std::string why_;
     void* lib_ = nullptr;

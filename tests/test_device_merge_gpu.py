@@ -33,6 +33,54 @@ def test_device_merge_matches_cpu_oracle(built, tmp_path, maps, reducers, recs, 
     assert all(len(b) <= (1 << 20) for c in consumers for b in c.blocks)
 
 
+def _text_mofs(tmpdir, n_maps, n_reduces, recs_per_part, seed, kl=10, compress=None, vl=None):
+    """Map outputs with serialized Text keys of one length: the first key byte is the key's own VInt length."""
+    import random
+
+    from uda_b200.utils import ifile
+    rng = random.Random(seed)
+    mofs, truth = {}, [[] for _ in range(n_reduces)]
+    for m in range(n_maps):
+        parts = []
+        for r in range(n_reduces):
+            n = rng.randint(1, recs_per_part)
+            recs = sorted(((bytes([kl - 1]) + bytes(rng.getrandbits(8) for _ in range(kl - 1)), bytes(rng.getrandbits(8) for _ in range(vl)))
+                           for _ in range(n)), key=lambda kv: kv[0])
+            parts.append(recs)
+            truth[r].append(recs)
+        data, index = ifile.write_mof(parts)
+        path = os.path.join(tmpdir, f"map_{m}.out")
+        with open(path, "wb") as f:
+            f.write(data)
+        mofs[f"attempt_m_{m:06d}_0"] = (path, ifile.read_index(index))
+    return mofs, truth
+
+
+@pytest.mark.parametrize("key_len,val_len,key_class", [(10, 90, "org.apache.hadoop.io.LongWritable"),    # TeraSort shape
+                                                       (8, 24, "org.apache.hadoop.io.LongWritable"),
+                                                       (11, 40, "org.apache.hadoop.io.Text")])             # 1-byte Text prefix + 10 compared bytes
+def test_device_merge_fixed_shape_takes_the_fused_record_merge(built, tmp_path, key_len, val_len, key_class):
+    """Records of one fixed shape reach the fused record merge (the kernel of the headline benchmark) through the plug-in
+    surface: provider -> fetch protocol -> consumer with merge approach 3 -> uda_merge_records_fixed -> dataFromUda."""
+    import test_runtime_cpu as T
+    from uda_b200.oracle.merge import kway_merge
+
+    real_make = T._make_mofs
+    if key_class.endswith("Text"):
+        T._make_mofs = _text_mofs
+    try:
+        streams, truth, consumers, _ = T._run_job(str(tmp_path), 5, 2, 3000, approach=3, key_class=key_class, key_len=key_len, seed=21,
+                                                  val_len=val_len)
+    finally:
+        T._make_mofs = real_make
+    for r, s in enumerate(streams):
+        want = list(kway_merge(truth[r]))
+        got = T.parse_stream(s)
+        assert [k for k, _ in got] == [k for k, _ in want] and sorted(got) == sorted(want)
+    assert all(c.final_stats["device_merges"] == 1 for c in consumers)
+    assert consumers[-1].final_stats["device_fused_merges"] >= len(consumers)
+
+
 def test_device_merge_snappy_segments(built, tmp_path):
     import ctypes as C
     import test_runtime_cpu as T

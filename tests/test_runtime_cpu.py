@@ -149,7 +149,7 @@ def test_snappy_builtin(L):
 
 
 # ------------------------------------------------------------------------------------------ plumbing end to end
-def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress=None):
+def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress=None, val_len=None):
     rng = random.Random(seed)
     mofs = {}
     truth = [[] for _ in range(n_reduces)]
@@ -157,7 +157,7 @@ def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress
         parts = []
         for r in range(n_reduces):
             n = rng.randint(0, recs_per_part)
-            recs = sorted(((bytes(rng.getrandbits(8) for _ in range(key_len)), bytes(rng.getrandbits(8) for _ in range(rng.randint(0, 200))))
+            recs = sorted(((bytes(rng.getrandbits(8) for _ in range(key_len)), bytes(rng.getrandbits(8) for _ in range(rng.randint(0, 200) if val_len is None else val_len)))
                            for _ in range(n)), key=lambda kv: kv[0])
             parts.append(recs)
             truth[r].append(recs)
@@ -183,8 +183,8 @@ def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress
 
 
 def _run_job(tmp, n_maps, n_reduces, recs, approach=1, buf_kb=8, key_class="org.apache.hadoop.io.LongWritable", key_len=10,
-             lpq_size=0, compress=None, codec="null", seed=1):
-    mofs, truth = _make_mofs(tmp, n_maps, n_reduces, recs, seed, key_len, compress)
+             lpq_size=0, compress=None, codec="null", seed=1, val_len=None):
+    mofs, truth = _make_mofs(tmp, n_maps, n_reduces, recs, seed, key_len, compress, val_len)
 
     def get_path(job, mapid, reduce):
         path, idx = mofs[mapid]
@@ -214,7 +214,7 @@ def _run_job(tmp, n_maps, n_reduces, recs, approach=1, buf_kb=8, key_class="org.
                     break
                 time.sleep(0.02)
             assert not cons.failed and cons.failures == 0, cons.last_error
-            cons.final_stats = {k: cons.stat(k) for k in ("records_emitted", "lpqs_spilled", "device_merges")}
+            cons.final_stats = {k: cons.stat(k) for k in ("records_emitted", "lpqs_spilled", "device_merges", "device_fused_merges")}
             streams.append(cons.stream())
             assert all(len(b) <= (1 << 20) for b in cons.blocks)
             assert cons.fetch_over >= 1
