@@ -257,10 +257,9 @@ def main():
     else:
         from uda_b200.models.terasort import TeraSortJob as Job
 
-    # measured on 8xB200 (profiles/pipeline_sweep.md): 12 sub-partitions pushed by the copy-engine kernel on 36 SMs
-    # of its own while the merge keeps the other 112 take the 8-GPU step from 33.6 ms (push, then merge) and 29.6 ms
-    # (4 sub-partitions, load/store push sharing all SMs with the merge) to 23.8 ms; on one GPU (no NVLink wait to
-    # hide) pipelining does not pay
+    # measured on 8xB200 (profiles/pipeline_sweep.md, profiles/r2/final): 12 sub-partitions pushed by the copy-engine kernel on
+    # SMs of its own (36; 48 on 8 GPUs: 21.1 - 22.0 ms against 22.0 - 22.2 ms) while the merge keeps the others; the local
+    # segments ride the copy engines
     if a.push_mode == "auto":
         a.push_mode = "tma" if world > 1 else "lsu"
     if a.subparts <= 0:
@@ -268,7 +267,7 @@ def main():
         # overlapping the merge (10.15 ms against 10.80 ms for copy-then-merge, profiles/r2)
         a.subparts = (12 if world > 2 else 8) if world > 1 else (1 if (a.graph or a.local_zero_copy or a.local_copy == "push") else 4)
     if a.push_ctas < 0:
-        a.push_ctas = ((36 if world > 2 else 32) if a.push_mode == "tma" else 296) if a.subparts > 1 else 0
+        a.push_ctas = (((48 if world >= 8 else 36) if world > 2 else 32) if a.push_mode == "tma" else 296) if a.subparts > 1 else 0
     if a.impl == "nccl_sort":
         job = Job(a.records_per_gpu, a.maps_per_gpu, device=dev).setup()
     else:
