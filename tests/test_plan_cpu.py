@@ -116,3 +116,65 @@ def test_plan_is_identical_on_every_rank():
     to1 = [x for x in d if int(x["dst"]) >> 32 == 1]
     lay1 = b.layout(1)
     assert sorted(int(x["dst"]) - (1 << 32) for x in to1) == sorted(int(lay1.run_offsets[a.run_id(2, m)]) for m in range(3))
+
+
+def _sub_index(world, maps, subparts, seed=0, stride=102):
+    rng = np.random.RandomState(seed)
+    idx = np.zeros((world, maps, world * subparts, 3), dtype=np.int64)
+    for s in range(world):
+        for m in range(maps):
+            cur = 0
+            for p in range(world * subparts):
+                body = int(rng.randint(0, 80)) * stride
+                idx[s, m, p] = (cur, body + 2, body + 6)
+                cur = (cur + body + 6 + 15) // 16 * 16
+    return idx
+
+
+def test_receive_ring_layout_reuses_slots_and_bounds_the_arena():
+    """`slots < subparts`: sub-partition j lives in slot j % slots; sub-partitions that share a slot overlap in memory (they
+    never coexist), sub-partitions in different slots never do, and the arena shrinks to about slots / subparts."""
+    world, maps, C, S = 3, 2, 8, 2
+    idx = _sub_index(world, maps, C, seed=5)
+    full = ShufflePlan(idx, record_stride=102, subparts=C)
+    ring = ShufflePlan(idx, record_stride=102, subparts=C, slots=S)
+    assert full.slots == C and ring.slots == S
+    assert ring.max_arena_bytes() < 0.5 * full.max_arena_bytes()
+    for r in range(world):
+        spans = []
+        for j in range(C):
+            lay = ring.layout(r, j)
+            lo = int(lay.run_offsets.min())
+            hi = int((lay.run_offsets + lay.run_bytes).max())
+            spans.append((lo, hi))
+            assert hi + 32 <= ring.arena_bytes[r]
+            # the same run sizes and record counts as in the full plan, phase preserved
+            assert (lay.run_bytes == full.layout(r, j).run_bytes).all() and (lay.run_nrec == full.layout(r, j).run_nrec).all()
+            for s in range(world):
+                for m in range(maps):
+                    assert lay.run_offsets[ring.run_id(s, m)] % 16 == idx[s, m, r * C + j, 0] % 16
+        for a in range(C):
+            for b in range(a + 1, C):
+                disjoint = spans[a][1] <= spans[b][0] or spans[b][1] <= spans[a][0]
+                if a % S != b % S:
+                    assert disjoint, (a, b, spans[a], spans[b])
+    # slots >= subparts or 0 means "whole partition"
+    assert ShufflePlan(idx, record_stride=102, subparts=C, slots=C + 3).slots == C
+    assert ShufflePlan(idx, record_stride=102, subparts=C, slots=0).max_arena_bytes() == full.max_arena_bytes()
+
+
+def test_receive_ring_descriptors_point_into_the_slots():
+    world, maps, C, S = 2, 3, 6, 2
+    idx = _sub_index(world, maps, C, seed=9)
+    ring = ShufflePlan(idx, record_stride=102, subparts=C, slots=S)
+    base = [1 << 40, 2 << 40]
+    flags = [3 << 40, 4 << 40]
+    for rank in range(world):
+        for j in range(C):
+            d = ring.push_descs(rank, [100_000 * (m + 1) for m in range(maps)], base, flags, j)
+            for i in range(len(d)):
+                p = (rank + 1 + i // maps) % world
+                off = int(d[i]["dst"]) - base[p]
+                assert 0 <= off and off + int(d[i]["bytes"]) <= ring.arena_bytes[p]
+                # landed-byte counters are per (sub-partition, run): never recycled with the slots
+                assert int(d[i]["flag"]) == flags[p] + 8 * (j * ring.nruns + ring.run_id(rank, i % maps))
