@@ -3,7 +3,7 @@
 # this file only gives the usual verbs.
 PY ?= python
 
-.PHONY: all native java test test-gpu bench sass sanitize asan tsan analyze wheel rpm clean
+.PHONY: all native java test test-gpu bench sass sanitize asan tsan analyze coverage wheel rpm deb install reference clean
 
 all: native
 
@@ -40,11 +40,26 @@ tsan:
 analyze:
 	scripts/ci/static_analysis.sh
 
+# line coverage of the host runtime by the CPU suite (gcc --coverage + gcov) -> build/coverage/summary.txt
+coverage:
+	scripts/ci/coverage.sh
+
+# the reference arm of bench.py: the reference's own reducer sources compiled unmodified (needs /root/reference or a copy)
+reference:
+	$(PY) baseline/build_ref.py
+
 wheel: native
 	$(PY) -m pip wheel --no-deps --no-build-isolation -w dist .
 
 rpm:
 	packaging/buildrpm.sh
+
+deb: native
+	$(PY) packaging/build_deb.py
+
+# unpacked-tree install + Hadoop hook: make install UDA_DIR=/opt/uda [HADOOP_CONF=/etc/hadoop/conf]
+install: native
+	packaging/install-uda.sh --uda-dir=$(UDA_DIR) $(if $(HADOOP_CONF),--uda-hadoop-conf-dir=$(HADOOP_CONF))
 
 clean:
 	rm -rf build dist uda_b200/lib/*.so *.egg-info
