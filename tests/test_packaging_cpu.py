@@ -65,3 +65,19 @@ def test_installer_writes_env_and_hooks_hadoop_once(tmp_path):
     assert out.strip() == f"x:{uda_dir}/uda.jar"
     p = subprocess.run(["bash", str(ROOT / "packaging" / "install-uda.sh")], capture_output=True, text=True)
     assert p.returncode != 0 and "Missing param" in p.stderr
+
+
+def test_scheduler_case_wrapper_maps_cases_to_the_regression_driver():
+    """cases/: the wrapper turns a case's arguments into the regression driver's command line (reference: cases/uda_wrapper.py)."""
+    import importlib.util
+    import xml.etree.ElementTree as ET
+
+    spec = importlib.util.spec_from_file_location("uda_b200_wrapper", ROOT / "cases" / "uda_b200_wrapper.py")
+    w = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(w)
+    cmd = w.get_command("cpu", "/tmp/x")
+    assert cmd[1].endswith("scripts/regression/auto_tester.py") and "--matrix" in cmd and cmd[cmd.index("--matrix") + 1].endswith("matrix_cpu.csv")
+    assert "--matrix" not in w.get_command("all", "/tmp/x")
+    tree = ET.parse(ROOT / "cases" / "uda_b200.cases")
+    assert tree.getroot().tag == "CASEDEF" and len(tree.getroot().findall("case")) == 2
+    assert tree.getroot().find("global/Case/wrapper").text == "./uda_b200_wrapper.py"
