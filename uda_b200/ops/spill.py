@@ -32,6 +32,18 @@ class SpillMerger:
         self.budget, self.device, self.max_group_runs = hbm_budget_bytes, device, max_group_runs
         self.s_in, self.s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
         self.stats = {}
+        #: pinned spill buffers, kept across merges: pinning host memory costs ~0.1 s per GB, far more than the copy it
+        #: serves, so the buffers of the first merge are reused by the following ones (the reference's LPQ files are
+        #: likewise created once per reduce task, src/Merger/MergeManager.cc:202-288)
+        self._pinned: List[torch.Tensor] = []
+
+    def _spill_buffer(self, i: int, nbytes: int) -> torch.Tensor:
+        """Pinned host buffer number ``i`` of this merger with room for ``nbytes`` (grown when a later merge needs more)."""
+        while len(self._pinned) <= i:
+            self._pinned.append(torch.empty(0, dtype=torch.uint8))
+        if self._pinned[i].numel() < nbytes:
+            self._pinned[i] = torch.empty(nbytes + nbytes // 16, dtype=torch.uint8, pin_memory=True)
+        return self._pinned[i][:nbytes]
 
     # ------------------------------------------------------------------------------------------------
     def _plan_groups(self, nrecs: Sequence[int]) -> List[List[int]]:
@@ -117,7 +129,7 @@ class SpillMerger:
                 nranges = max(2, -(-total * S // max(S, int(cap * 0.6))))
                 splitters = K.sample_splitters(d_out[oslot], n, S, self.key_off, self.key_len, nranges - 1)
             cuts.append(K.lower_bound_records(d_out[oslot], n, S, self.key_off, self.key_len, splitters))
-            h = torch.empty(n * S, dtype=torch.uint8, pin_memory=True)
+            h = self._spill_buffer(gi, n * S)
             with torch.cuda.stream(self.s_out):
                 self.s_out.wait_event(ev_merged[slot])
                 h.copy_(d_out[oslot][: n * S], non_blocking=True)   # the spill: pinned DRAM instead of uda.<task>.lpq-NNN
