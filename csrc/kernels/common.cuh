@@ -3,6 +3,9 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <map>
+#include <mutex>
+#include <utility>
 
 #define UDA_CHECK_LAUNCH()                                  \
     do {                                                    \
@@ -19,6 +22,22 @@
 namespace uda {
 
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+
+// Opt a kernel in to `smem` bytes of dynamic shared memory. The limit is an attribute of (function, device), and a
+// launch fails when it is below the launch's request, so it only ever grows here: two host threads launching different
+// shapes of one kernel on one device cannot lower each other's limit between the set and the launch. Set on every call
+// (a few hundred ns) so that a device whose context was reset is opted in again.
+inline cudaError_t ensure_dynamic_smem(const void* kernel, size_t smem) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, size_t> high;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(mu);
+    size_t& h = high[std::make_pair(kernel, dev)];
+    if (smem > h) h = smem;
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h);
+}
 
 // ---------------------------------------------------------------------------------------------
 // Sort entry: 16 bytes, compared as the 128-bit big integer (w0:w1).

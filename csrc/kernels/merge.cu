@@ -440,11 +440,7 @@ static int merge_back(const uda::Entry* E, const long long* run_off_dev, int nru
     }
     {
         size_t smem = (size_t)2 * MG_TILE * sizeof(Entry) + ((size_t)5 * nruns + 2) * sizeof(uint32_t);
-        static size_t configured = 0;
-        if (smem > configured) {
-            UDA_CUDA(cudaFuncSetAttribute(merge_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = smem;
-        }
+        UDA_CUDA(ensure_dynamic_smem((const void*)merge_tiles_kernel, smem));
         int per_sm = 0;
         UDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, merge_tiles_kernel, MG_THREADS, smem));
         if (per_sm < 1) return UDA_E_TOO_LARGE;

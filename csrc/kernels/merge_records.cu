@@ -968,9 +968,7 @@ extern "C" int uda_merge_records_fixed(const UdaRunDesc* runs_dev, int nruns, lo
             else if (align2 && stride == 100) kern = fr_merge_kernel<true, 100>;
             else if (align2) kern = fr_merge_kernel<true, 0>;
             else kern = fr_merge_kernel<false, 0>;
-            // the opt-in is a per-device attribute of the function: set it on every call (a few hundred ns) rather than
-            // remembering it per process, which breaks the second device of a multi-GPU process
-            UDA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            UDA_CUDA(ensure_dynamic_smem((const void*)kern, smem));
             int per_sm = 0;
             UDA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FR_THREADS_ALL, smem));
             if (per_sm < 1) return UDA_E_TOO_LARGE;

@@ -211,11 +211,7 @@ extern "C" int uda_partition_scatter(const void* recs, long long n, int stride, 
         partition_scatter_kernel<16><<<(int)b, PS_THREADS, smem, stream>>>((const uint8_t*)recs, n, stride, key_off, key_len, key_skip,
                                                                             mode, P, splitters_dev, dst_dev, cursor_dev);
     } else {
-        static size_t configured = 0;
-        if (smem > configured) {
-            UDA_CUDA(cudaFuncSetAttribute(partition_scatter_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = smem;
-        }
+        UDA_CUDA(ensure_dynamic_smem((const void*)partition_scatter_kernel<0>, smem));
         partition_scatter_kernel<0><<<(int)b, PS_THREADS, smem, stream>>>((const uint8_t*)recs, n, stride, key_off, key_len, key_skip,
                                                                            mode, P, splitters_dev, dst_dev, cursor_dev);
     }

@@ -14,17 +14,14 @@
 //                           out[i] = out[start - offset + i % offset], which needs no byte-serial loop.
 // Blocks are independent, so a segment of N blocks keeps N warps busy; the element chain inside a block is serial
 // by the format's definition.
+#include "block_table.cuh"
 #include "common.cuh"
 #include "../../include/uda_b200.h"
 
 namespace uda {
 namespace {
 
-struct SnBlock {
-    unsigned long long src_off;  // offset of the compressed bytes inside the segment
-    unsigned long long dst_off;  // offset of the plain bytes in the output
-    unsigned comp, raw;
-};
+using SnBlock = CodecBlock;   // block_table.cuh: {src offset, dst offset, compLen, rawLen}
 
 __device__ __forceinline__ unsigned be32(const uint8_t* p) {
     return ((unsigned)p[0] << 24) | ((unsigned)p[1] << 16) | ((unsigned)p[2] << 8) | (unsigned)p[3];

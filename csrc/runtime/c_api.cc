@@ -286,6 +286,10 @@ long long uda_rt_lzo1x_compress(const unsigned char* in, long long n, unsigned c
 int uda_rt_lzo1x_decompress(const unsigned char* in, long long n, unsigned char* out, long long out_len) {
     return lzo1x_decompress_builtin(in, (size_t)n, out, (size_t)out_len) ? 0 : -1;
 }
+// test hook: the device kernel's cooperative copy, run lane by lane on the host
+int uda_rt_lzo1x_decompress_lanes(const unsigned char* in, long long n, unsigned char* out, long long out_len, int lanes) {
+    return lanes > 0 && lzo1x_decompress_lanes(in, (size_t)n, out, (size_t)out_len, (unsigned)lanes) ? 0 : -1;
+}
 
 // out4 = {buffer_size, pairs, pair0, pair1}; returns 0, or 1/2 for the two sizing failures
 int uda_rt_plan_memory(int num_maps, long long max_buf, long long min_buf, long long shuffle_mem, int compressed, double ratio,

@@ -86,6 +86,7 @@ size_t snappy_compress(const uint8_t* in, size_t n, std::vector<uint8_t>* out); 
 size_t snappy_compress_literal(const uint8_t* in, size_t n, std::vector<uint8_t>* out);  // test helper: valid, uncompressed stream
 // LZO1X (lzo1x.cc): built-in block decoder used when liblzo2 cannot be loaded, and a greedy compressor for tests / tools
 bool lzo1x_decompress_builtin(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len);
+bool lzo1x_decompress_lanes(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len, unsigned lanes);
 size_t lzo1x_compress(const uint8_t* in, size_t n, std::vector<uint8_t>* out);
 
 // One map output partition being fetched chunk by chunk into a borrowed buffer pair.

@@ -17,91 +17,28 @@
 //   001L LLLL    match of 2 + L bytes (L == 0 -> 31 + extension), distance = D + 1, same 16-bit word
 //   01LD DDSS    match of 3 + L bytes, distance = (H << 3) + D + 1, followed by H
 //   1LLD DDSS    match of 5 + L bytes, distance = (H << 3) + D + 1, followed by H
+// The decoder itself lives in lzo1x_parse.h, shared with the device kernel (csrc/kernels/lzo.cu).
 #include <string.h>
 
 #include <cstdint>
 #include <vector>
 
 #include "consumer.h"
+#include "lzo1x_parse.h"
 
 namespace uda {
 
 bool lzo1x_decompress_builtin(const uint8_t* in, size_t n, uint8_t* out, size_t out_len) {
-    size_t ip = 0, op = 0;
-    unsigned state = 0;
-    auto need_in = [&](size_t k) { return ip + k <= n; };
-    auto copy_literals = [&](size_t len) -> bool {
-        if (!need_in(len) || op + len > out_len) return false;
-        memcpy(out + op, in + ip, len);
-        ip += len;
-        op += len;
-        return true;
-    };
-    auto copy_match = [&](size_t dist, size_t len) -> bool {
-        if (dist == 0 || dist > op || op + len > out_len) return false;
-        for (size_t i = 0; i < len; ++i) out[op + i] = out[op + i - dist];  // may overlap: byte-serial by definition
-        op += len;
-        return true;
-    };
-    // zero-byte run-length extension of a length field
-    auto extended = [&](size_t base, size_t* len) -> bool {
-        size_t t = 0;
-        while (need_in(1) && in[ip] == 0) { t += 255; ++ip; if (t > (1u << 30)) return false; }
-        if (!need_in(1)) return false;
-        *len = base + t + in[ip++];
-        return true;
-    };
-    if (!need_in(1)) return false;
-    if (in[0] > 17) {
-        const size_t t = in[ip++] - 17;
-        if (!copy_literals(t)) return false;
-        state = t < 4 ? (unsigned)t : 4u;
-    }
-    for (;;) {
-        if (!need_in(1)) return false;
-        const unsigned t = in[ip++];
-        size_t len, dist;
-        unsigned next_state;
-        if (t < 16) {
-            if (state == 0) {
-                if (t == 0) { if (!extended(15, &len)) return false; } else len = t;
-                if (!copy_literals(len + 3)) return false;
-                state = 4;
-                continue;
-            }
-            if (!need_in(1)) return false;
-            const unsigned h = in[ip++];
-            dist = ((size_t)h << 2) + (t >> 2) + (state == 4 ? 2049 : 1);
-            len = state == 4 ? 3 : 2;
-            next_state = t & 3;
-        } else if (t < 32) {
-            if ((t & 7) == 0) { if (!extended(7, &len)) return false; } else len = t & 7;
-            len += 2;
-            if (!need_in(2)) return false;
-            const unsigned w = in[ip] | ((unsigned)in[ip + 1] << 8);
-            ip += 2;
-            dist = 16384 + ((size_t)(t & 8) << 11) + (w >> 2);
-            next_state = w & 3;
-            if (dist == 16384) return op == out_len && ip == n;   // end-of-stream marker
-        } else if (t < 64) {
-            if ((t & 31) == 0) { if (!extended(31, &len)) return false; } else len = t & 31;
-            len += 2;
-            if (!need_in(2)) return false;
-            const unsigned w = in[ip] | ((unsigned)in[ip + 1] << 8);
-            ip += 2;
-            dist = (w >> 2) + 1;
-            next_state = w & 3;
-        } else {
-            if (!need_in(1)) return false;
-            const unsigned h = in[ip++];
-            dist = ((size_t)h << 3) + ((t >> 2) & 7) + 1;
-            len = t < 128 ? 3 + ((t >> 5) & 1) : 5 + ((t >> 5) & 3);
-            next_state = t & 3;
-        }
-        if (!copy_match(dist, len)) return false;
-        if (next_state && !copy_literals(next_state)) return false;
-        state = next_state;
-    }
+    Lzo1xHostCopier copier;
+    return lzo1x_decode_block(in, n, out, out_len, copier);
+}
+
+// The same parser with the device kernel's cooperative copy run lane by lane on the host (tests: the warp copier's
+// logic is checked against the byte-serial one without a GPU).
+bool lzo1x_decompress_lanes(const uint8_t* in, size_t n, uint8_t* out, size_t out_len, unsigned lanes) {
+    if (lanes < 1) return false;
+    Lzo1xLaneEmulation copier{lanes};
+    return lzo1x_decode_block(in, n, out, out_len, copier);
 }
 
 // ---- compressor (greedy, hash of 4 bytes; matches are emitted in the 001L LLLL form, distance <= 16384) -------------

@@ -208,6 +208,10 @@ int uda_snappy_scan_blocks(const void* seg, long long seg_len, int max_blocks, v
 /* one warp per block; `out` holds the total plain bytes; status_dev becomes 3 when a block is corrupt */
 int uda_snappy_decode_blocks(const void* seg, const void* table, const unsigned long long* nblocks_dev, int max_blocks, void* out,
                              unsigned* status_dev, cudaStream_t stream);
+/* LZO1X blocks (reference: src/Merger/LzoDecompressor.cc:121-167) in the same framing: the table comes from
+ * uda_snappy_scan_blocks (the framing is codec independent); one warp per block, status_dev becomes 3 on a corrupt block */
+int uda_lzo_decode_blocks(const void* seg, const void* table, const unsigned long long* nblocks_dev, int max_blocks, void* out,
+                          unsigned* status_dev, cudaStream_t stream);
 
 /* ---- symmetric receive arena plumbing (reference: registered MR + rkey exchange,
  *      src/DataNet/RDMAComm.cc:67-154,178-218, src/DataNet/RDMAComm.h:35-39). These allocate. ---- */

@@ -58,6 +58,8 @@ long long uda_rt_snappy_compress(const unsigned char* in, long long n, unsigned 
 /* built-in LZO1X block codec: greedy compressor (cap >= n + n/16 + 64 + 3 is always enough) and decoder (0 = ok) */
 long long uda_rt_lzo1x_compress(const unsigned char* in, long long n, unsigned char* out, long long cap);
 int uda_rt_lzo1x_decompress(const unsigned char* in, long long n, unsigned char* out, long long out_len);
+/* same decoder with the device kernel's warp-cooperative copy emulated lane by lane on the host (tests) */
+int uda_rt_lzo1x_decompress_lanes(const unsigned char* in, long long n, unsigned char* out, long long out_len, int lanes);
 int uda_rt_plan_memory(int num_maps, long long max_buf, long long min_buf, long long shuffle_mem, int compressed,
                        double ratio, long long* out4);
 int uda_rt_selftest_queues(void);

@@ -44,7 +44,12 @@ def test_snappy_decoder_never_crashes(L, data, out_len):
 def test_lzo_decoder_never_crashes(L, data, out_len):
     buf, n = _exact(data)
     out = (C.c_ubyte * max(out_len, 1))()
-    assert L.uda_rt_lzo1x_decompress(buf, C.c_longlong(n), out, C.c_longlong(out_len)) in (0, -1)
+    rc = L.uda_rt_lzo1x_decompress(buf, C.c_longlong(n), out, C.c_longlong(out_len))
+    assert rc in (0, -1)
+    # the device kernel's copy discipline (lane-strided, self-overlapping matches as a repeating pattern) agrees
+    out2 = (C.c_ubyte * max(out_len, 1))()
+    assert L.uda_rt_lzo1x_decompress_lanes(buf, C.c_longlong(n), out2, C.c_longlong(out_len), 32) == rc
+    assert rc != 0 or bytes(out2)[:out_len] == bytes(out)[:out_len]
 
 
 @FUZZ

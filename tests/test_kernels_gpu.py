@@ -1,5 +1,6 @@
 """GPU numerics tests: every kernel against a plain NumPy / Python restatement of the same op."""
 import random
+import struct
 import zlib
 
 import numpy as np
@@ -718,6 +719,63 @@ def test_snappy_decode_detects_corruption(built):
     dec2.decode(seg, len(comp), raw_len=len(plain))
     with pytest.raises(UdaFailure):
         dec2.check()
+
+
+@pytest.mark.parametrize("kind,n,block", [("random", 200_000, 65536), ("text", 1_000_000, 262144), ("runs", 500_000, 4096),
+                                          ("states", 300_000, 16384), ("tiny", 5, 65536), ("empty", 0, 65536)])
+def test_lzo_decode_blocks(built, kind, n, block):
+    """LZO1X blocks decoded by one warp each == the plain bytes (the parser is the host runtime's, tests/test_runtime_cpu.py
+    covers it instruction form by instruction form; here the warp-cooperative copies and the block table are under test)."""
+    from uda_b200.ops.compress import LzoDecoder, decoder_for, frame_compress_segment
+    rng = random.Random(n + 1)
+    if kind == "random":
+        plain = bytes(rng.randrange(256) for _ in range(n))
+    elif kind == "text":
+        words = [bytes(rng.choice(b"etaoinshr") for _ in range(rng.randint(1, 9))) for _ in range(200)]
+        plain = b" ".join(rng.choice(words) for _ in range(n // 5))[:n]
+    elif kind == "runs":
+        plain = b"".join(bytes([rng.randrange(256)]) * rng.randint(1, 300) for _ in range(n // 100))[:n]   # self-overlapping matches
+    elif kind == "states":   # 0..5 literals between matches: every trailing-literal state and the short-match forms
+        plain = b"".join(b"0123456789ABCDEF" + bytes(rng.randrange(256) for _ in range(rng.randint(0, 5))) for _ in range(n // 16 + 1))[:n]
+    else:
+        plain = b"abcde"[:n]
+    comp = frame_compress_segment(plain, block, codec="lzo")
+    if kind in ("text", "runs", "states"):
+        assert len(comp) < 0.8 * len(plain)       # the test really contains matches
+    dev = _dev()
+    seg = torch.from_numpy(np.frombuffer(comp + b"\0" * 16, dtype=np.uint8).copy()).to(dev)
+    dec = decoder_for("com.hadoop.compression.lzo.LzoCodec", dev, max(1, -(-len(plain) // block)))
+    assert isinstance(dec, LzoDecoder)
+    out, raw = dec.decode(seg, len(comp))
+    dec.check(expect_raw=len(plain))
+    assert raw == len(plain) and bytes(out.cpu().numpy()) == plain
+    out2, _ = dec.decode(seg, len(comp), raw_len=len(plain))    # sync-free form
+    assert bytes(out2.cpu().numpy()) == plain
+
+
+def test_lzo_decode_detects_corruption(built):
+    from uda_b200.ops.compress import LzoDecoder, frame_compress_segment
+    from uda_b200.runtime.failure import UdaFailure
+    plain = b"the quick brown fox jumps over the lazy dog " * 2000
+    good = frame_compress_segment(plain, 16384, codec="lzo")
+    dev = _dev()
+    dec = LzoDecoder(dev, 16)
+    for damage in ("end-marker", "distance"):
+        comp = bytearray(good)
+        first = struct.unpack(">I", good[4:8])[0]          # compLen of block 0
+        if damage == "end-marker":
+            comp[8 + first - 3] = 0x19                     # 0001 1001: a match 32768 bytes back where the end marker was
+        else:
+            comp[8] = 17 + 4                               # first byte: 4 literals, then whatever follows is misparsed
+            comp[9:13] = b"\x00\x00\x00\x00"
+        seg = torch.from_numpy(np.frombuffer(bytes(comp) + b"\0" * 16, dtype=np.uint8).copy()).to(dev)
+        dec.decode(seg, len(comp), raw_len=len(plain))
+        with pytest.raises(UdaFailure):
+            dec.check()
+    seg = torch.from_numpy(np.frombuffer(good + b"\0" * 16, dtype=np.uint8).copy()).to(dev)
+    out, _ = dec.decode(seg, len(good), raw_len=len(plain))     # the decoder recovers: status was cleared by check()
+    dec.check(expect_raw=len(plain))
+    assert bytes(out.cpu().numpy()) == plain
 
 
 def test_compressed_segments_through_var_merger(built):

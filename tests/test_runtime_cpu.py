@@ -366,6 +366,11 @@ def test_plumbing_device_merge_falls_back_without_a_gpu(built, tmp_path):
 def _lzo_dec(L, stream, n):
     out = _buf(max(n, 1))
     rc = L.uda_rt_lzo1x_decompress(stream, len(stream), out, n)
+    # the device kernel's cooperative copy (csrc/kernels/lzo.cu), emulated lane by lane: same verdict, same bytes
+    for lanes in (32, 3):
+        out2 = _buf(max(n, 1))
+        rc2 = L.uda_rt_lzo1x_decompress_lanes(stream, C.c_longlong(len(stream)), out2, C.c_longlong(n), lanes)
+        assert rc2 == rc and (rc != 0 or out2.raw[:n] == out.raw[:n]), (lanes, rc, rc2)
     return rc, out.raw[:n]
 
 

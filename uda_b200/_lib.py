@@ -63,6 +63,7 @@ _PROTOS = {
     "uda_snappy_table_bytes": (c_ll, [c_int]),
     "uda_snappy_scan_blocks": (c_int, [c_vp, c_ll, c_int, c_vp, c_vp, c_vp, c_vp]),
     "uda_snappy_decode_blocks": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]),
+    "uda_lzo_decode_blocks": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]),
     "uda_push_scratch_bytes": (c_ll, [c_int]),
     "uda_shuffle_push": (c_int, [c_vp, c_int, c_vp, c_int, c_vp]),
     "uda_shuffle_push_nway": (c_int, [c_vp, c_int, c_vp, c_int, c_int, c_vp]),
