@@ -479,6 +479,54 @@ def test_spill_merger(K, sizes, budget):
         assert sm.stats["groups"] > 1 and sm.stats["ranges"] > 1 and sm.stats["spilled_bytes"] == total * 102
 
 
+def test_spill_merger_skewed_keys(K):
+    """70 % of the records carry one of two keys: the sampled key ranges cannot be equi-depth, the oversize range is cut
+    further on the host (tests/test_spill_cpu.py) down to pieces of a single key, which are cut by position."""
+    from uda_b200.ops.spill import SpillMerger
+
+    dev = _dev()
+    sizes = [20_000] * 12
+    rng = np.random.RandomState(7)
+    heavy = rng.randint(0, 256, size=(2, 10), dtype=np.uint8)
+    host_runs, truth = [], []
+    row = 0
+    for n in sizes:
+        framed = tg.teragen_framed(n, 31, first_row=row).copy()
+        row += n
+        pick = rng.rand(n) < 0.7
+        framed[pick, 2:12] = heavy[rng.randint(0, 2, size=int(pick.sum()))]
+        w0, w1 = _entries_np(framed)
+        framed = framed[_sort_order(w0, w1)]
+        truth.append(framed)
+        h = torch.empty(n * 102, dtype=torch.uint8, pin_memory=True)
+        h[:] = torch.from_numpy(framed.reshape(-1))
+        host_runs.append(h)
+    total = sum(sizes)
+    out = torch.zeros(total * 102 + 2 + 64, dtype=torch.uint8, device=dev)
+    pos = [0]
+
+    def sink(block, nbytes):
+        out[pos[0]:pos[0] + nbytes].copy_(block[:nbytes])
+        pos[0] += nbytes
+
+    sm = SpillMerger(102, 2, 10, 24 << 20, dev)
+    assert sm.merge(host_runs, sizes, sink) == total
+    torch.cuda.synchronize()
+    assert pos[0] == total * 102 + 2
+    assert sm.stats["groups"] > 1 and sm.stats["refined_ranges"] >= 1, sm.stats
+    allrec = np.concatenate(truth)
+    w0 = np.concatenate([_entries_np(h, run=r)[0] for r, h in enumerate(truth)])
+    w1 = np.concatenate([_entries_np(h, run=r)[1] for r, h in enumerate(truth)])
+    want = allrec[_sort_order(w0, w1)]
+    host = out.cpu().numpy()
+    got = host[: total * 102].reshape(total, 102)
+    assert (got[:, 2:12] == want[:, 2:12]).all()                       # key order; equal keys may interleave differently
+    assert int(got.astype(np.int64).sum()) == int(want.astype(np.int64).sum())
+    rows = lambda a: np.sort(np.ascontiguousarray(a).view(np.dtype((np.void, 102))).ravel())
+    assert (rows(got) == rows(want)).all()                             # the same multiset of records
+    assert bytes(host[total * 102: total * 102 + 2]) == b"\xff\xff"
+
+
 # ------------------------------------------------------------------------------------------- general (var-length) path
 @pytest.mark.parametrize("m,hi", [(0, 10), (1, 10), (4097, 1000), (3_000_000, 1 << 31)])
 def test_scan_u32_to_u64(K, m, hi):

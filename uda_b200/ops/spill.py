@@ -12,16 +12,88 @@ i-1 overlap.
 
 Final-merge ranges: equi-depth splitters are sampled from the first merged group
 (``uda_sample_splitters``); every merged group is cut at those keys (``uda_lower_bound_records``) while it is
-still on the device, so the final phase needs no search in host memory.
+still on the device, so the final phase needs no search in host memory unless the keys are skewed: a range that the
+sampled splitters left larger than the staging buffer is halved at median keys on the host (``split_range``; binary
+searches in the pinned spill buffers), down to pieces of a single key value, which are cut by position.
 """
 from __future__ import annotations
 
-from typing import Callable, List, Optional, Sequence
+from typing import Callable, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
 
 from . import kernels as K
+
+
+Slice = Tuple[int, int, int]   # (spilled group, first record, one past the last record)
+
+
+def _key_at(buf: np.ndarray, i: int, S: int, key_off: int, key_len: int) -> bytes:
+    o = i * S + key_off
+    return buf[o:o + key_len].tobytes()
+
+
+def _bisect(buf: np.ndarray, lo: int, hi: int, S: int, key_off: int, key_len: int, key: bytes, upper: bool) -> int:
+    """First record in [lo, hi) whose key is >= ``key`` (``upper``: > ``key``); keys compare as unsigned bytes."""
+    while lo < hi:
+        mid = (lo + hi) // 2
+        k = _key_at(buf, mid, S, key_off, key_len)
+        if k < key or (upper and k == key):
+            lo = mid + 1
+        else:
+            hi = mid
+    return lo
+
+
+def split_range(spilled: Sequence[np.ndarray], slices: Sequence[Slice], S: int, key_off: int, key_len: int, cap_records: int) -> List[List[Slice]]:
+    """Cuts one final-merge key range that is larger than the staging buffer into consecutive sub-ranges of at most
+    ``cap_records`` records each (skewed keys: the sampled splitters are equi-depth only for the group they were sampled
+    from). ``slices`` names the range's sorted piece in every spilled group; the groups live in host memory, so the
+    search runs on the host: the range is halved at the median key of its largest piece until every part fits. Records
+    that share one key cannot be separated by a key, and need not be: any order among them is a valid merge order
+    (src/Merger/MergeQueue.h:250-269 breaks ties arbitrarily as well), so such a part is cut by position, group by
+    group. Returns the sub-ranges in key order; merging each of them and concatenating the results is the merged range."""
+    assert cap_records >= 1
+    slices = [(g, a, b) for g, a, b in slices if b > a]
+    total = sum(b - a for _, a, b in slices)
+    if total <= cap_records:
+        return [slices] if slices else []
+    kmin = min(_key_at(spilled[g], a, S, key_off, key_len) for g, a, _ in slices)
+    kmax = max(_key_at(spilled[g], b - 1, S, key_off, key_len) for g, _, b in slices)
+    if kmin == kmax:
+        # one key value: pack whole pieces greedily, cut a piece that alone is too large by position
+        tasks, cur, room = [], [], cap_records
+        for g, a, b in slices:
+            while a < b:
+                take = min(b - a, room)
+                cur.append((g, a, a + take))
+                a += take
+                room -= take
+                if room == 0:
+                    tasks.append(cur)
+                    cur, room = [], cap_records
+        if cur:
+            tasks.append(cur)
+        return tasks
+    g, a, b = max(slices, key=lambda t: t[2] - t[1])
+    pivot = _key_at(spilled[g], (a + b) // 2, S, key_off, key_len)
+    if pivot == kmin:
+        # everything below the median of the largest piece is the minimum key: peel that key off (left part = one key
+        # value, handled above), continue with the rest. kmax > kmin guarantees a next key exists.
+        nxt = []
+        for g2, a2, b2 in slices:
+            u = _bisect(spilled[g2], a2, b2, S, key_off, key_len, kmin, upper=True)
+            if u < b2:
+                nxt.append(_key_at(spilled[g2], u, S, key_off, key_len))
+        pivot = min(nxt)
+    left, right = [], []
+    for g2, a2, b2 in slices:
+        m = _bisect(spilled[g2], a2, b2, S, key_off, key_len, pivot, upper=False)
+        left.append((g2, a2, m))
+        right.append((g2, m, b2))
+    return (split_range(spilled, left, S, key_off, key_len, cap_records)
+            + split_range(spilled, right, S, key_off, key_len, cap_records))
 
 
 class SpillMerger:
@@ -143,20 +215,28 @@ class SpillMerger:
         gn = [h.numel() // S for h in spilled]
         cut = np.stack([np.concatenate([[0], c.cpu().numpy(), [gn[i]]]) for i, c in enumerate(cuts)])  # [G, nranges+1]
         nranges = cut.shape[1] - 1
-        sizes = (cut[:, 1:] - cut[:, :-1]).sum(0)
-        if int(sizes.max()) * S > cap + 64 * G:
-            # skewed ranges: fall back to more, finer ranges would be the production answer; refuse rather than overflow
-            raise RuntimeError("a final-merge key range does not fit the staging buffer; increase the HBM budget")
+        # a range the sampled splitters left larger than the staging buffer (skewed keys) is cut further on the host
+        cap_records = cap // S
+        views = [h.numpy() for h in spilled]
+        tasks: List[List[Slice]] = []
+        refined = 0
+        for c in range(nranges):
+            parts = split_range(views, [(g, int(cut[g, c]), int(cut[g, c + 1])) for g in range(G)], S, self.key_off, self.key_len, cap_records)
+            refined += len(parts) > 1
+            tasks.extend(parts)
+        if not tasks:
+            tasks = [[]]                                           # no records at all: one empty merge writes the EOF marker
         ev_in2 = [torch.cuda.Event() for _ in range(2)]
         ev_done2 = [torch.cuda.Event() for _ in range(2)]
 
         def stage_range(c: int, slot: int):
+            piece = {g: (a, b) for g, a, b in tasks[c]}
             bases, counts, off = [], [], slack
             with torch.cuda.stream(self.s_in):
                 if c >= 2:
                     self.s_in.wait_event(ev_done2[slot])
                 for g in range(G):
-                    a, b = int(cut[g, c]), int(cut[g, c + 1])
+                    a, b = piece.get(g, (0, 0))
                     off = (off + 15) // 16 * 16
                     if b > a:
                         d_in[slot][off:off + (b - a) * S].copy_(spilled[g][a * S:b * S], non_blocking=True)
@@ -167,14 +247,15 @@ class SpillMerger:
             return bases, counts
 
         staged = stage_range(0, 0)
-        for c in range(nranges):
+        for c in range(len(tasks)):
             slot = c % 2
-            nxt = stage_range(c + 1, (c + 1) % 2) if c + 1 < nranges else None
+            nxt = stage_range(c + 1, (c + 1) % 2) if c + 1 < len(tasks) else None
             cur.wait_event(ev_in2[slot])
-            last = c == nranges - 1
+            last = c == len(tasks) - 1
             n = device_merge(staged[0], staged[1], d_out[slot], write_eof=last)
             sink(d_out[slot], n * S + (2 if last else 0))
             ev_done2[slot].record(cur)
             staged = nxt
-        self.stats = {"groups": G, "ranges": int(nranges), "spilled_bytes": int(sum(h.numel() for h in spilled))}
+        self.stats = {"groups": G, "ranges": len(tasks), "refined_ranges": int(refined),
+                      "spilled_bytes": int(sum(h.numel() for h in spilled))}
         return total
