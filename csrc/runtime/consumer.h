@@ -97,9 +97,9 @@ public:
     void start();                       // issue the first fetch
     bool wait_first_chunk();            // true when the first chunk has landed (false: failed)
     bool next_block(const uint8_t** data, size_t* len) override;
-    long long raw_length() const { return raw_len_; }
-    long long part_length() const { return part_len_; }
-    long long size_hint() const override { return part_len_; }
+    long long raw_length() const { return raw_len_.load(std::memory_order_relaxed); }
+    long long part_length() const { return part_len_.load(std::memory_order_relaxed); }
+    long long size_hint() const override { return part_length(); }
     const std::string& map_id() const { return req_.map_id; }
 
 private:
@@ -115,7 +115,10 @@ private:
     bool have_pair_ = false;
     State state_[2] = {EMPTY, EMPTY};
     size_t filled_[2] = {0, 0};
-    long long fetched_ = 0, requested_ = 0, part_len_ = -1, raw_len_ = -1;
+    long long fetched_ = 0, requested_ = 0;
+    // written by the completion of every chunk (under mu_, always the same values after the first ack), read by the
+    // merge thread through the getters without the lock
+    std::atomic<long long> part_len_{-1}, raw_len_{-1};
     int next_slot_ = 0;   // slot the consumer reads next
     int busy_slot_ = -1;
     bool failed_ = false;

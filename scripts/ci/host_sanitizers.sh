@@ -28,10 +28,16 @@ if [ "$kind" = "thread" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
     tsan_lib="$(/usr/bin/g++ -print-file-name=libtsan.so)"
     stdcpp="$(/usr/bin/g++ -print-file-name=libstdc++.so.6)"
     log="$(mktemp)"
+    # reports go to files of their own (log_path): pytest captures the stderr of passing tests, which hid a report once
     UDA_KERNELS_LIB=/nonexistent.so UDA_B200_SKIP_BUILD=1 UDA_B200_RUNTIME_LIB="$root/build/thread/libuda.so" LD_PRELOAD="$tsan_lib $stdcpp" \
-        TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0" \
-        python -m pytest tests/test_runtime_cpu.py -x -q -p no:cacheprovider -k "plumbing or queues or thread_wrapper" > "$log" 2>&1 || { tail -30 "$log"; exit 1; }
+        TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 log_path=$tmp/tsan" \
+        python -m pytest tests/test_runtime_cpu.py -x -q -p no:cacheprovider -k "plumbing or queues or thread_wrapper" > "$log" 2>&1 || true
     tail -1 "$log"
-    if grep -q "WARNING: ThreadSanitizer" "$log"; then grep "SUMMARY: ThreadSanitizer" "$log" | sort | uniq -c; exit 1; fi
+    if ls "$tmp"/tsan.* > /dev/null 2>&1; then
+        grep -h -A12 "WARNING: ThreadSanitizer" "$tmp"/tsan.* | head -80
+        grep -h "SUMMARY: ThreadSanitizer" "$tmp"/tsan.* | sort | uniq -c
+        exit 1
+    fi
+    grep -q " passed" "$log" && ! grep -q " failed" "$log" || { tail -30 "$log"; exit 1; }
 fi
 echo "host sanitizer run ($kind): ok"
