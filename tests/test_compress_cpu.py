@@ -83,3 +83,32 @@ def test_frame_compress_segment_snappy_and_lzo_share_the_framing():
         assert pos == len(comp) and sum(raws) == len(plain) and all(r == 32768 for r in raws[:-1])
     with pytest.raises(KeyError):
         frame_compress_segment(plain, 32768, codec="zstd")
+
+
+@pytest.mark.parametrize("codec", ["snappy", "lzo"])
+def test_write_mof_compressed_layout(codec):
+    """Index of a compressed MOF: rawLength = plain bytes incl. the EOF marker, partLength = codec blocks + 4 checksum bytes;
+    the blocks of every segment decode back to the plain segment (what DeviceMOF.from_host_bytes(codec=...) does on the GPU)."""
+    import zlib
+    from uda_b200.utils import ifile
+    L = runtime()
+    rng = random.Random(3)
+    parts = [sorted((bytes(rng.randrange(97, 100) for _ in range(rng.randint(1, 12))), bytes(rng.randrange(256) for _ in range(rng.randint(0, 40))))
+                    for _ in range(n)) for n in (300, 0, 1200)]
+    file_out, index = ifile.write_mof_compressed(parts, lambda plain: frame_compress_segment(plain, 4096, codec=codec))
+    recs = ifile.read_index(index)
+    assert len(recs) == 3 and recs[0].start_offset == 0 and recs[2].start_offset + recs[2].part_length == len(file_out)
+    for p, r in enumerate(recs):
+        seg = file_out[r.start_offset:r.start_offset + r.part_length]
+        assert struct.unpack(">I", seg[-4:])[0] == zlib.crc32(seg[:-4]) & 0xFFFFFFFF
+        pos, plain = 0, b""
+        while pos + 8 <= len(seg) - 4:
+            raw, clen = struct.unpack(">II", seg[pos:pos + 8])
+            buf = C.create_string_buffer(max(raw, 1))
+            blk = seg[pos + 8:pos + 8 + clen]
+            fn = L.uda_rt_lzo1x_decompress if codec == "lzo" else L.uda_rt_snappy_uncompress
+            assert fn(blk, C.c_longlong(clen), buf, C.c_longlong(raw)) == 0
+            plain += buf.raw[:raw]
+            pos += 8 + clen
+        assert pos == len(seg) - 4 and len(plain) == r.raw_length
+        assert plain == ifile.encode_segment(parts[p], with_crc=False)

@@ -826,6 +826,31 @@ def test_lzo_decode_detects_corruption(built):
     assert bytes(out.cpu().numpy()) == plain
 
 
+@pytest.mark.parametrize("codec", ["org.apache.hadoop.io.compress.SnappyCodec", "com.hadoop.compression.lzo.LzoCodec"])
+def test_compressed_mof_is_expanded_while_it_is_loaded(built, codec):
+    """A Hadoop-written MOF of a job with compressed map outputs -> DeviceMOF of plain, 16-byte aligned segments with
+    valid checksums, equal to what the uncompressed job would have written."""
+    from uda_b200.mof import DeviceMOF
+    from uda_b200.ops.compress import frame_compress_segment
+    dev = _dev()
+    body = _cmp_body(1)
+    parts = [sorted(_tie_records(11 * p + 3, n, 1), key=body) for p, n in enumerate([900, 0, 2500, 40])]
+    short = "lzo" if "lzo" in codec.lower() else "snappy"
+    file_out, index = ifile.write_mof_compressed(parts, lambda plain: frame_compress_segment(plain, 4096, codec=short))
+    mof = DeviceMOF.from_host_bytes(file_out, index, dev, codec=codec, codec_block=4096)
+    assert mof.meta["expanded_from"] == codec and mof.num_partitions == len(parts)
+    host = mof.data.cpu().numpy()
+    for p, (start, raw, part) in enumerate(mof.index):
+        want = ifile.encode_segment(parts[p], with_crc=True)
+        assert start % 16 == 0 and raw == len(want) - 4 and part == len(want)
+        assert bytes(host[start:start + part]) == want
+        assert ifile.read_partition(bytes(host[:start + part]), mof.index_records()[p], verify_crc=True) == parts[p]
+    # a block table sized for larger blocks than the map side used is reported, not overrun
+    from uda_b200.runtime.failure import UdaFailure
+    with pytest.raises(UdaFailure):
+        DeviceMOF.from_host_bytes(file_out, index, dev, codec=codec, codec_block=1 << 20)
+
+
 def test_compressed_segments_through_var_merger(built):
     """Compressed sorted runs -> device Snappy decode -> VarMerger == CPU oracle."""
     from uda_b200.ops.compress import SnappyDecoder, frame_compress_segment

@@ -51,11 +51,43 @@ class DeviceMOF:
         return bytes(self.data[:end].cpu().numpy())
 
     @staticmethod
-    def from_host_bytes(file_out: bytes, file_out_index: bytes, device, path: str = "") -> "DeviceMOF":
+    def from_host_bytes(file_out: bytes, file_out_index: bytes, device, path: str = "", codec: Optional[str] = None,
+                        codec_block: int = 256 * 1024) -> "DeviceMOF":
+        """A MOF written by Hadoop (byte-exact ``file.out`` + ``file.out.index``) into HBM.
+
+        ``codec``: the job's ``mapred.map.output.compression.codec`` class name when the map outputs are compressed
+        (Snappy or LZO). The segments are then expanded on the device (``ops/compress.py``) as they are loaded, and the
+        resident MOF is the plain one the push and merge kernels expect: every segment on a 16-byte boundary,
+        ``rawLength`` plain bytes (records + EOF marker) followed by a CRC32 computed here, ``partLength = rawLength + 4``.
+        The reference expands compressed segments on the reducer, one block at a time on a decompress thread
+        (src/Merger/DecompressorWrapper.cc:168-197). ``codec_block`` is the smallest block size the map side may have
+        used (``io.compression.codec.{lzo,snappy}.buffersize``, 256 KiB by default): it sizes the block table.
+        """
         idx = np.array([[r.start_offset, r.raw_length, r.part_length] for r in read_index(file_out_index)], dtype=np.int64)
         buf = torch.empty(K.GATHER_SLACK + len(file_out) + K.GATHER_SLACK + 16, dtype=torch.uint8, device=device)
         buf[K.GATHER_SLACK:K.GATHER_SLACK + len(file_out)] = torch.frombuffer(bytearray(file_out), dtype=torch.uint8).to(device)
-        return DeviceMOF(buf[K.GATHER_SLACK:], idx, None, path)
+        if codec is None or codec in ("", "null"):
+            return DeviceMOF(buf[K.GATHER_SLACK:], idx, None, path)
+        from .ops.compress import decoder_for
+
+        comp = buf[K.GATHER_SLACK:]
+        starts, off = [], 0
+        for _, raw, _ in idx:
+            off = (off + 15) // 16 * 16
+            starts.append(off)
+            off += int(raw) + 4
+        out = torch.zeros(K.GATHER_SLACK + off + K.GATHER_SLACK + 16, dtype=torch.uint8, device=device)
+        plain = out[K.GATHER_SLACK:]
+        max_raw = int(idx[:, 1].max()) if len(idx) else 0
+        dec = decoder_for(codec, device, max(1, -(-max_raw // max(1, codec_block)) + 1))
+        for p, (start, raw, part) in enumerate(idx):
+            start, raw, part = int(start), int(raw), int(part)
+            seg = plain[starts[p]:]
+            dec.decode(comp[start:], part, out=seg, raw_len=raw)
+            dec.check(expect_raw=raw)                      # corrupt block, more blocks than planned, length mismatch
+            K.crc32(seg, raw, out_be4=seg[raw:raw + 4])
+        new_idx = np.array([[starts[p], int(idx[p, 1]), int(idx[p, 1]) + 4] for p in range(len(idx))], dtype=np.int64).reshape(-1, 3)
+        return DeviceMOF(plain, new_idx, None, path, {"expanded_from": codec})
 
 
 def uniform_splitters_w0(num_partitions: int) -> np.ndarray:

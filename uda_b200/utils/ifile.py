@@ -114,6 +114,22 @@ def write_mof(partitions: Sequence[Iterable[Tuple[bytes, bytes]]]) -> Tuple[byte
     return bytes(out), write_index(idx)
 
 
+def write_mof_compressed(partitions: Sequence[Iterable[Tuple[bytes, bytes]]], frame) -> Tuple[bytes, bytes]:
+    """Like :func:`write_mof` for a job with compressed map outputs. ``frame(plain) -> bytes`` turns a plain segment
+    body (records + EOF marker) into codec blocks ``[u32 BE rawLen][u32 BE compLen][bytes]...`` (e.g.
+    ``uda_b200.ops.compress.frame_compress_segment``). Hadoop's IFile.Writer puts the 4-byte checksum after the
+    compressed stream: ``rawLength`` = plain bytes incl. the EOF marker, ``partLength`` = compressed bytes + 4."""
+    out = bytearray()
+    idx: List[IndexRecord] = []
+    for recs in partitions:
+        plain = encode_segment(recs, with_crc=False)
+        seg = frame(plain)
+        seg += struct.pack(">I", zlib.crc32(seg) & 0xFFFFFFFF)
+        idx.append(IndexRecord(len(out), len(plain), len(seg)))
+        out += seg
+    return bytes(out), write_index(idx)
+
+
 def read_partition(mof: bytes, rec: IndexRecord, verify_crc: bool = True) -> List[Tuple[bytes, bytes]]:
     seg = mof[rec.start_offset : rec.start_offset + rec.part_length]
     return decode_segment(seg, verify_crc=verify_crc)
