@@ -149,7 +149,7 @@ def test_snappy_builtin(L):
 
 
 # ------------------------------------------------------------------------------------------ plumbing end to end
-def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress=None, val_len=None):
+def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress=None, val_len=None, dirs=None):
     rng = random.Random(seed)
     mofs = {}
     truth = [[] for _ in range(n_reduces)]
@@ -175,7 +175,9 @@ def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress
                 idx.append(ifile.IndexRecord(len(out), len(plain), len(seg)))
                 out += seg
             data, index = bytes(out), ifile.write_index(idx)
-        path = os.path.join(tmp, f"map_{m}.out")
+        where = dirs[m % len(dirs)] if dirs else tmp       # map outputs spread over the "disks" of mapred.local.dir
+        os.makedirs(where, exist_ok=True)
+        path = os.path.join(where, f"map_{m}.out")
         with open(path, "wb") as f:
             f.write(data)
         mofs[f"attempt_m_{m:06d}_0"] = (path, ifile.read_index(index))
@@ -183,15 +185,15 @@ def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress
 
 
 def _run_job(tmp, n_maps, n_reduces, recs, approach=1, buf_kb=8, key_class="org.apache.hadoop.io.LongWritable", key_len=10,
-             lpq_size=0, compress=None, codec="null", seed=1, val_len=None):
-    mofs, truth = _make_mofs(tmp, n_maps, n_reduces, recs, seed, key_len, compress, val_len)
+             lpq_size=0, compress=None, codec="null", seed=1, val_len=None, provider_conf=None, dirs=None):
+    mofs, truth = _make_mofs(tmp, n_maps, n_reduces, recs, seed, key_len, compress, val_len, dirs)
 
     def get_path(job, mapid, reduce):
         path, idx = mofs[mapid]
         r = idx[reduce]
         return r.start_offset, r.raw_length, r.part_length, path
 
-    prov = bridge.NativeRole(False, bridge.build_argv(port=0, buf_kb=buf_kb, provider=True), get_path=get_path)
+    prov = bridge.NativeRole(False, bridge.build_argv(port=0, buf_kb=buf_kb, provider=True), get_path=get_path, conf=provider_conf)
     assert not prov.failed, prov.last_error
     port = prov.port
     assert port > 0
@@ -233,6 +235,53 @@ def test_plumbing_online_4_maps_2_reducers(built, tmp_path):
         want = list(kway_merge(truth[r]))
         assert parse_stream(s) == want
         assert s == merged_stream(want)
+
+
+@pytest.mark.parametrize("threads_per_disk", [1, 3])
+def test_plumbing_blocked_reader_backend(built, tmp_path, threads_per_disk):
+    """The provider's second disk back-end (reference: AsyncReaderManager, src/MOFServer/AsyncReaderManager.cc:19-20 — a
+    queue and `mapred.uda.provider.blocked.threads.per.disk` pread threads per local dir); map outputs on two "disks" and
+    one outside every configured dir (served by the fallback queue)."""
+    d0, d1 = os.path.join(str(tmp_path), "disk0"), os.path.join(str(tmp_path), "disk1")
+    conf = {"mapred.uda.provider.reader": "blocked", "mapred.uda.provider.blocked.threads.per.disk": str(threads_per_disk),
+            "mapred.local.dir": f"{d0},{d1}"}
+    streams, truth, _, prov = _run_job(str(tmp_path), 5, 2, 350, buf_kb=16, seed=12, provider_conf=conf,
+                                       dirs=[d0, d1, os.path.join(str(tmp_path), "elsewhere")])
+    for r, s in enumerate(streams):
+        assert parse_stream(s) == list(kway_merge(truth[r]))
+    assert any("reader=blocked" in m for _, m in prov.logs)
+
+
+def test_log_to_unique_file_writes_the_provider_log(built, tmp_path):
+    """mapred.uda.log.to.unique.file = true: the native side logs to <log dir>/hadoop-<user>-udaMOFSupplier-<host>.log
+    instead of the host's logger (reference: src/CommUtils/IOUtility.cc log_to_unique_file, build/README 'log files')."""
+    logdir = str(tmp_path)
+    prov = bridge.NativeRole(False, bridge.build_argv(port=0, buf_kb=64, provider=True, log_dir=logdir), log_to_unique_file=True)
+    try:
+        assert not prov.failed, prov.last_error
+        prov.command(bridge.form_cmd(bridge.EXIT, []))
+    finally:
+        prov.close()
+    files = [f for f in os.listdir(logdir) if "udaMOFSupplier" in f and f.endswith(".log")]
+    assert len(files) == 1 and files[0].startswith("hadoop-")
+    text = open(os.path.join(logdir, files[0])).read()
+    assert "MOFSupplier ready" in text and "INFO" in text and "provider.cc" in text
+    assert not any("MOFSupplier ready" in m for _, m in prov.logs)      # nothing went to the host's logger
+    # the next role in this process logs through the host again
+    prov2 = bridge.NativeRole(False, bridge.build_argv(port=0, buf_kb=64, provider=True, log_dir=logdir))
+    try:
+        assert any("MOFSupplier ready" in m for _, m in prov2.logs)
+        prov2.command(bridge.form_cmd(bridge.EXIT, []))
+    finally:
+        prov2.close()
+
+
+def test_provider_refuses_an_unknown_reader_backend(built):
+    prov = bridge.NativeRole(False, bridge.build_argv(port=0, buf_kb=64, provider=True), conf={"mapred.uda.provider.reader": "mmap"})
+    try:
+        assert prov.failed and "unknown reader kind" in (prov.last_error or "") + " ".join(m for _, m in prov.logs)
+    finally:
+        prov.close()
 
 
 def test_plumbing_small_buffers_straddling_records(built, tmp_path):
