@@ -185,8 +185,9 @@ def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress
 
 
 def _run_job(tmp, n_maps, n_reduces, recs, approach=1, buf_kb=8, key_class="org.apache.hadoop.io.LongWritable", key_len=10,
-             lpq_size=0, compress=None, codec="null", seed=1, val_len=None, provider_conf=None, dirs=None):
-    mofs, truth = _make_mofs(tmp, n_maps, n_reduces, recs, seed, key_len, compress, val_len, dirs)
+             lpq_size=0, compress=None, codec="null", seed=1, val_len=None, provider_conf=None, dirs=None, prebuilt=None,
+             max_block=1 << 20, expect_failure=False):
+    mofs, truth = prebuilt or _make_mofs(tmp, n_maps, n_reduces, recs, seed, key_len, compress, val_len, dirs)
 
     def get_path(job, mapid, reduce):
         path, idx = mofs[mapid]
@@ -215,10 +216,14 @@ def _run_job(tmp, n_maps, n_reduces, recs, approach=1, buf_kb=8, key_class="org.
                 if s.endswith(b"\xff\xff") and cons.stat("records_emitted") == want:
                     break
                 time.sleep(0.02)
+            if expect_failure:
+                assert cons.failed and cons.failures >= 1
+                streams.append(cons.stream())
+                continue
             assert not cons.failed and cons.failures == 0, cons.last_error
             cons.final_stats = {k: cons.stat(k) for k in ("records_emitted", "lpqs_spilled", "device_merges", "device_fused_merges")}
             streams.append(cons.stream())
-            assert all(len(b) <= (1 << 20) for b in cons.blocks)
+            assert all(len(b) <= max_block for b in cons.blocks)
             assert cons.fetch_over >= 1
         return streams, truth, consumers, prov
     finally:
@@ -282,6 +287,54 @@ def test_provider_refuses_an_unknown_reader_backend(built):
         assert prov.failed and "unknown reader kind" in (prov.last_error or "") + " ".join(m for _, m in prov.logs)
     finally:
         prov.close()
+
+
+def _prebuilt_mofs(tmp, per_map_parts):
+    """MOFs from explicit record lists: per_map_parts[m][r] = sorted records of map m for reducer r."""
+    mofs, truth = {}, [[] for _ in per_map_parts[0]]
+    for m, parts in enumerate(per_map_parts):
+        data, index = ifile.write_mof(parts)
+        path = os.path.join(tmp, f"map_{m}.out")
+        with open(path, "wb") as f:
+            f.write(data)
+        mofs[f"attempt_m_{m:06d}_0"] = (path, ifile.read_index(index))
+        for r, recs in enumerate(parts):
+            truth[r].append(recs)
+    return mofs, truth
+
+
+@pytest.mark.parametrize("approach", [1, 2])
+def test_plumbing_record_larger_than_a_block(built, tmp_path, approach):
+    """A record above 1 MiB cannot share a block: it is delivered alone, in a block of its own size, between ordinary
+    blocks of whole records (reference: write_kv_to_stream refuses nothing, the Java side grows its buffer)."""
+    big = bytes(range(256)) * 5000                                    # 1.28 MB value
+    parts = [[[(b"a" * 10, b"x"), (b"m" * 10, big), (b"z" * 10, b"y")]],
+             [[(b"b" * 10, b"p" * 100), (b"n" * 10, b"q" * 100)]],
+             [[(b"c" * 10, b""), (b"m" * 10 + b"!", b"after the big one")]]]
+    streams, truth, consumers, _ = _run_job(str(tmp_path), 3, 1, 0, approach=approach, prebuilt=_prebuilt_mofs(str(tmp_path), parts),
+                                            max_block=len(big) + 64)
+    assert parse_stream(streams[0]) == list(kway_merge(truth[0]))
+    sizes = [len(b) for b in consumers[0].blocks]
+    assert max(sizes) > (1 << 20) and sum(1 for x in sizes if x > (1 << 20)) == 1
+
+
+def test_unsupported_merge_approach_fails_over(built, tmp_path):
+    """An approach the native side does not know ends in one failureInUda up-call (-> vanilla shuffle), not in a hang."""
+    parts = [[[(b"k" * 10, b"v")]]]
+    _run_job(str(tmp_path), 1, 1, 0, approach=7, prebuilt=_prebuilt_mofs(str(tmp_path), parts), expect_failure=True)
+
+
+def test_truncated_segment_is_a_failure_not_garbage(built, tmp_path):
+    """The index promises more bytes than the segment's records fill (EOF marker missing): the consumer must not emit a
+    silently shortened stream (reference: BaseSegment::nextKVInternal bounds checks, src/Merger/StreamRW.cc:334-404)."""
+    recs = [(bytes([65 + i]) * 10, b"v" * 50) for i in range(20)]
+    body = ifile.encode_segment(recs, with_crc=False)[:-2]           # records without the EOF marker
+    cut = body[:len(body) - 30]                                      # ... and the last record cut short
+    path = os.path.join(str(tmp_path), "map_0.out")
+    with open(path, "wb") as f:
+        f.write(cut + b"\0\0\0\0")
+    mofs = {"attempt_m_000000_0": (path, [ifile.IndexRecord(0, len(cut), len(cut) + 4)])}
+    _run_job(str(tmp_path), 1, 1, 0, prebuilt=(mofs, [[recs]]), expect_failure=True)
 
 
 def test_plumbing_small_buffers_straddling_records(built, tmp_path):
@@ -550,8 +603,21 @@ def test_provider_rejects_malformed_fetch_requests(built, tmp_path):
                     "job_1:attempt_unknown:0:0:0:7:4096:0::0:0"):             # no such map output
             text, plen = ask(bad)
             assert "UDA_FETCH_REJECTED" in text and plen == 0, (bad, text)
+        # an offset exactly at the end of the partition is legal: empty chunk, normal ack
+        text, plen = ask(f"job_1:{mapid}:{part_len}:0:0:7:4096:0::0:0")
+        assert "UDA_FETCH_REJECTED" not in text and plen == 0
+        # follow-up requests carry the index record themselves: a file that does not exist, a file shorter than the record
+        # claims (short read), a path above the 600-character limit (answered with the marker the reducer logs about)
+        text, plen = ask(f"job_1:{mapid}:0:0:0:7:4096:0:{path}.missing:{part_len}:{part_len}")
+        assert "UDA_FETCH_REJECTED" in text and plen == 0
+        text, plen = ask(f"job_1:{mapid}:{(part_len + 4095) // 4096 * 4096 + 8192}:0:0:7:4096:0:{path}:{part_len + 100000}:{part_len + 100000}")
+        assert "UDA_FETCH_REJECTED" in text and plen == 0                         # a chunk past the end of the file: short read
+        long_path = "/" + "d" * 700
+        text, plen = ask(f"job_1:{mapid}:0:0:0:7:4096:0:{long_path}:10:10")
+        assert plen == 0 and "UDA_FETCH_REJECTED" not in text and long_path not in text
         good, plen = ask(f"job_1:{mapid}:0:0:0:7:4096:0::0:0")              # the provider is still serving
         assert plen == min(4096, part_len)
+        assert any("short" in m or "failed" in m for lvl, m in prov.logs if lvl <= 2)
     finally:
         prov.command(bridge.form_cmd(bridge.EXIT, []))
         prov.close()
