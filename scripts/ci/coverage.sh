@@ -19,7 +19,7 @@ g++ $flags tests/native/test_jni_mock.cc -o "$out/test_jni_mock" -L"$out" -luda 
 tmp="$(mktemp -d)"; trap 'rm -rf "$tmp"' EXIT
 "$out/test_jni_mock" "$out/libuda.so" "$tmp" > "$out/test_jni_mock.log" 2>&1
 UDA_KERNELS_LIB=/nonexistent.so UDA_B200_SKIP_BUILD=1 UDA_B200_RUNTIME_LIB="$root/$out/libuda.so" \
-    python -m pytest tests/test_runtime_cpu.py tests/test_fuzz_cpu.py -x -q -p no:cacheprovider -k "not reader_bench and not regression_driver and not jni" \
+    python -m pytest tests/test_runtime_cpu.py tests/test_fuzz_cpu.py tests/test_device_merge_mock_cpu.py -x -q -p no:cacheprovider -k "not reader_bench and not regression_driver and not jni" \
     > "$out/pytest.log" 2>&1 || { tail -20 "$out/pytest.log"; exit 1; }
 tail -1 "$out/pytest.log"
 # one JSON report per translation unit; a header's inline functions appear in every unit that includes it and count as
@@ -46,10 +46,6 @@ with open(f"{out}/summary.txt", "w") as fh:
         tot += n; cov += c
         fh.write(f"{name:40s} {100 * c / max(n, 1):6.1f} % of {n} lines\n")
     fh.write(f"{'TOTAL':40s} {100 * cov / max(tot, 1):6.1f} % of {tot} lines\n")
-    gpu_only = "csrc/runtime/device_merge.cc"
-    if gpu_only in lines:
-        n = len(lines[gpu_only]); c = sum(1 for v in lines[gpu_only].values() if v > 0)
-        fh.write(f"{'TOTAL without ' + gpu_only + ' (needs a GPU)':40s} {100 * (cov - c) / max(tot - n, 1):6.1f} % of {tot - n} lines\n")
     with open(f"{out}/missed.txt", "w") as mh:
         for name in sorted(lines):
             miss = sorted(k for k, v in lines[name].items() if v == 0)

@@ -21,7 +21,7 @@ if [ "$kind" = "address" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
     stdcpp="$(/usr/bin/g++ -print-file-name=libstdc++.so.6)"
     UDA_B200_SKIP_BUILD=1 UDA_B200_RUNTIME_LIB="$root/build/address/libuda.so" LD_PRELOAD="$asan_lib $stdcpp" \
         ASAN_OPTIONS="detect_leaks=0:abort_on_error=0:protect_shadow_gap=0" \
-        python -m pytest tests/test_runtime_cpu.py tests/test_fuzz_cpu.py -x -q -p no:cacheprovider -k "not reader_bench and not regression_driver"
+        python -m pytest tests/test_runtime_cpu.py tests/test_fuzz_cpu.py tests/test_device_merge_mock_cpu.py -x -q -p no:cacheprovider -k "not reader_bench and not regression_driver"
 fi
 if [ "$kind" = "thread" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
     # the multi-threaded part of the suite (provider, consumers, transport, hybrid merge, decompression) under TSAN
@@ -31,7 +31,7 @@ if [ "$kind" = "thread" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
     # reports go to files of their own (log_path): pytest captures the stderr of passing tests, which hid a report once
     UDA_KERNELS_LIB=/nonexistent.so UDA_B200_SKIP_BUILD=1 UDA_B200_RUNTIME_LIB="$root/build/thread/libuda.so" LD_PRELOAD="$tsan_lib $stdcpp" \
         TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 log_path=$tmp/tsan" \
-        python -m pytest tests/test_runtime_cpu.py -x -q -p no:cacheprovider -k "plumbing or queues or thread_wrapper" > "$log" 2>&1 || true
+        python -m pytest tests/test_runtime_cpu.py tests/test_device_merge_mock_cpu.py -x -q -p no:cacheprovider -k "plumbing or queues or thread_wrapper or mock" > "$log" 2>&1 || true
     tail -1 "$log"
     if ls "$tmp"/tsan.* > /dev/null 2>&1; then
         grep -h -A12 "WARNING: ThreadSanitizer" "$tmp"/tsan.* | head -80

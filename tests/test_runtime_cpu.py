@@ -187,7 +187,8 @@ def _make_mofs(tmp, n_maps, n_reduces, recs_per_part, seed, key_len=10, compress
 def _run_job(tmp, n_maps, n_reduces, recs, approach=1, buf_kb=8, key_class="org.apache.hadoop.io.LongWritable", key_len=10,
              lpq_size=0, compress=None, codec="null", seed=1, val_len=None, provider_conf=None, dirs=None, prebuilt=None,
              max_block=1 << 20, expect_failure=False):
-    mofs, truth = prebuilt or _make_mofs(tmp, n_maps, n_reduces, recs, seed, key_len, compress, val_len, dirs)
+    # (_make_mofs is replaced by callers that need other record shapes: only pass `dirs` when it is used)
+    mofs, truth = prebuilt or _make_mofs(tmp, n_maps, n_reduces, recs, seed, key_len, compress, val_len, **({"dirs": dirs} if dirs else {}))
 
     def get_path(job, mapid, reduce):
         path, idx = mofs[mapid]

@@ -109,6 +109,13 @@ def build(verbose: bool = False) -> dict:
         if cc_objs:
             _run([CXX, *CXX_FLAGS, str(src), "-o", str(exe), f"-L{LIB_DIR}", "-luda", f"-Wl,-rpath,{LIB_DIR}", "-ldl"])
             out[src.stem] = exe
+    # host-only stand-in for the kernel library: lets the CPU tests drive csrc/runtime/device_merge.cc (UDA_KERNELS_LIB)
+    mock = ROOT / "tests" / "native" / "mock" / "mock_kernels.cc"
+    if mock.exists():
+        mlib = bin_dir / "libuda_kernels_mock.so"
+        if not mlib.exists() or mlib.stat().st_mtime < max(mock.stat().st_mtime, (ROOT / "include" / "uda_b200.h").stat().st_mtime):
+            _run([CXX, *CXX_FLAGS, "-shared", str(mock), "-o", str(mlib)])
+        out["kernels_mock"] = mlib
     if verbose:
         for o in cu_objs:
             log = o.with_suffix(".log")
@@ -136,6 +143,11 @@ def build_host_sanitized(kind: str) -> dict:
         exe = out_dir / src.stem
         _run([cxx, *flags, str(src), "-o", str(exe), f"-L{out_dir}", "-luda", f"-Wl,-rpath,{out_dir}", "-ldl"])
         out[src.stem] = exe
+    mock = ROOT / "tests" / "native" / "mock" / "mock_kernels.cc"
+    if mock.exists():
+        mlib = out_dir / "libuda_kernels_mock.so"
+        _run([cxx, *flags, "-shared", str(mock), "-o", str(mlib)])
+        out["kernels_mock"] = mlib
     return out
 
 
