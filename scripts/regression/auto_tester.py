@@ -38,7 +38,23 @@ WORKLOADS = {
     "spill": ("benchmarks/spill_bench.py", lambda r, n: [*(r.get("extra", "").split())]),
     "sort": ("benchmarks/sort_bench.py", lambda r, n: ["--records", r.get("records", "200000"), *(r.get("extra", "").split())]),
     "plumbing": ("benchmarks/plumbing_bench.py", lambda r, n: [*(r.get("extra", "").split())]),
+    # the reference arm of bench.py: the reference's own reducer code, CPU only (baseline/build_ref.py)
+    "reference": ("bench.py", lambda r, n: ["--impl", "reference", "--gpus", str(n), "--steps", r.get("steps") or "2", "--warmup", r.get("warmup") or "1",
+                                           "--records-per-gpu", r.get("records") or "2000000", "--maps-per-gpu", r.get("maps") or "4",
+                                           *(r.get("extra", "").split())]),
 }
+CPU_WORKLOADS = ("plumbing", "reference")   # rows that run without a GPU
+
+
+def row_env(t):
+    """Optional `env` column: `NAME=value;NAME2=value2`, `$ROOT` expands to the repository (e.g. the host-only mock of the
+    kernel library for merge approach 3: UDA_KERNELS_LIB=$ROOT/build/bin/libuda_kernels_mock.so)."""
+    out = {}
+    for item in (t.get("env") or "").split(";"):
+        if "=" in item:
+            k, v = item.split("=", 1)
+            out[k.strip()] = v.strip().replace("$ROOT", str(ROOT))
+    return out
 
 
 def sh(cmd, **kw):
@@ -67,7 +83,7 @@ def phase_control(ctx):
     ctx["ngpu"] = torch.cuda.device_count() if torch.cuda.is_available() else 0
     for t in ctx["tests"]:
         need = int(t.get("gpus", "1") or 1)
-        t["skip"] = "" if need <= ctx["ngpu"] or t["workload"] == "plumbing" else f"needs {need} GPUs, {ctx['ngpu']} visible"
+        t["skip"] = "" if need <= ctx["ngpu"] or t["workload"] in CPU_WORKLOADS else f"needs {need} GPUs, {ctx['ngpu']} visible"
 
 
 def phase_configure(ctx):
@@ -106,7 +122,7 @@ def phase_execute(ctx):
             cmd = [sys.executable, str(ROOT / script), *args]
         t0 = time.time()
         try:
-            p = sh(cmd, cwd=ROOT, timeout=int(t.get("timeout", "900") or 900), env={**os.environ, "UDA_REGRESSION_DIR": t["dir"]})
+            p = sh(cmd, cwd=ROOT, timeout=int(t.get("timeout", "900") or 900), env={**os.environ, "UDA_REGRESSION_DIR": t["dir"], **row_env(t)})
             rc, out, err = p.returncode, p.stdout, p.stderr
         except subprocess.TimeoutExpired as e:
             rc, out, err = 124, (e.stdout or b"").decode() if isinstance(e.stdout, bytes) else (e.stdout or ""), "timeout"
