@@ -14,6 +14,13 @@ python -m pytest tests/ -x -q -m "not gpu"
 echo "== host sanitizers =="
 scripts/ci/host_sanitizers.sh address
 scripts/ci/host_sanitizers.sh thread
+scripts/ci/host_sanitizers.sh undefined
+echo "== coverage of the host runtime =="
+scripts/ci/coverage.sh | tail -3
+echo "== reference arm (the reference's own reducer sources, unmodified) =="
+python baseline/build_ref.py > /dev/null && python bench.py --impl reference --steps 1 --warmup 0 --records-per-gpu 500000 | cut -c1-160
+echo "== CPU regression =="
+UDA_LIMITED_HOME="${TMPDIR:-/tmp}/uda_ci_regression" scripts/regression_limited/run.sh | tail -8
 echo "== static analysis =="
 scripts/ci/static_analysis.sh
 echo "== SASS evidence =="
