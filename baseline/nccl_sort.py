@@ -22,6 +22,17 @@ from uda_b200.mof import TERA_STRIDE
 from uda_b200.ops import kernels as K
 
 
+def pack_keys(recs: torch.Tensor):
+    """10-byte keys of framed records ``[n, 102]`` -> (8-byte prefix as a sortable int64, 2-byte tail as int32).
+
+    One byte-reversed copy of the key bytes viewed as integers (little-endian hosts): 10 bytes written per record,
+    no per-byte widening. (The first version of this arm shifted and summed an ``[n, 8]`` int64 temporary, 64 bytes per
+    record; the numbers in BASELINE.md were measured with that version.)"""
+    w0 = recs[:, 2:10].flip(1).contiguous().view(torch.int64).view(-1) ^ (-(1 << 63))   # unsigned order as signed order
+    tail = recs[:, 10:12].flip(1).contiguous().view(torch.int16).view(-1).to(torch.int32) & 0xFFFF
+    return w0, tail
+
+
 class NcclSortJob:
     launches_per_step = 0  # no kernels of this repository inside the timed region
 
@@ -56,7 +67,6 @@ class NcclSortJob:
         assert self.n_out == j.n_out
         self.recv = torch.empty((self.n_out, TERA_STRIDE), dtype=torch.uint8, device=dev)
         self.out = torch.empty(self.n_out * TERA_STRIDE + 2 + 64, dtype=torch.uint8, device=dev)
-        self.shifts = torch.tensor([56, 48, 40, 32, 24, 16, 8, 0], dtype=torch.int64, device=dev)
         # free what the baseline does not use
         j.mofs = []
         j.merger = None
@@ -68,9 +78,7 @@ class NcclSortJob:
             dist.all_to_all_single(self.recv, self.send, output_split_sizes=self.recv_counts, input_split_sizes=self.send_counts)
         else:
             self.recv.copy_(self.send)
-        keys = self.recv[:, 2:12]
-        tail = (keys[:, 8].to(torch.int32) << 8) | keys[:, 9].to(torch.int32)
-        w0 = (keys[:, :8].to(torch.int64) << self.shifts).sum(dim=1) ^ (-(1 << 63))
+        w0, tail = pack_keys(self.recv)
         i1 = torch.sort(tail, stable=True).indices
         i2 = torch.sort(w0[i1], stable=True).indices
         perm = i1[i2]

@@ -1,0 +1,27 @@
+"""The NCCL + torch.sort comparison arm (baseline/nccl_sort.py): its key packing and two-pass ordering, on CPU tensors."""
+import numpy as np
+import torch
+
+from baseline.nccl_sort import pack_keys
+
+
+def test_pack_keys_orders_like_the_key_bytes():
+    g = torch.Generator().manual_seed(3)
+    recs = torch.randint(0, 256, (5000, 102), dtype=torch.uint8, generator=g)
+    recs[:200, 2:10] = recs[0, 2:10]                        # equal 8-byte prefixes: the tail decides
+    recs[200:260, 2:12] = recs[200, 2:12]                   # fully equal keys: stable order decides
+    recs[300, 2:12] = 0
+    recs[301, 2:12] = 255
+    w0, tail = pack_keys(recs)
+    keys = recs[:, 2:12].numpy()
+    # straightforward restatement
+    want_w0 = np.zeros(len(keys), dtype=np.uint64)
+    for b in range(8):
+        want_w0 = (want_w0 << np.uint64(8)) | keys[:, b].astype(np.uint64)
+    assert ((w0.numpy().view(np.uint64) ^ np.uint64(1 << 63)) == want_w0).all()
+    assert (tail.numpy() == ((keys[:, 8].astype(np.int32) << 8) | keys[:, 9])).all()
+    # the arm's two stable passes give the order of the raw key bytes, ties in input order
+    i1 = torch.sort(tail, stable=True).indices
+    perm = i1[torch.sort(w0[i1], stable=True).indices].numpy()
+    want = sorted(range(len(keys)), key=lambda i: (keys[i].tobytes(), i))
+    assert perm.tolist() == want
