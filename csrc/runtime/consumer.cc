@@ -821,7 +821,8 @@ void Consumer::merge_device() {
     const auto t_fetched = std::chrono::steady_clock::now();
     fetch_ms_ = (int)std::chrono::duration_cast<std::chrono::milliseconds>(t_fetched - t_start).count();
     UDA_LOG(lsINFO, "device merge fetch: %d ms total, %lld ms waiting for chunks, %lld ms copying", fetch_ms_.load(), fetch_wait_us_ / 1000, fetch_copy_us_ / 1000);
-    if (DeviceMerge::instance().merge(segs, key_kind_, kStagingBytes, deliver, &records, &why)) {
+    DeviceMerge::Refusal refusal = DeviceMerge::Refusal::NONE;
+    if (DeviceMerge::instance().merge(segs, key_kind_, kStagingBytes, deliver, &records, &why, &refusal)) {
         emitted_ += (uint64_t)records;
         device_merges_++;
         device_ms_ = (int)std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t_fetched).count();
@@ -829,11 +830,84 @@ void Consumer::merge_device() {
                 fetch_ms_.load(), device_ms_.load());
         return;
     }
+    if (refusal == DeviceMerge::Refusal::MEMORY && segs.size() >= 2) {
+        UDA_LOG(lsINFO, "device merge: %s; merging in groups", why.c_str());
+        if (merge_device_grouped(&segs, deliver)) {
+            device_ms_ = (int)std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t_fetched).count();
+            return;
+        }
+        why += "; no grouping fits either";
+    }
     UDA_LOG(lsWARN, "device merge not possible (%s): merging on the CPU", why.c_str());
     MergeHeap heap(key_kind_);
     for (auto& hs : segs)
         heap.insert(std::make_unique<Segment>(std::make_unique<MemorySource>(hs.bytes.data(), (size_t)hs.raw_len()), segment_seq_++));
     merging_phase(&heap, deliver, true);
+}
+
+bool Consumer::merge_device_grouped(std::vector<HostSegment>* segs, const std::function<void(const uint8_t*, size_t)>& deliver) {
+    DeviceMerge& dm = DeviceMerge::instance();
+    const size_t k = segs->size();
+    std::vector<std::vector<uint8_t>> runs;
+    size_t groups = 2;
+    for (;; groups *= 2) {
+        if (groups > k) return false;   // even single segments do not fit: the caller merges on the CPU
+        // consecutive segments per group, cut at equal shares of the bytes (the arrival order is already shuffled)
+        long long total = 0;
+        for (const auto& sg : *segs) total += sg.raw_len();
+        std::vector<size_t> first(groups + 1, k);
+        first[0] = 0;
+        {
+            long long acc = 0;
+            size_t g = 1;
+            for (size_t i = 0; i < k && g < groups; ++i) {
+                acc += (*segs)[i].raw_len();
+                // the cut after segment i closes group g when the share is reached, keeping one segment for every later group
+                while (g < groups && (acc * (long long)groups >= total * (long long)g || k - (i + 1) <= groups - g)) first[g++] = i + 1;
+            }
+        }
+        runs.clear();
+        bool ok = true, memory = false;
+        for (size_t g = 0; g < groups && ok; ++g) {
+            if (stop_) throw UdaError("stopped while merging");
+            const size_t a = first[g], b = first[g + 1];
+            if (a >= b) { runs.emplace_back(std::vector<uint8_t>{0xFF, 0xFF}); continue; }   // an empty group is an empty run
+            std::vector<HostSegment> part;
+            part.reserve(b - a);
+            long long bytes = 2;
+            for (size_t i = a; i < b; ++i) { bytes += (*segs)[i].raw_len() - 2; part.push_back(std::move((*segs)[i])); }
+            std::vector<uint8_t> run;
+            run.reserve((size_t)bytes);
+            std::string why;
+            long long recs = 0;
+            DeviceMerge::Refusal refusal = DeviceMerge::Refusal::NONE;
+            try {
+                ok = dm.merge(part, key_kind_, kStagingBytes, [&](const uint8_t* p, size_t len) { run.insert(run.end(), p, p + len); }, &recs, &why,
+                              &refusal);
+            } catch (...) {
+                for (size_t i = a; i < b; ++i) (*segs)[i] = std::move(part[i - a]);
+                throw;
+            }
+            for (size_t i = a; i < b; ++i) (*segs)[i] = std::move(part[i - a]);   // the caller may still need them (CPU merge)
+            if (!ok) {
+                memory = refusal == DeviceMerge::Refusal::MEMORY;
+                UDA_LOG(lsINFO, "device merge of group %zu/%zu refused (%s)", g + 1, groups, why.c_str());
+                break;
+            }
+            runs.push_back(std::move(run));
+        }
+        if (ok) break;
+        if (!memory) return false;
+    }
+    UDA_LOG(lsINFO, "device merge in %zu groups of segments (device memory bounds the group size); final merge of the %zu runs on the CPU", groups,
+            runs.size());
+    for (auto& sg : *segs) { std::vector<uint8_t>().swap(sg.bytes); std::vector<long long>().swap(sg.rec_off); }   // the runs hold the data now
+    MergeHeap heap(key_kind_);
+    for (auto& r : runs) heap.insert(std::make_unique<Segment>(std::make_unique<MemorySource>(r.data(), r.size()), segment_seq_++));
+    device_groups_ = (int)groups;
+    device_merges_ += (int)groups;
+    merging_phase(&heap, deliver, true);
+    return true;
 }
 
 void Consumer::merge_hybrid() {

@@ -41,6 +41,8 @@ constexpr int kExtraBuffers = 10;           // EXTRA_RDMA_BUFFERS (src/Merger/re
 constexpr int kProgressEvery = 20;          // fetchOverMessage cadence (src/Merger/MergeManager.cc:124-130)
 
 // ---- byte sources -------------------------------------------------------------------------------------
+struct HostSegment;   // device_merge.h
+
 class ByteSource {
 public:
     virtual ~ByteSource() = default;
@@ -226,6 +228,7 @@ public:
     uint64_t records_emitted() const { return emitted_.load(); }
     int lpqs_spilled() const { return spilled_.load(); }
     int device_merges() const { return device_merges_.load(); }
+    int device_groups() const { return device_groups_.load(); }
     int fetch_ms() const { return fetch_ms_.load(); }
     int device_ms() const { return device_ms_.load(); }
 
@@ -236,6 +239,9 @@ private:
     void merge_online();
     void merge_hybrid();
     void merge_device();   // approach 3: fetch to host memory, merge on the GPU (device_merge.h), CPU heap merge as fallback
+    // a partition that does not fit the device's free memory: groups of segments are merged on the device into host runs
+    // (the hybrid merge's LPQs, src/Merger/MergeManager.cc:202-288, with the device as the LPQ merger), a heap merges the runs
+    bool merge_device_grouped(std::vector<HostSegment>* segs, const std::function<void(const uint8_t*, size_t)>& deliver);
     // fetch `count` map outputs into `heap`; reports progress every kProgressEvery segments
     void fetching_phase(MergeHeap* heap, int count, int* progress);
     void merging_phase(MergeHeap* heap, const std::function<void(const uint8_t*, size_t)>& sink, bool final_stream);
@@ -258,7 +264,7 @@ private:
     std::vector<uint8_t> staging_[2];
     std::atomic<uint64_t> emitted_{0};
     std::atomic<int> spilled_{0};
-    std::atomic<int> device_merges_{0}, fetch_ms_{0}, device_ms_{0};
+    std::atomic<int> device_merges_{0}, device_groups_{0}, fetch_ms_{0}, device_ms_{0};
     int segment_seq_ = 0;
     long long fetch_wait_us_ = 0, fetch_copy_us_ = 0;   // merge_device(): time blocked in next_block / appending to host memory
 };

@@ -261,7 +261,8 @@ void DeviceMerge::stream_out(const uint8_t* d_out, const std::vector<unsigned lo
 // Fixed-shape records: H2D of the segments, the fused record merge (uda_merge_records_fixed: every record is read once and
 // written once on the device), D2H window by window. Returns false with *why set when nothing has been delivered yet.
 bool DeviceMerge::merge_fixed(const std::vector<HostSegment>& segs, int stride, int key_off, int key_len, long long n, size_t max_block,
-                              const std::function<void(const uint8_t*, size_t)>& sink, std::string* why) {
+                              const std::function<void(const uint8_t*, size_t)>& sink, std::string* why, bool* out_of_memory) {
+    *out_of_memory = false;
     const Api& a = *api_;
     const int k = (int)segs.size();
     bool delivered = false;
@@ -284,6 +285,7 @@ bool DeviceMerge::merge_fixed(const std::vector<HostSegment>& segs, int stride, 
         long long free_b = 0, total_b = 0;
         if (a.mem_info(&free_b, &total_b) != 0 || need > (long long)(0.9 * (double)free_b)) {
             *why = "partition needs " + std::to_string(need >> 20) + " MiB of device memory, " + std::to_string(free_b >> 20) + " MiB free";
+            *out_of_memory = true;
             return false;
         }
         DeviceArena arena{this, a.dev_free, {}};
@@ -331,8 +333,12 @@ bool DeviceMerge::merge_fixed(const std::vector<HostSegment>& segs, int stride, 
 }
 
 bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size_t max_block,
-                        const std::function<void(const uint8_t*, size_t)>& sink, long long* records_out, std::string* why) {
-    if (!ok_) { if (why) *why = why_; return false; }
+                        const std::function<void(const uint8_t*, size_t)>& sink, long long* records_out, std::string* why,
+                        Refusal* refusal) {
+    Refusal dummy;
+    if (!refusal) refusal = &dummy;
+    *refusal = Refusal::NONE;
+    if (!ok_) { if (why) *why = why_; *refusal = Refusal::UNAVAILABLE; return false; }
     const Api& a = *api_;
     const int k = (int)segs.size();
     long long n = 0, data_bytes = 64, out_bytes = 2;
@@ -355,22 +361,33 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
         return true;
     }
     // limits of the kernel library: uda_kway_merge_entries takes at most 4096 runs, the entry format 2^31 - 2 records
-    if (k > 4096 || n >= (1LL << 31) - 1) { if (why) *why = "partition too large for the device merge (runs > 4096 or records >= 2^31 - 1)"; return false; }
+    if (k > 4096 || n >= (1LL << 31) - 1) {
+        if (why) *why = "partition too large for the device merge (runs > 4096 or records >= 2^31 - 1)";
+        *refusal = Refusal::LIMITS;
+        return false;
+    }
     // ---- fast path: records of one fixed shape go through the fused record merge (the kernel of the TeraSort headline)
     FixedShape fs{0, 0, 0};
     if (fixed_shape(segs, kind, &fs) && a.merge_records_supported(k, n, fs.stride, fs.key_len)) {
         std::string why_fixed;
-        if (merge_fixed(segs, fs.stride, fs.key_off, fs.key_len, n, max_block, sink, &why_fixed)) return true;
+        bool oom = false;
+        if (merge_fixed(segs, fs.stride, fs.key_off, fs.key_len, n, max_block, sink, &why_fixed, &oom)) return true;
+        if (oom) {   // the general path needs more memory than the fused one: no point in trying it
+            if (why) *why = why_fixed;
+            *refusal = Refusal::MEMORY;
+            return false;
+        }
         UDA_LOG(lsWARN, "fused record merge not used (%s): general device path", why_fixed.c_str());
     }
     const long long nn = std::max<long long>(n, 1);
     const long long merge_scratch = a.merge_scratch_bytes(nn, k), tb_scratch = a.tiebreak_scratch_bytes(nn), scan_scratch = a.scan64_scratch_bytes(nn);
-    if (merge_scratch < 0 || tb_scratch < 0 || scan_scratch < 0) { if (why) *why = "scratch size query failed"; return false; }
+    if (merge_scratch < 0 || tb_scratch < 0 || scan_scratch < 0) { if (why) *why = "scratch size query failed"; *refusal = Refusal::FAILED; return false; }
     const long long need = data_bytes + ro_bytes + 2 * nn * 16 + merge_scratch + tb_scratch + scan_scratch + nn * 4 + (nn + 1) * 8 + out_bytes + 64 +
                            (long long)k * 24 + 4096;
     long long free_b = 0, total_b = 0;
     if (a.mem_info(&free_b, &total_b) != 0 || need > (long long)(0.9 * (double)free_b)) {
         if (why) *why = "partition needs " + std::to_string(need >> 20) + " MiB of device memory, " + std::to_string(free_b >> 20) + " MiB free";
+        *refusal = Refusal::MEMORY;
         return false;
     }
     // Anything that goes wrong before the first block has been handed to the sink (allocation, a copy, a kernel launch, a
@@ -450,6 +467,7 @@ bool DeviceMerge::merge(const std::vector<HostSegment>& segs, KeyKind kind, size
     } catch (const UdaError& e) {
         if (delivered) throw;
         if (why) *why = e.info();
+        *refusal = Refusal::FAILED;
         return false;
     }
     return true;

@@ -51,13 +51,17 @@ public:
     // stream, every block <= max_block bytes and made of whole records (a single larger record travels alone); the
     // last block ends with the EOF marker. Returns false (nothing delivered) when the device cannot take the job:
     // *why says so and the caller merges on the CPU. Throws UdaError on CUDA errors after work has started.
+    // *refusal (optional) tells the caller what kind of "no" it was: a partition that only lacks device memory can be
+    // merged in groups (Consumer::merge_device_grouped), the other refusals go to the CPU merge.
+    enum class Refusal { NONE, UNAVAILABLE, LIMITS, MEMORY, FAILED };
     bool merge(const std::vector<HostSegment>& segs, KeyKind kind, size_t max_block,
-               const std::function<void(const uint8_t*, size_t)>& sink, long long* records_out, std::string* why);
+               const std::function<void(const uint8_t*, size_t)>& sink, long long* records_out, std::string* why,
+               Refusal* refusal = nullptr);
 
 private:
     DeviceMerge();
     bool merge_fixed(const std::vector<HostSegment>& segs, int stride, int key_off, int key_len, long long n, size_t max_block,
-                     const std::function<void(const uint8_t*, size_t)>& sink, std::string* why);
+                     const std::function<void(const uint8_t*, size_t)>& sink, std::string* why, bool* out_of_memory);
     void stream_out(const uint8_t* d_out, const std::vector<unsigned long long>& off, size_t n, size_t max_block,
                     const std::function<void(const uint8_t*, size_t)>& deliver);
     bool ok_ = false;

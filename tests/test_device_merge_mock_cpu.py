@@ -165,6 +165,50 @@ def test_inner_failure_after_the_first_block_fails_the_task(tmp_path):
     assert 0 < len(streams[0]) < 3 * 7000 * 4010                      # some blocks were delivered, not all
 
 
+def _big_parts(n_maps, recs, val, var_len):
+    """Sorted map outputs with random 10-byte keys, generated quickly (os.urandom): ~recs * (len(val) + 14) bytes per map."""
+    parts = []
+    for m in range(n_maps):
+        blob = os.urandom(recs * 10)
+        keys = sorted(blob[i * 10:(i + 1) * 10] for i in range(recs))
+        parts.append([[(k, val[: len(val) - (k[0] % 7 if var_len else 0)]) for k in keys]])
+    return parts
+
+
+@inner
+@pytest.mark.parametrize("var_len", [True, False], ids=["general-path", "fused-path"])
+def test_inner_partition_beyond_device_memory_is_merged_in_groups(tmp_path, var_len):
+    """Free device memory below what the whole partition needs, above what half of it needs: the segments are merged on
+    the device in groups into host runs (the hybrid merge's LPQs with the device as the merger) and a heap merges the
+    runs; with memory for no group at all the CPU merges everything."""
+    import test_runtime_cpu as T
+    parts = _big_parts(8, 12_000, b"v" * 100, var_len)               # 8 x 1.4 MB
+    total = sum(len(k) + len(v) + 2 for p in parts for k, v in p[0])
+    d = tmp_path / "grp"
+    d.mkdir()
+    prebuilt = T._prebuilt_mofs(str(d), parts)
+    # the fused path needs ~2x the data (input + output), the general path ~3x: pick a budget between half and all of it
+    need_all = total * (3.6 if var_len else 2.1)
+    os.environ["UDA_MOCK_FREE_BYTES"] = str(int(need_all * 0.62 / 0.9))
+    try:
+        streams, truth, cons, _ = T._run_job(str(d), 8, 1, 0, approach=3, prebuilt=prebuilt)
+    finally:
+        del os.environ["UDA_MOCK_FREE_BYTES"]
+    _check(T, streams, truth, exact=False)
+    st = cons[0].final_stats
+    assert st["device_groups"] in (2, 4) and st["device_merges"] == st["device_groups"], st
+    assert any("merging in groups" in m for _, m in cons[0].logs) and any("final merge of the" in m for _, m in cons[0].logs)
+    # memory for nothing: every grouping is refused, the CPU merges
+    os.environ["UDA_MOCK_FREE_BYTES"] = "100000"
+    try:
+        streams, truth, cons, _ = T._run_job(str(d), 8, 1, 0, approach=3, prebuilt=prebuilt)
+    finally:
+        del os.environ["UDA_MOCK_FREE_BYTES"]
+    _check(T, streams, truth, exact=False)
+    assert cons[0].final_stats["device_merges"] == 0
+    assert any("no grouping fits either" in m and "merging on the CPU" in m for _, m in cons[0].logs)
+
+
 @inner
 def test_inner_no_device(tmp_path):
     T, (streams, truth, cons, _) = _job(tmp_path, n_maps=4, n_reduces=1, recs=200, approach=3, seed=8)

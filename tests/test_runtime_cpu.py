@@ -222,7 +222,7 @@ def _run_job(tmp, n_maps, n_reduces, recs, approach=1, buf_kb=8, key_class="org.
                 streams.append(cons.stream())
                 continue
             assert not cons.failed and cons.failures == 0, cons.last_error
-            cons.final_stats = {k: cons.stat(k) for k in ("records_emitted", "lpqs_spilled", "device_merges", "device_fused_merges")}
+            cons.final_stats = {k: cons.stat(k) for k in ("records_emitted", "lpqs_spilled", "device_merges", "device_fused_merges", "device_groups")}
             streams.append(cons.stream())
             assert all(len(b) <= max_block for b in cons.blocks)
             assert cons.fetch_over >= 1
