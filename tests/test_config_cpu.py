@@ -122,9 +122,24 @@ def test_log_collector_and_pre_req(tmp_path):
 
 
 def test_job_kwargs_from_config():
+    """Zeros in the uda.b200.* keys resolve to the defaults bench.py measured (docs/TUNING.md)."""
     c = UdaConfig()
-    assert c.terasort_job_kwargs(1) == {"subparts": 1, "push_mode": "lsu", "push_ctas": 0, "merge_ctas_per_sm": 0}
-    assert c.terasort_job_kwargs(2) == {"subparts": 8, "push_mode": "tma", "push_ctas": 32, "merge_ctas_per_sm": 0}
-    assert c.terasort_job_kwargs(8)["subparts"] == 12 and c.terasort_job_kwargs(8)["push_ctas"] == 36
-    c2 = UdaConfig.from_dict({"uda.b200.shuffle.subpartitions": 4, "uda.b200.shuffle.push.ctas": 24})
-    assert c2.terasort_job_kwargs(8) == {"subparts": 4, "push_mode": "tma", "push_ctas": 24, "merge_ctas_per_sm": 0}
+    base = {"merge_ctas_per_sm": 0, "arena_slots": 0, "device_cuts": False, "local_copy": "auto"}
+    assert c.terasort_job_kwargs(1) == {"subparts": 4, "push_mode": "lsu", "push_ctas": 296, **base}
+    assert c.terasort_job_kwargs(2) == {"subparts": 8, "push_mode": "tma", "push_ctas": 32, **base}
+    assert c.terasort_job_kwargs(4) == {"subparts": 12, "push_mode": "tma", "push_ctas": 36, **base}
+    assert c.terasort_job_kwargs(8) == {"subparts": 12, "push_mode": "tma", "push_ctas": 48, **base}
+    c2 = UdaConfig.from_dict({"uda.b200.shuffle.subpartitions": 4, "uda.b200.shuffle.push.ctas": 24, "uda.b200.shuffle.arena.slots": 2,
+                              "uda.b200.shuffle.device.cuts": "true", "uda.b200.shuffle.local.copy": "ce"})
+    assert c2.terasort_job_kwargs(8) == {"subparts": 4, "push_mode": "tma", "push_ctas": 24, "merge_ctas_per_sm": 0, "arena_slots": 2,
+                                         "device_cuts": True, "local_copy": "ce"}
+    # one GPU without pipelining: the push kernel moves everything, then the merge runs
+    assert UdaConfig.from_dict({"uda.b200.shuffle.local.copy": "push"}).terasort_job_kwargs(1)["subparts"] == 1
+    assert UdaConfig.from_dict({"uda.b200.shuffle.subpartitions": 1}).terasort_job_kwargs(1)["push_ctas"] == 0
+    import pytest
+    with pytest.raises(ValueError):
+        c2.terasort_job_kwargs(1)                                   # a receive ring needs the copy-engine push
+    with pytest.raises(ValueError):
+        UdaConfig.from_dict({"uda.b200.shuffle.subpartitions": 4, "uda.b200.shuffle.arena.slots": 5})
+    with pytest.raises(ValueError):
+        UdaConfig.from_dict({"uda.b200.shuffle.local.copy": "dma"})

@@ -43,6 +43,9 @@ _KEYS = {
     "subparts": ("uda.b200.shuffle.subpartitions", int),
     "push_ctas": ("uda.b200.shuffle.push.ctas", int),
     "merge_ctas_per_sm": ("uda.b200.merge.ctas.per.sm", int),
+    "arena_slots": ("uda.b200.shuffle.arena.slots", int),
+    "device_cuts": ("uda.b200.shuffle.device.cuts", bool),
+    "local_copy": ("uda.b200.shuffle.local.copy", str),
     "verify_crc": ("uda.b200.shuffle.verify.crc", bool),
     "wait_max_spins": ("uda.b200.shuffle.wait.max.spins", int),
 }
@@ -91,9 +94,12 @@ class UdaConfig:
     map_output_key_class: str = "org.apache.hadoop.io.Text"
     child_java_opts: str = "-Xmx200m"
     hbm_budget_bytes: int = 0               # 0 -> 80 % of the free HBM at job set-up
-    subparts: int = 0                       # 0 -> 1 on one GPU, 8 on two, 12 on more
-    push_ctas: int = 0                      # 0 -> library default
+    subparts: int = 0                       # 0 -> 4 on one GPU, 8 on two, 12 on more
+    push_ctas: int = 0                      # 0 -> measured default for the GPU count
     merge_ctas_per_sm: int = 0
+    arena_slots: int = 0                    # 0 -> one receive slot per sub-partition; fewer = ring with credits (several GPUs)
+    device_cuts: bool = False               # cut the sub-partitions on the device (map outputs with Hadoop's P partitions)
+    local_copy: str = "auto"                # auto | push | ce: how a rank's own map outputs reach its arena
     verify_crc: bool = False
     wait_max_spins: int = 50_000_000
     extra: Dict[str, str] = field(default_factory=dict)   # keys this object does not know: kept for getConfData
@@ -147,6 +153,10 @@ class UdaConfig:
             raise ValueError("mapred.job.shuffle.input.buffer.percent must be in (0, 1]")
         if self.wqe_per_conn < 2 or not (0 < self.cma_port < 65536):
             raise ValueError("bad mapred.rdma.wqe.per.conn / mapred.rdma.cma.port")
+        if self.local_copy not in ("auto", "push", "ce"):
+            raise ValueError("uda.b200.shuffle.local.copy must be auto, push or ce")
+        if self.arena_slots < 0 or (self.subparts > 0 and self.arena_slots > self.subparts):
+            raise ValueError("uda.b200.shuffle.arena.slots must be between 0 and the number of sub-partitions")
 
     # ---------------------------------------------------------------------------------------- derived values
     def get(self, name: str, default: str = "") -> str:
@@ -202,13 +212,26 @@ class UdaConfig:
 
     def terasort_job_kwargs(self, world: int) -> Dict[str, object]:
         """Keyword arguments for :class:`uda_b200.models.terasort.TeraSortJob` derived from the ``uda.b200.*`` keys:
-        zeros mean "measured default for this many GPUs" (one GPU: load/store push, no pipelining; two: copy-engine
-        push on 32 SMs, 8 sub-partitions; more: 36 SMs, 12 sub-partitions — profiles/pipeline_sweep.md)."""
+        zeros mean "measured default for this many GPUs", the same defaults ``bench.py`` uses (docs/TUNING.md): one GPU
+        load/store push with 4 pipelined sub-partitions and the local segments on the copy engines; two GPUs copy-engine
+        push on 32 SMs, 8 sub-partitions; more 12 sub-partitions on 36 SMs (48 on 8 GPUs)."""
         multi = world > 1
-        subparts = self.subparts if self.subparts > 0 else ((12 if world > 2 else 8) if multi else 1)
-        mode = "tma" if multi and subparts > 1 else "lsu"
-        ctas = self.push_ctas if self.push_ctas > 0 else ((36 if world > 2 else 32) if mode == "tma" else 0)
-        return {"subparts": subparts, "push_mode": mode, "push_ctas": ctas, "merge_ctas_per_sm": self.merge_ctas_per_sm}
+        subparts = self.subparts if self.subparts > 0 else ((12 if world > 2 else 8) if multi else (1 if self.local_copy == "push" else 4))
+        mode = "tma" if multi else "lsu"
+        if self.arena_slots and not multi:
+            raise ValueError("uda.b200.shuffle.arena.slots needs the copy-engine push, which serves several GPUs")
+        if self.arena_slots > subparts:
+            raise ValueError("uda.b200.shuffle.arena.slots exceeds the number of sub-partitions")
+        if self.push_ctas > 0:
+            ctas = self.push_ctas
+        elif subparts <= 1:
+            ctas = 0
+        elif mode == "tma":
+            ctas = 32 if world == 2 else (48 if world >= 8 else 36)
+        else:
+            ctas = 296
+        return {"subparts": subparts, "push_mode": mode, "push_ctas": ctas, "merge_ctas_per_sm": self.merge_ctas_per_sm,
+                "arena_slots": self.arena_slots, "device_cuts": self.device_cuts, "local_copy": self.local_copy}
 
     def replace(self, **kw) -> "UdaConfig":
         c = dataclasses.replace(self, **kw)
