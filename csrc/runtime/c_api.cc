@@ -152,6 +152,8 @@ long long uda_rt_stat(uda_role_t h, const char* what) {
         if (w == "records_emitted") return (long long)r->consumer->records_emitted();
         if (w == "lpqs_spilled") return r->consumer->lpqs_spilled();
         if (w == "device_merges") return r->consumer->device_merges();
+        if (w == "fetch_stall_us") return fetch_stall_us();
+        if (w == "fetch_stalls") return fetch_stalls();
         if (w == "device_groups") return r->consumer->device_groups();   // groups of the last partition that was merged group-wise
         if (w == "device_fused_merges") return DeviceMerge::fused_merges();   // process-wide: merges that took the fused record merge
         if (w == "fetch_ms") return r->consumer->fetch_ms();

@@ -263,6 +263,11 @@ bool codec_decompress(Codec c, const uint8_t* in, size_t in_len, uint8_t* out, s
 }
 
 // ========================================================================================== sources
+// process-wide: time merge threads spent waiting for a chunk that had not landed yet (the prefetch did not hide the fetch)
+static std::atomic<long long> g_fetch_stall_us{0}, g_fetch_stalls{0};
+long long fetch_stall_us() { return g_fetch_stall_us.load(); }
+long long fetch_stalls() { return g_fetch_stalls.load(); }
+
 FetchSource::FetchSource(InputClient* client, BufferPool* pool, std::string host, FetchRequest first, size_t chunk)
     : client_(client), pool_(pool), host_(std::move(host)), req_(std::move(first)), chunk_(chunk) {}
 
@@ -362,7 +367,10 @@ bool FetchSource::next_block(const uint8_t** data, size_t* len) {
         if (state_[next_slot_] == READY) break;
         const bool more = state_[0] == FETCHING || state_[1] == FETCHING;
         if (!more) return false;  // everything fetched and consumed
+        const auto t0 = std::chrono::steady_clock::now();
         cv_.wait(lk);
+        g_fetch_stall_us += std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count();
+        ++g_fetch_stalls;
     }
     const int s = next_slot_;
     state_[s] = BUSY;
@@ -473,15 +481,28 @@ bool Segment::next() {
     }
 }
 
-bool MergeHeap::less(const Segment* a, const Segment* b) const {
-    const Record &x = a->cur(), &y = b->cur();
+uint64_t MergeHeap::prefix_of(const Record& r) const {
+    const uint8_t* body;
+    int n;
+    key_body(kind_, r.key, r.klen, &body, &n);
+    uint64_t v = 0;
+    if (n >= 8) {
+        memcpy(&v, body, 8);
+        return __builtin_bswap64(v);
+    }
+    for (int i = 0; i < n; ++i) v |= (uint64_t)body[i] << (56 - 8 * i);
+    return v;
+}
+bool MergeHeap::less(const Node& a, const Node& b) const {
+    if (a.prefix != b.prefix) return a.prefix < b.prefix;
+    const Record &x = a.seg->cur(), &y = b.seg->cur();
     int c = compare_keys(kind_, x.key, x.klen, y.key, y.klen);
-    return c ? c < 0 : a->id() < b->id();
+    return c ? c < 0 : a.seg->id() < b.seg->id();
 }
 void MergeHeap::sift_up(size_t i) {
     while (i > 0) {
         size_t p = (i - 1) / 2;
-        if (!less(heap_[i].get(), heap_[p].get())) break;
+        if (!less(heap_[i], heap_[p])) break;
         std::swap(heap_[i], heap_[p]);
         i = p;
     }
@@ -490,8 +511,8 @@ void MergeHeap::sift_down(size_t i) {
     const size_t n = heap_.size();
     for (;;) {
         size_t l = 2 * i + 1, r = l + 1, m = i;
-        if (l < n && less(heap_[l].get(), heap_[m].get())) m = l;
-        if (r < n && less(heap_[r].get(), heap_[m].get())) m = r;
+        if (l < n && less(heap_[l], heap_[m])) m = l;
+        if (r < n && less(heap_[r], heap_[m])) m = r;
         if (m == i) return;
         std::swap(heap_[i], heap_[m]);
         i = m;
@@ -499,11 +520,13 @@ void MergeHeap::sift_down(size_t i) {
 }
 void MergeHeap::insert(std::unique_ptr<Segment> s) {
     if (!s->next()) return;  // empty partition: nothing to merge, buffers go back to the pool
-    heap_.push_back(std::move(s));
+    const uint64_t pre = prefix_of(s->cur());
+    heap_.push_back(Node{pre, std::move(s)});
     sift_up(heap_.size() - 1);
 }
 void MergeHeap::advance() {
-    if (heap_.front()->next()) {
+    if (heap_.front().seg->next()) {
+        heap_.front().prefix = prefix_of(heap_.front().seg->cur());
         sift_down(0);
     } else {
         std::swap(heap_.front(), heap_.back());
@@ -607,7 +630,7 @@ void Consumer::on_init(const HadoopCmd& cmd) {
     double ratio = atof(conf_get(host_, "mapred.rdma.compression.buffer.ratio", "0.20").c_str());
     long long cfg_kb = atoll(conf_get(host_, "mapred.rdma.buf.size", "1024").c_str());
     plan_ = plan_memory(init_, num_kv_bufs, codec_, ratio, cfg_kb * 1024);
-    client_ = std::make_unique<TcpInputClient>(opt_.data_port, opt_.wqes_per_conn);
+    client_ = make_input_client(opt_.data_port, opt_.wqes_per_conn);
     client_->start();
     pool_ = std::make_unique<BufferPool>(plan_.pairs, plan_.pair_size[0], plan_.pair_size[1]);
     /* the next line is parsed by the regression's buffer-size checks: keep its wording */

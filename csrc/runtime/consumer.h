@@ -42,6 +42,8 @@ constexpr int kProgressEvery = 20;          // fetchOverMessage cadence (src/Mer
 
 // ---- byte sources -------------------------------------------------------------------------------------
 struct HostSegment;   // device_merge.h
+long long fetch_stall_us();   // process-wide: microseconds merge threads waited for chunks that had not landed yet
+long long fetch_stalls();
 
 class ByteSource {
 public:
@@ -196,15 +198,24 @@ public:
     void insert(std::unique_ptr<Segment> s);   // primes the segment; empty segments are dropped
     bool empty() const { return heap_.empty(); }
     size_t size() const { return heap_.size(); }
-    const Record& top() const { return heap_.front()->cur(); }
+    const Record& top() const { return heap_.front().seg->cur(); }
     void advance();                            // pop-or-sift after the top record has been consumed
 
 private:
-    bool less(const Segment* a, const Segment* b) const;
+    // The first 8 compared key bytes (big-endian, zero padded) ride in the heap array: most comparisons of a sift are
+    // decided by two integers that are already in cache instead of two pointer chases and a memcmp. Equal prefixes fall
+    // through to the exact comparator (a shorter key that is a prefix of a longer one has the smaller or equal padded
+    // prefix, so the integer order never contradicts the comparator's).
+    struct Node {
+        uint64_t prefix;
+        std::unique_ptr<Segment> seg;
+    };
+    uint64_t prefix_of(const Record& r) const;
+    bool less(const Node& a, const Node& b) const;
     void sift_down(size_t i);
     void sift_up(size_t i);
     KeyKind kind_;
-    std::vector<std::unique_ptr<Segment>> heap_;
+    std::vector<Node> heap_;
 };
 
 // ---- the reduce task ----------------------------------------------------------------------------------

@@ -280,4 +280,25 @@ void TcpInputClient::stop() {
     }
 }
 
+// ---- fetcher factory ------------------------------------------------------------------------------------
+namespace {
+std::mutex g_factory_mu;
+InputClientFactory g_factory;
+}  // namespace
+
+void set_input_client_factory(InputClientFactory f) {
+    std::lock_guard<std::mutex> lk(g_factory_mu);
+    g_factory = std::move(f);
+}
+
+std::unique_ptr<InputClient> make_input_client(int port, int wqes_per_conn) {
+    InputClientFactory f;
+    {
+        std::lock_guard<std::mutex> lk(g_factory_mu);
+        f = g_factory;
+    }
+    if (f) return f(port, wqes_per_conn);
+    return std::make_unique<TcpInputClient>(port, wqes_per_conn);
+}
+
 }  // namespace uda

@@ -80,6 +80,13 @@ public:
     virtual void fetch(const std::string& host, FetchRequest req, uint8_t* dest, size_t capacity, Done done) = 0;
 };
 
+// Benchmark / test hook: when set, the consumer obtains its fetcher from this factory instead of creating a
+// TcpInputClient (tests/native/cpu_merge_bench.cc feeds the consumer from memory the way baseline/ref_harness.cc feeds
+// the reference's reducer, so the two CPU mergers can be compared without a network or disks in the way).
+using InputClientFactory = std::function<std::unique_ptr<InputClient>(int port, int wqes_per_conn)>;
+void set_input_client_factory(InputClientFactory f);
+std::unique_ptr<InputClient> make_input_client(int port, int wqes_per_conn);
+
 class TcpInputClient : public InputClient {
 public:
     TcpInputClient(int port, int wqes_per_conn);

@@ -1,0 +1,285 @@
+// The host runtime's own reducer (online / hybrid CPU merge) fed from memory: the counterpart of baseline/ref_harness.cc,
+// which feeds the REFERENCE's reducer the same way. Same record shape (teragen: 10-byte key, 90-byte value, IFile framed),
+// same generator, same "transport" (a copy thread that memcpy's the next chunk into the consumer's buffer and completes the
+// fetch), same timed span (INIT -> last block handed to "Java", a byte counter), so the two CPU mergers can be compared
+// without a network, disks or a JVM in the way:
+//
+//   build/bin/cpu_merge_bench <libuda.so> --maps 8 --records 20000000 --steps 3 --warmup 1 [--approach 1|2] [--check]
+//   baseline/_ref/bin/ref_merger           --maps 8 --records 20000000 --steps 3 --warmup 1 [--check]
+//
+// prints one line:  OURS steps=<k> seconds=<s0,...> bytes=<merged stream bytes per step> blocks=<n> check=<ok|skipped|FAILED>
+// (the first argument is accepted for symmetry with the other native tests; the program links libuda.so)
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include <algorithm>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/uda_rt_api.h"
+#include "../../csrc/runtime/transport.h"
+
+namespace {
+
+constexpr int KEY = 10, VAL = 90, REC = 102;
+std::vector<std::vector<char>> g_maps;
+
+inline uint64_t splitmix(uint64_t& s) {
+    uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+struct KeyIdx {
+    uint64_t hi;
+    uint16_t lo;
+    uint32_t idx;
+    bool operator<(const KeyIdx& o) const { return hi != o.hi ? hi < o.hi : (lo != o.lo ? lo < o.lo : idx < o.idx); }
+};
+void build_map(int m, long long n, uint64_t seed) {   // identical to baseline/ref_harness.cc: both arms merge the same bytes
+    std::vector<KeyIdx> keys((size_t)n);
+    uint64_t s = seed * 0x100000001B3ull + (uint64_t)m * 0x9E3779B1ull + 17;
+    for (long long i = 0; i < n; ++i) {
+        keys[(size_t)i].hi = splitmix(s);
+        keys[(size_t)i].lo = (uint16_t)splitmix(s);
+        keys[(size_t)i].idx = (uint32_t)i;
+    }
+    std::sort(keys.begin(), keys.end());
+    std::vector<char>& seg = g_maps[(size_t)m];
+    seg.resize((size_t)n * REC + 2);
+    char* p = seg.data();
+    for (long long i = 0; i < n; ++i) {
+        const KeyIdx& k = keys[(size_t)i];
+        p[0] = (char)KEY; p[1] = (char)VAL;
+        for (int b = 0; b < 8; ++b) p[2 + b] = (char)(k.hi >> (56 - 8 * b));
+        p[10] = (char)(k.lo >> 8); p[11] = (char)k.lo;
+        uint64_t v = ((uint64_t)m << 40) ^ k.idx ^ seed;
+        for (int b = 0; b < VAL; b += 8) {
+            const uint64_t x = splitmix(v);
+            memcpy(p + 12 + b, &x, (size_t)std::min(8, VAL - b));
+        }
+        p += REC;
+    }
+    p[0] = (char)0xFF; p[1] = (char)0xFF;
+}
+bool g_verbose = false;   // UDA_BENCH_VERBOSE=1: per-step busy time of the copy thread on stderr
+double now_s() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+
+// ---- transport: one copy thread, like the reference harness ------------------------------------------------------
+class MemoryInputClient : public uda::InputClient {
+public:
+    MemoryInputClient() { th_ = std::thread([this] { run(); }); }
+    ~MemoryInputClient() override {
+        stop();
+        if (g_verbose) fprintf(stderr, "copy thread: %.3f s busy in %lld copies\n", copy_busy_, copies_);
+    }
+    void start() override {}
+    void stop() override {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            if (stop_) return;
+            stop_ = true;
+        }
+        cv_.notify_all();
+        if (th_.joinable()) th_.join();
+        for (auto& j : q_) j.done(false, uda::FetchAck());   // fail what was still queued, like a closed connection would
+        q_.clear();
+    }
+    void fetch(const std::string&, uda::FetchRequest req, uint8_t* dest, size_t capacity, Done done) override {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            q_.push_back(Job{std::move(req), dest, capacity, std::move(done)});
+        }
+        cv_.notify_one();
+    }
+
+private:
+    struct Job { uda::FetchRequest req; uint8_t* dest; size_t cap; Done done; };
+    void run() {
+        for (;;) {
+            Job j;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return stop_ || !q_.empty(); });
+                if (stop_) return;
+                j = std::move(q_.front());
+                q_.pop_front();
+            }
+            const int m = atoi(j.req.map_id.c_str());
+            const std::vector<char>& seg = g_maps[(size_t)m];
+            const long long total = (long long)seg.size();
+            long long n = total - j.req.map_offset;
+            if (n > j.req.chunk_size) n = j.req.chunk_size;
+            if (n > (long long)j.cap) n = (long long)j.cap;
+            if (n < 0) n = 0;
+            const double tc = g_verbose ? now_s() : 0;
+            memcpy(j.dest, seg.data() + j.req.map_offset, (size_t)n);
+            if (g_verbose) { copy_busy_ += now_s() - tc; ++copies_; }
+            uda::FetchAck ack;
+            ack.raw_length = total;
+            ack.part_length = total;
+            ack.sent = n;
+            ack.file_offset = 0;
+            ack.path = "mem";
+            j.done(true, ack);
+        }
+    }
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::deque<Job> q_;
+    bool stop_ = false;
+    double copy_busy_ = 0;
+    long long copies_ = 0;
+    std::thread th_;
+};
+
+// ---- "Java" side ---------------------------------------------------------------------------------------------------
+struct Sink {
+    std::mutex mu;
+    std::condition_variable cv;
+    long long bytes = 0, blocks = 0, records = 0;
+    double t_last = 0;
+    bool check = false, check_ok = true, failed = false;
+    std::string prev_key;
+} g_sink;
+long long g_expected = 0;
+
+void on_data(void*, const void* buf, int len) {
+    const char* p = (const char*)buf;
+    if (g_sink.check) {
+        int off = 0;
+        while (off + 2 <= len) {
+            if ((unsigned char)p[off] == 0xFF && (unsigned char)p[off + 1] == 0xFF) break;
+            if (p[off] != KEY || p[off + 1] != VAL || off + REC > len) { g_sink.check_ok = false; break; }
+            std::string k(p + off + 2, KEY);
+            if (!g_sink.prev_key.empty() && k < g_sink.prev_key) g_sink.check_ok = false;
+            g_sink.prev_key.swap(k);
+            ++g_sink.records;
+            off += REC;
+        }
+    }
+    std::lock_guard<std::mutex> lk(g_sink.mu);
+    g_sink.bytes += len;
+    ++g_sink.blocks;
+    g_sink.t_last = now_s();
+    if (g_sink.bytes >= g_expected) g_sink.cv.notify_all();
+}
+void on_failure(void*) {
+    std::lock_guard<std::mutex> lk(g_sink.mu);
+    g_sink.failed = true;
+    g_sink.cv.notify_all();
+}
+int on_conf(void*, const char*, const char*, char*, int) { return 0; }
+
+struct StepResult { double seconds; long long bytes, blocks, records; int check_ok; };
+
+bool run_reduce_task(int maps, int approach, bool check, StepResult* out) {
+    g_sink.bytes = g_sink.blocks = g_sink.records = 0;
+    g_sink.t_last = 0;
+    g_sink.check_ok = true;
+    g_sink.failed = false;
+    g_sink.prev_key.clear();
+    g_sink.check = check;
+    uda_host_callbacks_t cb;
+    memset(&cb, 0, sizeof(cb));
+    cb.data_from_uda = on_data;
+    cb.failure_in_uda = on_failure;
+    cb.get_conf_data = on_conf;
+    const double t0 = now_s();
+    const std::string a = std::to_string(approach);
+    const char* argv[] = {"-w", "256", "-r", "9011", "-a", a.c_str(), "-m", "1", "-g", "/tmp/", "-s", "1024"};
+    uda_role_t h = uda_rt_start(1, (int)(sizeof(argv) / sizeof(argv[0])), argv, 0 /* logging off */, 0, &cb);
+    if (!h) return false;
+    char init[512];
+    const long long shuffle_mem = (long long)maps * 2 * (1 << 20) + (64LL << 20);
+    snprintf(init, sizeof(init), "13:7:%d:job_ref_0001:attempt_ref_0001_r_000000_0:0:%d:%d:org.apache.hadoop.io.ByteWritable:null:0:%lld:1:/tmp",
+             maps, 1 << 20, 16 << 10, shuffle_mem);
+    bool ok = uda_rt_do_command(h, init) == 0;
+    for (int m = 0; ok && m < maps; ++m) {
+        char fetch[256];
+        snprintf(fetch, sizeof(fetch), "5:4:localhost:job_ref_0001:%d:0", m);
+        ok = uda_rt_do_command(h, fetch) == 0;
+    }
+    if (ok) {
+        std::unique_lock<std::mutex> lk(g_sink.mu);
+        g_sink.cv.wait(lk, [] { return g_sink.failed || g_sink.bytes >= g_expected; });
+        ok = !g_sink.failed;
+    }
+    out->seconds = g_sink.t_last - t0;
+    out->bytes = g_sink.bytes;
+    out->blocks = g_sink.blocks;
+    out->records = g_sink.records;
+    out->check_ok = g_sink.check_ok ? 1 : 0;
+    if (!ok) fprintf(stderr, "reduce task failed: %s\n", uda_rt_last_error(h));
+    if (g_verbose) fprintf(stderr, "merge thread: %lld stalls, %.3f s waiting for chunks (cumulative)\n", uda_rt_stat(h, "fetch_stalls"),
+                           1e-6 * (double)uda_rt_stat(h, "fetch_stall_us"));
+    uda_rt_reduce_exit(h);   // outside the timed span, like the JVM's exit
+    uda_rt_destroy(h);
+    return ok;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+    int maps = 8, steps = 3, warmup = 1, approach = 1;
+    long long records = 2000000;
+    uint64_t seed = 1234;
+    double budget_s = 600;
+    bool check = false;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        auto val = [&]() -> const char* { return i + 1 < argc ? argv[++i] : "0"; };
+        if (a == "--maps") maps = atoi(val());
+        else if (a == "--records") records = atoll(val());
+        else if (a == "--steps") steps = atoi(val());
+        else if (a == "--warmup") warmup = atoi(val());
+        else if (a == "--seed") seed = strtoull(val(), nullptr, 10);
+        else if (a == "--approach") approach = atoi(val());
+        else if (a == "--budget-s") budget_s = atof(val());
+        else if (a == "--check") check = true;
+    }
+    if (maps < 1 || records < 1 || (approach != 1 && approach != 2)) { fprintf(stderr, "bad arguments\n"); return 2; }
+    g_verbose = getenv("UDA_BENCH_VERBOSE") != nullptr;
+    const double t_begin = now_s();
+    g_maps.resize((size_t)maps);
+    {
+        // `records` is the total of the reduce task (what bench.py calls records per GPU), spread over the maps
+        std::vector<std::thread> th;
+        for (int m = 0; m < maps; ++m) {
+            const long long n = records / maps + (m < records % maps ? 1 : 0);
+            th.emplace_back([=] { build_map(m, n, seed); });
+        }
+        for (auto& t : th) t.join();
+    }
+    g_expected = records * REC + 2;
+    uda::set_input_client_factory([](int, int) { return std::unique_ptr<uda::InputClient>(new MemoryInputClient()); });
+    std::vector<double> secs;
+    long long bytes = 0, blocks = 0;
+    bool all_ok = true, checked = false;
+    double per_step = 0;
+    for (int s = 0; s < warmup + steps; ++s) {
+        if (s > 0 && per_step > 0 && (now_s() - t_begin) + per_step > budget_s) break;
+        StepResult r;
+        if (!run_reduce_task(maps, approach, check && s == 0, &r)) { all_ok = false; break; }
+        per_step = r.seconds;
+        if (check && s == 0) { checked = true; all_ok = all_ok && r.check_ok && r.records == records; }
+        if (s >= warmup) secs.push_back(r.seconds);
+        bytes = r.bytes;
+        blocks = r.blocks;
+    }
+    printf("OURS steps=%zu seconds=", secs.size());
+    for (size_t i = 0; i < secs.size(); ++i) printf("%s%.6f", i ? "," : "", secs[i]);
+    printf(" bytes=%lld blocks=%lld check=%s\n", bytes, blocks, !all_ok ? "FAILED" : (checked ? "ok" : "skipped"));
+    return all_ok ? 0 : 1;
+}

@@ -438,6 +438,25 @@ def test_reader_bench_selftest(built):
     assert p.stdout.count("BW:") == 3 and "checksums agree" in p.stdout
 
 
+@pytest.mark.parametrize("approach,maps", [(1, 8), (2, 16)])
+def test_cpu_merge_bench_memory_fed_reducer(built, approach, maps):
+    """The host runtime's reducer fed from memory through the fetcher factory hook (tests/native/cpu_merge_bench.cc, the
+    counterpart of baseline/ref_harness.cc): the merged stream is complete, ordered, and every record is delivered."""
+    import subprocess
+    from pathlib import Path
+    rt = os.environ.get("UDA_B200_RUNTIME_LIB")
+    exe = (Path(rt).parent if rt else Path(__file__).resolve().parent.parent / "build" / "bin") / "cpu_merge_bench"
+    if not exe.exists():
+        pytest.skip(f"{exe} not built")
+    p = subprocess.run([str(exe), "libuda.so", "--maps", str(maps), "--records", "300000", "--steps", "2", "--warmup", "1", "--approach", str(approach),
+                        "--check"], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    line = next(l for l in p.stdout.splitlines() if l.startswith("OURS "))
+    kv = dict(x.split("=", 1) for x in line.split()[1:])
+    assert kv["steps"] == "2" and kv["check"] == "ok" and int(kv["bytes"]) == 300000 * 102 + 2
+    assert all(float(x) > 0 for x in kv["seconds"].split(","))
+
+
 def test_regression_driver_parses_matrix(tmp_path):
     """The single-node regression driver reads its matrix and produces a report without executing anything."""
     import json, subprocess, sys
