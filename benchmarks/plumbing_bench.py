@@ -91,7 +91,7 @@ def main() -> int:
             while c.stat("records_emitted") < want[r] and not c.failed and time.perf_counter() - t0 < 600:
                 time.sleep(0.005)
             ok = ok and not c.failed and c.stat("records_emitted") == want[r]
-        phase = [{k: c.stat(k) for k in ("device_merges", "fetch_ms", "device_ms")} for c in cons]
+        phase = [{k: c.stat(k) for k in ("device_merges", "fetch_ms", "device_ms", "fetch_stalls", "fetch_stall_us")} for c in cons]
         dt = time.perf_counter() - t0
         # validation: order inside every reducer's stream + byte count (TeraValidate-style, done after the clock stops)
         out_bytes = 0

@@ -7,6 +7,11 @@
 //   build/bin/cpu_merge_bench <libuda.so> --maps 8 --records 20000000 --steps 3 --warmup 1 [--approach 1|2] [--check]
 //   baseline/_ref/bin/ref_merger           --maps 8 --records 20000000 --steps 3 --warmup 1 [--check]
 //
+//   build/bin/cpu_merge_bench <libuda.so> --tcp --maps 4 --reducers 2 --records 10000000    (BASELINE config 1, native)
+//     the map outputs are written as Hadoop file.out files, a provider role of this process serves them over TCP
+//     loop-back (index look-up, chunk pool, disk reader, fetch protocol with credits) and --reducers consumer roles
+//     fetch and merge them at the same time; --records is the total over all reducers
+//
 // prints one line:  OURS steps=<k> seconds=<s0,...> bytes=<merged stream bytes per step> blocks=<n> check=<ok|skipped|FAILED>
 // (the first argument is accepted for symmetry with the other native tests; the program links libuda.so)
 #include <stdint.h>
@@ -148,14 +153,24 @@ private:
 struct Sink {
     std::mutex mu;
     std::condition_variable cv;
-    long long bytes = 0, blocks = 0, records = 0;
+    long long bytes = 0, blocks = 0, records = 0, expected = 0;
     double t_last = 0;
     bool check = false, check_ok = true, failed = false;
     std::string prev_key;
-} g_sink;
-long long g_expected = 0;
+    void reset(bool chk, long long expect) {
+        bytes = blocks = records = 0;
+        expected = expect;
+        t_last = 0;
+        check = chk;
+        check_ok = true;
+        failed = false;
+        prev_key.clear();
+    }
+};
+std::deque<Sink> g_sinks;   // one per reducer (a deque: Sink is not movable)
 
-void on_data(void*, const void* buf, int len) {
+void on_data(void* user, const void* buf, int len) {
+    Sink& g_sink = *(Sink*)user;
     const char* p = (const char*)buf;
     if (g_sink.check) {
         int off = 0;
@@ -173,9 +188,10 @@ void on_data(void*, const void* buf, int len) {
     g_sink.bytes += len;
     ++g_sink.blocks;
     g_sink.t_last = now_s();
-    if (g_sink.bytes >= g_expected) g_sink.cv.notify_all();
+    if (g_sink.bytes >= g_sink.expected) g_sink.cv.notify_all();
 }
-void on_failure(void*) {
+void on_failure(void* user) {
+    Sink& g_sink = *(Sink*)user;
     std::lock_guard<std::mutex> lk(g_sink.mu);
     g_sink.failed = true;
     g_sink.cv.notify_all();
@@ -184,48 +200,99 @@ int on_conf(void*, const char*, const char*, char*, int) { return 0; }
 
 struct StepResult { double seconds; long long bytes, blocks, records; int check_ok; };
 
-bool run_reduce_task(int maps, int approach, bool check, StepResult* out) {
-    g_sink.bytes = g_sink.blocks = g_sink.records = 0;
-    g_sink.t_last = 0;
-    g_sink.check_ok = true;
-    g_sink.failed = false;
-    g_sink.prev_key.clear();
-    g_sink.check = check;
+// ---- file-backed map outputs for the --tcp mode -------------------------------------------------------------------------
+struct MofIndex { long long start, raw, part; };
+std::vector<std::string> g_mof_path;                 // per map
+std::vector<std::vector<MofIndex>> g_mof_index;      // [map][reducer]
+int g_reducers = 1;
+
+// segment (map m, reducer r) lives in g_maps[m * g_reducers + r]; file.out = the map's segments, each followed by 4 checksum bytes
+bool write_mofs(const std::string& dir, int maps) {
+    g_mof_path.assign((size_t)maps, "");
+    g_mof_index.assign((size_t)maps, std::vector<MofIndex>((size_t)g_reducers));
+    for (int m = 0; m < maps; ++m) {
+        g_mof_path[(size_t)m] = dir + "/map_" + std::to_string(m) + ".out";
+        FILE* f = fopen(g_mof_path[(size_t)m].c_str(), "wb");
+        if (!f) return false;
+        long long pos = 0;
+        for (int r = 0; r < g_reducers; ++r) {
+            const std::vector<char>& seg = g_maps[(size_t)(m * g_reducers + r)];
+            const char crc[4] = {0, 0, 0, 0};
+            if (fwrite(seg.data(), 1, seg.size(), f) != seg.size() || fwrite(crc, 1, 4, f) != 4) { fclose(f); return false; }
+            g_mof_index[(size_t)m][(size_t)r] = MofIndex{pos, (long long)seg.size(), (long long)seg.size() + 4};
+            pos += (long long)seg.size() + 4;
+        }
+        fclose(f);
+    }
+    return true;
+}
+int on_path(void*, const char*, const char* map, int reduce, long long* start, long long* raw, long long* part, char* path_out, int cap) {
+    const int m = atoi(map);
+    if (m < 0 || m >= (int)g_mof_path.size() || reduce < 0 || reduce >= g_reducers) return 0;
+    const MofIndex& ix = g_mof_index[(size_t)m][(size_t)reduce];
+    *start = ix.start; *raw = ix.raw; *part = ix.part;
+    snprintf(path_out, (size_t)cap, "%s", g_mof_path[(size_t)m].c_str());
+    return 1;
+}
+
+// One job: every reducer's consumer role is started, initialised and told about every map; the span runs from the first
+// INIT to the last block of the slowest reducer. `port` > 0: fetch over TCP from the provider role listening there.
+bool run_job(int maps, int approach, bool check, int port, StepResult* out) {
+    const int R = g_reducers;
     uda_host_callbacks_t cb;
     memset(&cb, 0, sizeof(cb));
     cb.data_from_uda = on_data;
     cb.failure_in_uda = on_failure;
     cb.get_conf_data = on_conf;
     const double t0 = now_s();
-    const std::string a = std::to_string(approach);
-    const char* argv[] = {"-w", "256", "-r", "9011", "-a", a.c_str(), "-m", "1", "-g", "/tmp/", "-s", "1024"};
-    uda_role_t h = uda_rt_start(1, (int)(sizeof(argv) / sizeof(argv[0])), argv, 0 /* logging off */, 0, &cb);
-    if (!h) return false;
-    char init[512];
-    const long long shuffle_mem = (long long)maps * 2 * (1 << 20) + (64LL << 20);
-    snprintf(init, sizeof(init), "13:7:%d:job_ref_0001:attempt_ref_0001_r_000000_0:0:%d:%d:org.apache.hadoop.io.ByteWritable:null:0:%lld:1:/tmp",
-             maps, 1 << 20, 16 << 10, shuffle_mem);
-    bool ok = uda_rt_do_command(h, init) == 0;
-    for (int m = 0; ok && m < maps; ++m) {
-        char fetch[256];
-        snprintf(fetch, sizeof(fetch), "5:4:localhost:job_ref_0001:%d:0", m);
-        ok = uda_rt_do_command(h, fetch) == 0;
+    const std::string a = std::to_string(approach), prt = std::to_string(port > 0 ? port : 9011);
+    const char* argv[] = {"-w", "256", "-r", prt.c_str(), "-a", a.c_str(), "-m", "1", "-g", "/tmp/", "-s", "1024"};
+    std::vector<uda_role_t> roles;
+    bool ok = true;
+    for (int r = 0; r < R && ok; ++r) {
+        long long expect = 2;
+        for (int m = 0; m < maps; ++m) expect += (long long)g_maps[(size_t)(m * R + r)].size() - 2;
+        g_sinks[(size_t)r].reset(check, expect);
+        cb.user = &g_sinks[(size_t)r];
+        uda_role_t h = uda_rt_start(1, (int)(sizeof(argv) / sizeof(argv[0])), argv, 0 /* logging off */, 0, &cb);
+        if (!h) { ok = false; break; }
+        roles.push_back(h);
+        char init[512];
+        const long long shuffle_mem = (long long)maps * 2 * (1 << 20) + (64LL << 20);
+        snprintf(init, sizeof(init), "13:7:%d:job_ref_0001:attempt_ref_0001_r_%06d_0:0:%d:%d:org.apache.hadoop.io.ByteWritable:null:0:%lld:1:/tmp",
+                 maps, r, 1 << 20, 16 << 10, shuffle_mem);
+        ok = uda_rt_do_command(h, init) == 0;
+        for (int m = 0; ok && m < maps; ++m) {
+            char fetch[256];
+            // memory-fed: the map id is the segment index; over TCP the provider resolves (map, reduce) through on_path
+            snprintf(fetch, sizeof(fetch), "5:4:127.0.0.1:job_ref_0001:%d:%d", port > 0 ? m : m * R + r, r);
+            ok = uda_rt_do_command(h, fetch) == 0;
+        }
     }
-    if (ok) {
-        std::unique_lock<std::mutex> lk(g_sink.mu);
-        g_sink.cv.wait(lk, [] { return g_sink.failed || g_sink.bytes >= g_expected; });
-        ok = !g_sink.failed;
+    out->seconds = 0;
+    out->bytes = out->blocks = out->records = 0;
+    out->check_ok = 1;
+    for (size_t r = 0; r < roles.size(); ++r) {
+        Sink& sk = g_sinks[r];
+        if (ok) {
+            std::unique_lock<std::mutex> lk(sk.mu);
+            sk.cv.wait(lk, [&] { return sk.failed || sk.bytes >= sk.expected; });
+            ok = !sk.failed;
+        }
+        out->seconds = std::max(out->seconds, sk.t_last - t0);
+        out->bytes += sk.bytes;
+        out->blocks += sk.blocks;
+        out->records += sk.records;
+        out->check_ok = out->check_ok && sk.check_ok;
+        if (!ok) fprintf(stderr, "reduce task %zu failed: %s\n", r, uda_rt_last_error(roles[r]));
     }
-    out->seconds = g_sink.t_last - t0;
-    out->bytes = g_sink.bytes;
-    out->blocks = g_sink.blocks;
-    out->records = g_sink.records;
-    out->check_ok = g_sink.check_ok ? 1 : 0;
-    if (!ok) fprintf(stderr, "reduce task failed: %s\n", uda_rt_last_error(h));
-    if (g_verbose) fprintf(stderr, "merge thread: %lld stalls, %.3f s waiting for chunks (cumulative)\n", uda_rt_stat(h, "fetch_stalls"),
-                           1e-6 * (double)uda_rt_stat(h, "fetch_stall_us"));
-    uda_rt_reduce_exit(h);   // outside the timed span, like the JVM's exit
-    uda_rt_destroy(h);
+    if (g_verbose && !roles.empty())
+        fprintf(stderr, "merge threads: %lld stalls, %.3f s waiting for chunks (cumulative)\n", uda_rt_stat(roles[0], "fetch_stalls"),
+                1e-6 * (double)uda_rt_stat(roles[0], "fetch_stall_us"));
+    for (uda_role_t h : roles) {   // outside the timed span, like the JVM's exit
+        uda_rt_reduce_exit(h);
+        uda_rt_destroy(h);
+    }
     return ok;
 }
 
@@ -236,11 +303,12 @@ int main(int argc, char** argv) {
     long long records = 2000000;
     uint64_t seed = 1234;
     double budget_s = 600;
-    bool check = false;
+    bool check = false, tcp = false;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
         auto val = [&]() -> const char* { return i + 1 < argc ? argv[++i] : "0"; };
         if (a == "--maps") maps = atoi(val());
+        else if (a == "--reducers") g_reducers = atoi(val());
         else if (a == "--records") records = atoll(val());
         else if (a == "--steps") steps = atoi(val());
         else if (a == "--warmup") warmup = atoi(val());
@@ -248,22 +316,43 @@ int main(int argc, char** argv) {
         else if (a == "--approach") approach = atoi(val());
         else if (a == "--budget-s") budget_s = atof(val());
         else if (a == "--check") check = true;
+        else if (a == "--tcp") tcp = true;
     }
-    if (maps < 1 || records < 1 || (approach != 1 && approach != 2)) { fprintf(stderr, "bad arguments\n"); return 2; }
+    if (maps < 1 || records < 1 || g_reducers < 1 || (approach != 1 && approach != 2)) { fprintf(stderr, "bad arguments\n"); return 2; }
     g_verbose = getenv("UDA_BENCH_VERBOSE") != nullptr;
     const double t_begin = now_s();
-    g_maps.resize((size_t)maps);
+    const int R = g_reducers, nseg = maps * R;
+    g_maps.resize((size_t)nseg);
+    g_sinks.resize((size_t)R);
     {
-        // `records` is the total of the reduce task (what bench.py calls records per GPU), spread over the maps
+        // `records` is the total of the job (what bench.py calls records per GPU for one reducer), spread over maps x reducers
         std::vector<std::thread> th;
-        for (int m = 0; m < maps; ++m) {
-            const long long n = records / maps + (m < records % maps ? 1 : 0);
-            th.emplace_back([=] { build_map(m, n, seed); });
+        for (int sgi = 0; sgi < nseg; ++sgi) {
+            const long long n = records / nseg + (sgi < records % nseg ? 1 : 0);
+            th.emplace_back([=] { build_map(sgi, n, seed); });
+            if (th.size() == 16) { for (auto& t : th) t.join(); th.clear(); }
         }
         for (auto& t : th) t.join();
     }
-    g_expected = records * REC + 2;
-    uda::set_input_client_factory([](int, int) { return std::unique_ptr<uda::InputClient>(new MemoryInputClient()); });
+    uda_role_t provider = nullptr;
+    int port = 0;
+    char tmpl[] = "/tmp/uda_cpu_merge_bench_XXXXXX";
+    std::string dir;
+    if (tcp) {
+        if (!mkdtemp(tmpl)) { perror("mkdtemp"); return 1; }
+        dir = tmpl;
+        if (!write_mofs(dir, maps)) { fprintf(stderr, "cannot write the map outputs under %s\n", dir.c_str()); return 1; }
+        uda_host_callbacks_t pcb;
+        memset(&pcb, 0, sizeof(pcb));
+        pcb.get_path_uda = on_path;
+        pcb.get_conf_data = on_conf;
+        const char* pargv[] = {"-w", "256", "-r", "0", "-m", "1", "-g", "/tmp/", "-s", "1024"};
+        provider = uda_rt_start(0, (int)(sizeof(pargv) / sizeof(pargv[0])), pargv, 0, 0, &pcb);
+        port = provider ? uda_rt_port(provider) : 0;
+        if (port <= 0) { fprintf(stderr, "the provider role did not start\n"); return 1; }
+    } else {
+        uda::set_input_client_factory([](int, int) { return std::unique_ptr<uda::InputClient>(new MemoryInputClient()); });
+    }
     std::vector<double> secs;
     long long bytes = 0, blocks = 0;
     bool all_ok = true, checked = false;
@@ -271,12 +360,18 @@ int main(int argc, char** argv) {
     for (int s = 0; s < warmup + steps; ++s) {
         if (s > 0 && per_step > 0 && (now_s() - t_begin) + per_step > budget_s) break;
         StepResult r;
-        if (!run_reduce_task(maps, approach, check && s == 0, &r)) { all_ok = false; break; }
+        if (!run_job(maps, approach, check && s == 0, port, &r)) { all_ok = false; break; }
         per_step = r.seconds;
         if (check && s == 0) { checked = true; all_ok = all_ok && r.check_ok && r.records == records; }
         if (s >= warmup) secs.push_back(r.seconds);
         bytes = r.bytes;
         blocks = r.blocks;
+    }
+    if (provider) {
+        uda_rt_do_command(provider, "");   // the empty command is EXIT
+        uda_rt_destroy(provider);
+        for (const auto& p : g_mof_path) remove(p.c_str());
+        remove(dir.c_str());
     }
     printf("OURS steps=%zu seconds=", secs.size());
     for (size_t i = 0; i < secs.size(); ++i) printf("%s%.6f", i ? "," : "", secs[i]);

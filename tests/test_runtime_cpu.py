@@ -438,6 +438,22 @@ def test_reader_bench_selftest(built):
     assert p.stdout.count("BW:") == 3 and "checksums agree" in p.stdout
 
 
+def test_cpu_merge_bench_native_plumbing_over_tcp(built):
+    """BASELINE config 1 without Python in the loop: a provider role serving file.out files over TCP loop-back and two
+    consumer roles merging at the same time, all inside tests/native/cpu_merge_bench."""
+    import subprocess
+    from pathlib import Path
+    rt = os.environ.get("UDA_B200_RUNTIME_LIB")
+    exe = (Path(rt).parent if rt else Path(__file__).resolve().parent.parent / "build" / "bin") / "cpu_merge_bench"
+    if not exe.exists():
+        pytest.skip(f"{exe} not built")
+    p = subprocess.run([str(exe), "libuda.so", "--tcp", "--maps", "4", "--reducers", "2", "--records", "400000", "--steps", "2", "--warmup", "1",
+                        "--check"], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    kv = dict(x.split("=", 1) for x in next(l for l in p.stdout.splitlines() if l.startswith("OURS ")).split()[1:])
+    assert kv["steps"] == "2" and kv["check"] == "ok" and int(kv["bytes"]) == 400000 * 102 + 2 * 2
+
+
 @pytest.mark.parametrize("approach,maps", [(1, 8), (2, 16)])
 def test_cpu_merge_bench_memory_fed_reducer(built, approach, maps):
     """The host runtime's reducer fed from memory through the fetcher factory hook (tests/native/cpu_merge_bench.cc, the
