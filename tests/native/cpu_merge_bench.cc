@@ -4,7 +4,8 @@
 // fetch), same timed span (INIT -> last block handed to "Java", a byte counter), so the two CPU mergers can be compared
 // without a network, disks or a JVM in the way:
 //
-//   build/bin/cpu_merge_bench <libuda.so> --maps 8 --records 20000000 --steps 3 --warmup 1 [--approach 1|2] [--check]
+//   build/bin/cpu_merge_bench <libuda.so> --maps 8 --records 20000000 --steps 3 --warmup 1 [--approach 1|2|3] [--check]
+//     (approach 3 = the device merge: needs a GPU, or UDA_KERNELS_LIB pointing at the host-only mock)
 //   baseline/_ref/bin/ref_merger           --maps 8 --records 20000000 --steps 3 --warmup 1 [--check]
 //
 //   build/bin/cpu_merge_bench <libuda.so> --tcp --maps 4 --reducers 2 --records 10000000    (BASELINE config 1, native)
@@ -318,7 +319,7 @@ int main(int argc, char** argv) {
         else if (a == "--check") check = true;
         else if (a == "--tcp") tcp = true;
     }
-    if (maps < 1 || records < 1 || g_reducers < 1 || (approach != 1 && approach != 2)) { fprintf(stderr, "bad arguments\n"); return 2; }
+    if (maps < 1 || records < 1 || g_reducers < 1 || (approach < 1 || approach > 3)) { fprintf(stderr, "bad arguments\n"); return 2; }
     g_verbose = getenv("UDA_BENCH_VERBOSE") != nullptr;
     const double t_begin = now_s();
     const int R = g_reducers, nseg = maps * R;
