@@ -15,6 +15,7 @@
 //   UDA_MOCK_NO_FUSED=1           uda_merge_records_supported answers no (forces the general path)
 //   UDA_MOCK_FAIL_MALLOC_AT=K     the K-th device allocation of the process fails (1-based)
 //   UDA_MOCK_FAIL_D2H_AT=K        the K-th device-to-host copy of the process fails (1-based)
+//   UDA_MOCK_FAIL_FN=name         the named kernel entry point (e.g. uda_tiebreak_var) returns an error instead of running
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -32,6 +33,11 @@ long long env_ll(const char* name, long long dflt) {
     return v && *v ? atoll(v) : dflt;
 }
 std::atomic<long long> g_mallocs{0}, g_d2h{0}, g_live{0};
+bool fails(const char* fn) {
+    const char* v = getenv("UDA_MOCK_FAIL_FN");
+    return v && strcmp(v, fn) == 0;
+}
+#define MOCK_FAIL_POINT() do { if (fails(__func__)) return 700; } while (0)
 
 // Hadoop VInt (csrc/runtime/vint.h restated: the mock must not link the library under test)
 int vint_decode(const uint8_t* p, int64_t* out) {
@@ -114,6 +120,7 @@ const char* uda_error_string(int rc) {
 // ---- general path -------------------------------------------------------------------------------------------------
 int uda_extract_keys_var(const void* data, const long long* rec_off, long long n, int key_kind, unsigned run_id, unsigned idx0, void* entries_out,
                          unsigned* long_key_flag, cudaStream_t) {
+    MOCK_FAIL_POINT();
     if (key_kind < 0 || key_kind > 2 || run_id > 0xFFFFu) return UDA_E_INVALID;
     UdaEntry* e = (UdaEntry*)entries_out;
     for (long long i = 0; i < n; ++i) {
@@ -130,6 +137,7 @@ int uda_extract_keys_var(const void* data, const long long* rec_off, long long n
 }
 long long uda_merge_scratch_bytes(long long n, int nruns) { return n < 0 || nruns < 0 ? UDA_E_INVALID : 256; }
 int uda_kway_merge_entries(const void* entries, const long long* run_off, int nruns, long long n, void* sorted_out, void*, cudaStream_t) {
+    MOCK_FAIL_POINT();
     if (nruns > 4096) return UDA_E_TOO_LARGE;
     const UdaEntry* e = (const UdaEntry*)entries;
     for (int r = 0; r < nruns; ++r)   // the contract: every run is sorted already
@@ -143,6 +151,7 @@ int uda_kway_merge_entries(const void* entries, const long long* run_off, int nr
 long long uda_tiebreak_scratch_bytes(long long n) { return n < 0 ? UDA_E_INVALID : 256; }
 int uda_tiebreak_var(void* sorted_entries, long long n, const unsigned long long* run_base, const unsigned long long* run_recoff, int key_kind,
                      void*, void*, cudaStream_t) {
+    MOCK_FAIL_POINT();
     UdaEntry* e = (UdaEntry*)sorted_entries;
     auto rec = [&](const UdaEntry& x) {
         const unsigned r = run_of(x);
@@ -163,6 +172,7 @@ int uda_tiebreak_var(void* sorted_entries, long long n, const unsigned long long
     return 0;
 }
 int uda_gather_var_lengths(const void* sorted_entries, long long n, const unsigned long long* run_recoff, unsigned* rec_len_out, cudaStream_t) {
+    MOCK_FAIL_POINT();
     const UdaEntry* e = (const UdaEntry*)sorted_entries;
     for (long long i = 0; i < n; ++i) {
         const long long* ro = (const long long*)(uintptr_t)run_recoff[run_of(e[i])];
@@ -172,6 +182,7 @@ int uda_gather_var_lengths(const void* sorted_entries, long long n, const unsign
 }
 long long uda_scan_u32_to_u64_scratch_bytes(long long m) { return m < 0 ? UDA_E_INVALID : 256; }
 int uda_scan_u32_to_u64(const unsigned* v, long long m, unsigned long long* out, void*, cudaStream_t) {
+    MOCK_FAIL_POINT();
     unsigned long long run = 0;
     for (long long i = 0; i < m; ++i) { out[i] = run; run += v[i]; }
     out[m] = run;   // m + 1 outputs: the total closes the table
@@ -179,6 +190,7 @@ int uda_scan_u32_to_u64(const unsigned* v, long long m, unsigned long long* out,
 }
 int uda_gather_var(const void* sorted_entries, long long n, const unsigned long long* run_base, const unsigned long long* run_recoff,
                    const unsigned long long* dst_off, void* dst, cudaStream_t) {
+    MOCK_FAIL_POINT();
     const UdaEntry* e = (const UdaEntry*)sorted_entries;
     for (long long i = 0; i < n; ++i) {
         const unsigned r = run_of(e[i]);
@@ -189,6 +201,7 @@ int uda_gather_var(const void* sorted_entries, long long n, const unsigned long 
     return 0;
 }
 int uda_write_eof_at(void* dst, const unsigned long long* total, cudaStream_t) {
+    MOCK_FAIL_POINT();
     uint8_t* p = (uint8_t*)dst + (total ? *total : 0);
     p[0] = 0xFF; p[1] = 0xFF;
     return 0;
@@ -202,6 +215,7 @@ int uda_merge_records_supported(int nruns, long long n, int stride, int key_len)
 long long uda_merge_records_scratch_bytes(long long n, int nruns) { return n < 0 || nruns < 1 ? UDA_E_INVALID : 256; }
 int uda_merge_records_fixed(const UdaRunDesc* runs, int nruns, long long n, long long max_nrec, int stride, int key_off, int key_len, int align2,
                             void* out, int write_eof, void*, int ctas_per_sm, cudaStream_t) {
+    MOCK_FAIL_POINT();
     if (!uda_merge_records_supported(nruns, n, stride, key_len) && !env_ll("UDA_MOCK_NO_FUSED", 0)) return UDA_E_INVALID;
     if (align2 && ((stride | key_off) & 1)) return UDA_E_INVALID;
     if (ctas_per_sm < 0 || ctas_per_sm > 32) return UDA_E_INVALID;

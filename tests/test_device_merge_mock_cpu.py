@@ -137,6 +137,29 @@ def test_inner_failures_before_the_first_block_fall_back_to_the_cpu_merge(tmp_pa
         assert mock.uda_mock_live_allocations() == 0                  # nothing leaks on the failure path
 
 
+@inner
+def test_inner_kernel_errors_before_delivery(tmp_path):
+    """A kernel entry point that reports an error: in the general path the whole device merge is abandoned for the CPU merge
+    (nothing was delivered yet); a failing fused merge only demotes the partition to the general device path."""
+    for fn in ("uda_extract_keys_var", "uda_tiebreak_var", "uda_gather_var"):
+        os.environ["UDA_MOCK_FAIL_FN"] = fn
+        try:
+            T, (streams, truth, cons, _) = _job(tmp_path / fn, n_maps=4, n_reduces=1, recs=300, approach=3, key_len=24, seed=9)
+        finally:
+            del os.environ["UDA_MOCK_FAIL_FN"]
+        _check(T, streams, truth)
+        assert cons[0].final_stats["device_merges"] == 0
+        assert any("device merge not possible" in m and fn in m for _, m in cons[0].logs), [m for _, m in cons[0].logs][-4:]
+    os.environ["UDA_MOCK_FAIL_FN"] = "uda_merge_records_fixed"
+    try:
+        T, (streams, truth, cons, _) = _job(tmp_path / "fused", n_maps=4, n_reduces=1, recs=500, approach=3, key_len=10, val_len=20, seed=2)
+    finally:
+        del os.environ["UDA_MOCK_FAIL_FN"]
+    _check(T, streams, truth, exact=False)
+    assert cons[0].final_stats["device_merges"] == 1
+    assert any("fused record merge not used" in m for _, m in cons[0].logs)
+
+
 def _allocations_so_far(mock):
     import ctypes as C
     mock.uda_mock_allocation_count.restype = C.c_longlong
