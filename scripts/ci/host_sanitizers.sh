@@ -14,6 +14,8 @@ tmp="$(mktemp -d)"
 trap 'rm -rf "$tmp"' EXIT
 # the test program dlopens the library it is given: the sanitizer runtime must come first in the process
 "build/$kind/test_jni_mock" "build/$kind/libuda.so" "$tmp"
+# the same flow with the JNI consumer on merge approach 3, against the host-only mock of the kernel library
+UDA_KERNELS_LIB="$root/build/$kind/libuda_kernels_mock.so" "build/$kind/test_jni_mock" "build/$kind/libuda.so" "$tmp" 3
 if [ "$kind" = "address" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
     # the whole CPU suite of the runtime (plumbing over TCP, hybrid merge, Snappy / LZO segments, approach 3 fallback)
     # against the instrumented library: the sanitizer runtime and libstdc++ are preloaded into the Python process

@@ -340,7 +340,11 @@ int main(int argc, char** argv) {
     ports = std::to_string(uda_rt_port(prov));
     g_stream.clear();
     g_fetch_over = 0;
-    CHECK(start(env, cls, 1, J(jarray_of({"-w", "256", "-r", ports, "-a", "1", "-m", "1", "-g", "/tmp/", "-s", "16"})), 4, 0) == 0);
+    // (optional third program argument: the merge approach of this consumer; "3" = device merge, which the test driver
+    //  runs against the host-only mock of the kernel library: blocks then come out of the pinned delivery windows at
+    //  arbitrary offsets, every one through a direct buffer of exactly its length)
+    const std::string approach = argc >= 4 ? argv[3] : "1";
+    CHECK(start(env, cls, 1, J(jarray_of({"-w", "256", "-r", ports, "-a", approach, "-m", "1", "-g", "/tmp/", "-s", "16"})), 4, 0) == 0);
     docmd(env, cls, J(mk(Obj::STRING, "12:7:2:job_1:attempt_r_0:0:16384:4096:org.apache.hadoop.io.LongWritable:null:0:67108864:0")));
     docmd(env, cls, J(mk(Obj::STRING, "5:4:127.0.0.1:job_1:attempt_m_0:0")));
     docmd(env, cls, J(mk(Obj::STRING, "5:4:127.0.0.1:job_1:attempt_m_1:0")));
@@ -351,6 +355,7 @@ int main(int argc, char** argv) {
     { std::lock_guard<std::mutex> lk(g_mu); CHECK(g_stream == expect); }
     CHECK(g_fetch_over >= 1 && g_failures == 0);
     CHECK(g_direct_buffers >= 1 && g_buffer_cap_ok);  // one buffer per delivered block, capacity == delivered length
+    if (approach == "3") CHECK(has_log("device merge of 2 segments"));   // the device path really served this stream
     rexit(env, cls);
 
     // 5. consumer whose provider is gone: the merge thread's failure arrives as failureInUda()
