@@ -3,7 +3,7 @@
 # this file only gives the usual verbs.
 PY ?= python
 
-.PHONY: all native java test test-gpu bench sass sanitize asan tsan analyze coverage wheel rpm deb install reference clean
+.PHONY: all native java test test-gpu bench cpu-bench ci sass sanitize asan tsan analyze coverage wheel rpm deb install reference clean
 
 all: native
 
@@ -47,6 +47,17 @@ coverage:
 # the reference arm of bench.py: the reference's own reducer sources compiled unmodified (needs /root/reference or a copy)
 reference:
 	$(PY) baseline/build_ref.py
+
+# the CPU mergers side by side, both fed from memory (this runtime's reducer and the reference's own), then BASELINE config 1
+# natively (provider role over TCP loop-back, two reducers)
+cpu-bench: native reference
+	build/bin/cpu_merge_bench x --maps 8 --records 20000000 --steps 3 --warmup 1 --check
+	baseline/_ref/bin/ref_merger --maps 8 --records 20000000 --steps 3 --warmup 1 --check
+	build/bin/cpu_merge_bench x --tcp --maps 4 --reducers 2 --records 10000000 --steps 3 --warmup 1 --check
+
+# one full CI pass (scripts/ci/build.sh): build, CPU suite, sanitizers, coverage, static analysis, reference arm, regression
+ci:
+	scripts/ci/build.sh
 
 wheel: native
 	$(PY) -m pip wheel --no-deps --no-build-isolation -w dist .
