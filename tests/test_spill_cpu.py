@@ -89,3 +89,38 @@ def test_split_range_sub_slices():
     got = [k for t in tasks for k in sorted(k for g, a, b in t for k in _keys(groups[g], a, b))]
     assert got == sorted(k for g, a, b in window for k in _keys(groups[g], a, b))
     assert all(sum(b - a for _, a, b in t) <= 37 for t in tasks)
+
+
+def test_split_range_property():
+    """Random group counts, sizes, duplicate densities and capacities: every record exactly once, every part within the
+    capacity, parts in key order."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=60, deadline=None)
+    @given(seed=st.integers(0, 10**6), ngroups=st.integers(1, 6), cap=st.integers(1, 400), alphabet=st.integers(1, 40))
+    def run(seed, ngroups, cap, alphabet):
+        rng = random.Random(seed)
+        sizes = [rng.randint(0, 300) for _ in range(ngroups)]
+        pool = [bytes(rng.randrange(256) for _ in range(KLEN)) for _ in range(alphabet)]     # few distinct keys: heavy duplicates
+        groups = []
+        for n in sizes:
+            keys = sorted(rng.choice(pool) for _ in range(n))
+            buf = np.zeros(n * S, dtype=np.uint8)
+            for i, k in enumerate(keys):
+                buf[i * S + KOFF:i * S + KOFF + KLEN] = np.frombuffer(k, dtype=np.uint8)
+            groups.append(buf)
+        tasks = split_range(groups, [(g, 0, n) for g, n in enumerate(sizes)], S, KOFF, KLEN, cap)
+        nxt = [0] * ngroups
+        prev_max = None
+        for t in tasks:
+            assert t and sum(b - a for _, a, b in t) <= cap
+            ks = []
+            for g, a, b in t:
+                assert a == nxt[g] and b > a
+                nxt[g] = b
+                ks += _keys(groups[g], a, b)
+            assert prev_max is None or min(ks) >= prev_max
+            prev_max = max(ks)
+        assert nxt == sizes
+
+    run()
