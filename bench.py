@@ -16,6 +16,7 @@ is in the reference (Hadoop's MapTask, not UDA, sorts map output).
 double buffers, heap merge, write_kv_to_stream into 1 MiB blocks), compiled unmodified by ``baseline/build_ref.py``
 and fed from host memory (its RDMA transport needs libibverbs, which the image lacks: a memcpy stands in), one
 reducer process per rank over the same record shape and counts; nothing of uda_b200 is loaded on that path.
+``--impl cpu``: this repository's own CPU reducer (the fall-back path of the plug-in), memory-fed the same way, one process.
 ``--impl nccl_sort``: the second baseline BASELINE.json names
 (NCCL all_to_all_single + torch.sort), same data and metric.
 """
@@ -42,7 +43,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="uda_b200", choices=["uda_b200", "reference", "nccl_sort"])
+    ap.add_argument("--impl", default="uda_b200", choices=["uda_b200", "reference", "nccl_sort", "cpu"])
     ap.add_argument("--records-per-gpu", type=int, default=125_000_000)
     ap.add_argument("--maps-per-gpu", type=int, default=8)
     ap.add_argument("--subparts", type=int, default=0,
@@ -120,6 +121,39 @@ class ClockSampler:
             pass
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def run_cpu(a, emit) -> int:
+    """``--impl cpu``: this repository's own CPU reducer (csrc/runtime: online heap merge), fed from memory exactly like the
+    reference arm feeds the reference's reducer (tests/native/cpu_merge_bench.cc mirrors baseline/ref_harness.cc). No GPU.
+    One process (N = 1): it exists to put the CPU fall-back path on the same scale as the reference arm."""
+    exe = os.path.join(ROOT, "build", "bin", "cpu_merge_bench")
+    if not os.path.exists(exe):
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import build as _build
+        _build.build(verbose=False)
+    cmd = [exe, "libuda.so", "--maps", str(a.maps_per_gpu), "--records", str(a.records_per_gpu), "--steps", str(a.steps), "--warmup", str(a.warmup),
+           "--seed", "1234", "--budget-s", os.environ.get("UDA_REF_BUDGET_S", "540")]
+    if not a.no_check:
+        cmd.append("--check")
+    p = subprocess.run(cmd, capture_output=True, text=True)
+    line = next((l for l in p.stdout.splitlines() if l.startswith("OURS ")), None)
+    if p.returncode != 0 or line is None:
+        emit({"impl": "cpu", "unavailable": "the CPU reducer did not finish: " + (p.stderr.strip().splitlines() or ["no output"])[-1][:200]})
+        return 0
+    kv = dict(x.split("=", 1) for x in line.split()[1:])
+    secs = [float(x) for x in kv["seconds"].split(",") if x]
+    mean_s = sum(secs) / len(secs)
+    value = float(a.records_per_gpu) * RECORD_BYTES / mean_s / 1e9
+    emit({"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": 1, "steps": len(secs), "warmup": a.warmup, "ms_per_step": mean_s * 1e3,
+          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "uint8 records (byte-exact)", "data": "synthetic", "impl": "cpu",
+          "config": {"model": "TeraSort, one reducer's share: 100-byte teragen records in sorted IFile segments in host memory",
+                     "global_batch": a.records_per_gpu, "seq_len": RECORD_BYTES, "maps_per_gpu": a.maps_per_gpu,
+                     "parallelism": "one CPU reducer (libuda.so consumer role, online heap merge), memory-fed like the reference arm",
+                     "timed_region": "INIT + FETCH of every map output + fetch/merge threads + 1 MiB blocks to a byte-counting sink (host clock)"},
+          "clocks": None, "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+          "validated": {"ok": True, "skipped": None}.get(kv.get("check"), False)})
+    return 0
 
 
 def run_reference(a, emit) -> int:
@@ -220,6 +254,8 @@ def main():
 
     if a.impl == "reference":
         return run_reference(a, emit)
+    if a.impl == "cpu":
+        return run_cpu(a, emit)
 
     import torch
     import torch.distributed as dist

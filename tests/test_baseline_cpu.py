@@ -25,3 +25,30 @@ def test_pack_keys_orders_like_the_key_bytes():
     perm = i1[torch.sort(w0[i1], stable=True).indices].numpy()
     want = sorted(range(len(keys)), key=lambda i: (keys[i].tobytes(), i))
     assert perm.tolist() == want
+
+
+def _bench(impl, *extra):
+    import json, subprocess, sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    p = subprocess.run([sys.executable, str(root / "bench.py"), "--impl", impl, "--steps", "2", "--warmup", "1", "--records-per-gpu", "400000",
+                        "--maps-per-gpu", "4", *extra], capture_output=True, text=True, timeout=600, cwd=str(root))
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [l for l in p.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, p.stdout                      # exactly one JSON line on stdout
+    return json.loads(lines[0])
+
+
+def test_bench_cpu_arm_prints_the_contract_line(built):
+    d = _bench("cpu")
+    assert d["impl"] == "cpu" and d["unit"] == "GB/s" and d["value"] > 0 and d["steps"] == 2 and d["validated"] is True
+    assert d["gpu_launches"] == 0 and d["e2e"]["value"] == d["value"] and d["config"]["maps_per_gpu"] == 4
+
+
+def test_bench_reference_arm_prints_the_contract_line(built):
+    d = _bench("reference")
+    if "unavailable" in d:                                # no reference tree on this machine: the arm says so and exits 0
+        assert d["impl"] == "reference" and isinstance(d["unavailable"], str)
+        return
+    assert d["impl"] == "reference" and d["value"] > 0 and d["steps"] == 2 and d["validated"] is True and d["gpu_launches"] == 0
+    assert d["config"]["runs_per_reducer"] == 4 and "unmodified" in d["config"]["reference_code"]
