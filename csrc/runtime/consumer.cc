@@ -306,7 +306,14 @@ void FetchSource::send(int slot, const FetchRequest& r) {
             const int other = slot ^ 1;
             {
                 std::lock_guard<std::mutex> lk(mu_);
-                if (!ok || ack.path == kPathTooLong || ack.path == kFetchRejected) {
+                // whatever transport delivered it, an ack is only believed when its numbers are possible: a chunk fits its
+                // buffer, lengths are not negative, the partition does not shrink below what has been fetched
+                const bool sane = ack.sent >= 0 && (size_t)ack.sent <= pair_.size[slot] && ack.part_length >= 0 && ack.raw_length >= 0 &&
+                                  fetched_ + ack.sent <= ack.part_length;
+                if (ok && !sane && ack.path != kPathTooLong && ack.path != kFetchRejected)
+                    UDA_LOG(lsERROR, "impossible fetch ack for map %s: sent=%lld part=%lld raw=%lld after %lld bytes", req_.map_id.c_str(), ack.sent,
+                            ack.part_length, ack.raw_length, fetched_);
+                if (!ok || !sane || ack.path == kPathTooLong || ack.path == kFetchRejected) {
                     if (ok && ack.path == kPathTooLong) UDA_LOG(lsERROR, "Mof path is too long, UDA supports path of max %zu chars", kMaxMofPath);
                     else if (ok) UDA_LOG(lsERROR, "the provider rejected the fetch of map %s", req_.map_id.c_str());
                     failed_ = true;

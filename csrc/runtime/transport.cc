@@ -248,6 +248,11 @@ void TcpInputClient::read_loop(std::shared_ptr<Peer> p) {
         if (known) {
             FetchAck ack;
             bool parsed = parse_fetch_ack(text, &ack);
+            // the ack text comes off a socket too: what it claims to have sent must be what actually followed it
+            if (parsed && ok && ack.sent != (long long)h.payload_len) {
+                UDA_LOG(lsERROR, "fetch ack claims %lld bytes, the frame carried %llu", ack.sent, (unsigned long long)h.payload_len);
+                parsed = false;
+            }
             pend.done(ok && parsed, ack);
         }
         if (!ok) break;

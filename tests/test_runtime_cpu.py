@@ -258,6 +258,74 @@ def test_plumbing_blocked_reader_backend(built, tmp_path, threads_per_disk):
     assert any("reader=blocked" in m for _, m in prov.logs)
 
 
+@pytest.mark.parametrize("lie", ["sent-larger-than-payload", "partition-shrinks", "negative-length", "chunk-larger-than-buffer"])
+def test_consumer_rejects_impossible_fetch_acks(built, lie):
+    """The other direction of the hostile-request test: a provider (or anything else on that port) whose acks cannot be
+    true must fail the fetch -- and through it the task, which falls back to the vanilla shuffle -- not make the reducer
+    parse bytes that never arrived."""
+    import socket
+    import threading
+
+    srv = socket.socket()
+    srv.bind(("127.0.0.1", 0))
+    srv.listen(4)
+    port = srv.getsockname()[1]
+    rec = ifile.encode_record(b"k" * 10, b"v" * 30)
+
+    def serve():
+        try:
+            conn, _ = srv.accept()
+        except OSError:
+            return
+        with conn:
+            try:
+                while True:
+                    hdr = b""
+                    while len(hdr) < 24:
+                        c = conn.recv(24 - len(hdr))
+                        if not c:
+                            return
+                        hdr += c
+                    _t, _c, _p, tot, _cookie, _pl = struct.unpack("<BBHIQQ", hdr)
+                    text = b""
+                    while len(text) < tot:
+                        text += conn.recv(tot - len(text))
+                    cookie = int(text.decode().split(":")[5])
+                    payload = rec * 3
+                    raw = part = len(payload) + 2
+                    sent = len(payload)
+                    if lie == "sent-larger-than-payload":
+                        sent = 500_000
+                    elif lie == "partition-shrinks":
+                        raw = part = 10
+                    elif lie == "negative-length":
+                        raw = -5
+                    elif lie == "chunk-larger-than-buffer":
+                        payload = rec * 2000                  # 88 KB into the 8 KiB buffers this consumer asked to fill
+                        sent, raw, part = len(payload), len(payload) + 2, len(payload) + 2
+                    ack = f"{raw}:{part}:{sent}:0:/some/file.out:".encode()
+                    conn.sendall(struct.pack("<BBHIQQ", 0x10, 1, 0, len(ack), cookie, len(payload)) + ack + payload)
+            except (OSError, ValueError, IndexError):
+                return
+
+    t = threading.Thread(target=serve, daemon=True)
+    t.start()
+    cons = bridge.NativeRole(True, bridge.build_argv(port=port, approach=1, buf_kb=8))
+    try:
+        init = ["1", "job_1", "attempt_r_000000_0", "0", str(8 * 1024), "4096", "org.apache.hadoop.io.LongWritable", "null", "0", str(1 << 20), "1", "/tmp"]
+        assert cons.command(bridge.form_cmd(bridge.INIT, init)) == 0, cons.last_error
+        assert cons.command(bridge.form_cmd(bridge.FETCH, ["127.0.0.1", "job_1", "attempt_m_000000_0", "0"])) == 0
+        deadline = time.time() + 30
+        while time.time() < deadline and not cons.failed:
+            time.sleep(0.02)
+        assert cons.failed and cons.failures >= 1
+        assert cons.stream() == b"" or not cons.stream().endswith(b"\xff\xff")      # no complete stream was fabricated
+    finally:
+        srv.close()
+        cons.reduce_exit()
+        cons.close()
+
+
 def test_log_to_unique_file_writes_the_provider_log(built, tmp_path):
     """mapred.uda.log.to.unique.file = true: the native side logs to <log dir>/hadoop-<user>-udaMOFSupplier-<host>.log
     instead of the host's logger (reference: src/CommUtils/IOUtility.cc log_to_unique_file, build/README 'log files')."""
