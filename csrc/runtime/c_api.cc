@@ -308,6 +308,50 @@ int uda_rt_plan_memory(int num_maps, long long max_buf, long long min_buf, long 
     }
 }
 
+// Test hook: `n` bytes handed to the record parser of the merge (Segment) as one map-output segment arriving in blocks of
+// `chunk` bytes, every block in a heap buffer of exactly its size (a read past a block is visible to a sanitizer). Returns the
+// number of records before the EOF marker, or -1 when the parser rejects the stream. *digest = order-sensitive FNV-1a hash
+// over (key length, value length, key bytes, value bytes) of every record, for comparison with an independent parser.
+long long uda_rt_selftest_parse_segment(const unsigned char* data, long long n, int chunk, unsigned long long* digest) {
+    class Chunked : public ByteSource {
+    public:
+        Chunked(const uint8_t* p, size_t n, size_t c) : p_(p), n_(n), c_(c ? c : 1) {}
+        bool next_block(const uint8_t** d, size_t* len) override {
+            if (off_ >= n_) return false;
+            const size_t take = std::min(c_, n_ - off_);
+            block_.reset(new uint8_t[take]);          // the previous block dies here, like a recycled fetch buffer
+            memcpy(block_.get(), p_ + off_, take);
+            off_ += take;
+            *d = block_.get();
+            *len = take;
+            return true;
+        }
+    private:
+        const uint8_t* p_;
+        size_t n_, c_, off_ = 0;
+        std::unique_ptr<uint8_t[]> block_;
+    };
+    if (n < 0 || chunk < 1) return -1;
+    unsigned long long h = 1469598103934665603ull;
+    auto mix = [&](const uint8_t* b, size_t len) { for (size_t i = 0; i < len; ++i) { h ^= b[i]; h *= 1099511628211ull; } };
+    long long records = 0;
+    try {
+        Segment seg(std::make_unique<Chunked>(data, (size_t)n, (size_t)chunk), 0);
+        while (seg.next()) {
+            const Record& r = seg.cur();
+            const uint32_t lens[2] = {(uint32_t)r.klen, (uint32_t)r.vlen};
+            mix((const uint8_t*)lens, sizeof(lens));
+            mix(r.key, (size_t)r.klen);
+            mix(r.val, (size_t)r.vlen);
+            ++records;
+        }
+    } catch (const UdaError&) {
+        return -1;
+    }
+    if (digest) *digest = h;
+    return records;
+}
+
 // Exercises the three queues with real threads; returns 0 when all invariants held.
 int uda_rt_selftest_queues(void) {
     ConcurrentQueue<int> q;

@@ -63,6 +63,8 @@ int uda_rt_lzo1x_decompress_lanes(const unsigned char* in, long long n, unsigned
 int uda_rt_plan_memory(int num_maps, long long max_buf, long long min_buf, long long shuffle_mem, int compressed,
                        double ratio, long long* out4);
 int uda_rt_selftest_queues(void);
+/* test hook: the merge's record parser over a segment arriving in blocks of `chunk` bytes; records before the EOF marker or -1 */
+long long uda_rt_selftest_parse_segment(const unsigned char* data, long long n, int chunk, unsigned long long* digest);
 /* thread wrapper (exception -> one failure up-call) and Fisher-Yates fetch-order helpers; 0 = all invariants held */
 int uda_rt_selftest_threads(unsigned long long seed, int n, int* perm_out);
 

@@ -10,7 +10,11 @@ from hypothesis import strategies as st
 
 from uda_b200 import bridge
 
-FUZZ = settings(max_examples=300, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+import os
+
+# UDA_FUZZ_EXAMPLES=20000 turns the quick pass into a long session (run against the ASAN build: scripts/ci/host_sanitizers.sh)
+FUZZ = settings(max_examples=int(os.environ.get("UDA_FUZZ_EXAMPLES", "300")), deadline=None,
+                suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
 
 
 @pytest.fixture(scope="module")
@@ -92,3 +96,59 @@ def test_vint_decoder_bounds(L, data):
     got = C.c_longlong()
     r = L.uda_rt_vint_decode(buf, n, C.byref(got))
     assert 0 <= r <= max(n, 0) and r <= 9
+
+
+# ---------------------------------------------------------------------------------------- the merge's record parser
+def _fnv_records(recs):
+    import struct
+    h = 1469598103934665603
+    for k, v in recs:
+        for b in struct.pack("<II", len(k), len(v)) + k + v:
+            h = ((h ^ b) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def _parse_segment(L, data: bytes, chunk: int):
+    L.uda_rt_selftest_parse_segment.restype = C.c_longlong
+    buf, n = _exact(data)
+    digest = C.c_ulonglong(0)
+    rc = L.uda_rt_selftest_parse_segment(buf, C.c_longlong(n), C.c_int(chunk), C.byref(digest))
+    return rc, digest.value
+
+
+@FUZZ
+@given(recs=st.lists(st.tuples(st.binary(max_size=40), st.binary(max_size=300)), max_size=30), chunk=st.integers(1, 400),
+       big=st.booleans())
+def test_segment_parser_is_independent_of_the_block_size(L, recs, chunk, big):
+    """Records straddling block boundaries anywhere (inside a VInt, a key, a value) parse to the same records."""
+    from uda_b200.utils import ifile
+    if big and recs:
+        recs = recs + [(recs[0][0], recs[0][1] * 40)]             # one record much larger than a block
+    data = ifile.encode_segment(recs, with_crc=False)
+    rc, digest = _parse_segment(L, data, chunk)
+    assert rc == len(recs) and digest == _fnv_records(recs)
+    rc2, digest2 = _parse_segment(L, data + b"\\0\\0\\0\\0", max(1, chunk // 2))     # trailing checksum bytes are ignored
+    assert rc2 == len(recs) and digest2 == digest
+
+
+@FUZZ
+@given(data=st.binary(max_size=500), chunk=st.integers(1, 64))
+def test_segment_parser_never_crashes_on_garbage(L, data, chunk):
+    rc, _ = _parse_segment(L, data, chunk)
+    assert rc >= -1
+
+
+@FUZZ
+@given(seed=st.integers(0, 10**6), flips=st.integers(1, 5), chunk=st.integers(1, 128))
+def test_segment_parser_on_mutated_segments(L, seed, flips, chunk):
+    from uda_b200.utils import ifile
+    rng = random.Random(seed)
+    recs = [(bytes(rng.randrange(256) for _ in range(rng.randint(0, 20))), bytes(rng.randrange(256) for _ in range(rng.randint(0, 200))))
+            for _ in range(rng.randint(0, 20))]
+    data = bytearray(ifile.encode_segment(recs, with_crc=False))
+    for _ in range(flips):
+        data[rng.randrange(len(data))] ^= 1 << rng.randrange(8)
+    cut = rng.randint(0, len(data))
+    for s in (bytes(data), bytes(data[:cut])):
+        rc, _ = _parse_segment(L, s, chunk)
+        assert rc >= -1
