@@ -436,6 +436,10 @@ bool FileSource::next_block(const uint8_t** data, size_t* len) {
 }
 
 // ========================================================================================== records
+// Hadoop serialises key and value lengths as ints: a longer length in a header is corruption (or an attack), and the
+// arithmetic below (header + key + value as one size) must never see two lengths whose sum wraps.
+static constexpr int64_t kMaxRecordPart = 0x7FFFFFFF;
+
 bool Segment::next() {
     if (done_) return false;
     for (;;) {
@@ -445,7 +449,7 @@ bool Segment::next() {
             int n2 = n1 ? vint_decode(p_ + n1, end_, &vl) : 0;
             if (n1 && n2) {
                 if (kl == -1 && vl == -1) { done_ = true; return false; }
-                if (kl < 0 || vl < 0) throw UdaError("corrupt IFile record header");
+                if (kl < 0 || vl < 0 || kl > kMaxRecordPart || vl > kMaxRecordPart) throw UdaError("corrupt IFile record header");
                 const size_t total = (size_t)n1 + n2 + (size_t)kl + (size_t)vl;
                 if ((size_t)(end_ - p_) >= total) {
                     rec_.key = p_ + n1 + n2; rec_.klen = (int)kl;
@@ -463,9 +467,14 @@ bool Segment::next() {
             const uint8_t* d;
             size_t len;
             if (!src_->next_block(&d, &len)) {
-                if (carry_.empty()) { done_ = true; return false; }
+                // every segment, fetched or spilled, closes with the EOF marker: a stream that just stops -- even at a
+                // record boundary -- has lost its tail, and delivering the shorter stream would lose records silently
+                // (a partition of zero bytes -- an index record with partLength 0 -- is simply empty)
+                if (carry_.empty() && !seen_bytes_) { done_ = true; return false; }
+                if (carry_.empty()) throw UdaError("segment ended without its EOF marker");
                 throw UdaError("segment ended inside a record");
             }
+            seen_bytes_ = seen_bytes_ || len > 0;
             if (carry_.empty()) { p_ = d; end_ = d + len; break; }
             SplitCursor c{carry_.data(), carry_.size(), d, len};
             int64_t kl = 0, vl = 0;
@@ -473,7 +482,7 @@ bool Segment::next() {
             int n2 = n1 ? c.read_vint(&vl) : 0;
             if (!n1 || !n2) { carry_.insert(carry_.end(), d, d + len); continue; }
             if (kl == -1 && vl == -1) { done_ = true; return false; }
-            if (kl < 0 || vl < 0) throw UdaError("corrupt IFile record header");
+            if (kl < 0 || vl < 0 || kl > kMaxRecordPart || vl > kMaxRecordPart) throw UdaError("corrupt IFile record header");
             const size_t total = (size_t)n1 + n2 + (size_t)kl + (size_t)vl;
             if (carry_.size() + len < total) { carry_.insert(carry_.end(), d, d + len); continue; }
             const size_t take = total > carry_.size() ? total - carry_.size() : 0;

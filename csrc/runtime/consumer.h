@@ -189,6 +189,7 @@ private:
     std::vector<uint8_t> carry_;
     Record rec_;
     bool done_ = false;
+    bool seen_bytes_ = false;   // any byte of this segment was ever received
 };
 
 // Binary min-heap of segments ordered by (current key, segment id)

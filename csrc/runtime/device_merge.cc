@@ -23,7 +23,9 @@ void index_segment(HostSegment* seg) {
         if (!n1 || !n2) throw UdaError("segment ended without EOF marker");
         seg->rec_off.push_back((long long)(p - base));
         if (kl == -1 && vl == -1) return;   // the entry just pushed is the EOF marker position
-        if (kl < 0 || vl < 0 || p + n1 + n2 + kl + vl > end) throw UdaError("corrupt record header in a fetched segment");
+        // lengths first (Hadoop's are ints), then the bound as a length comparison: a pointer sum could wrap
+        if (kl < 0 || vl < 0 || kl > 0x7FFFFFFF || vl > 0x7FFFFFFF || (int64_t)(end - p) - n1 - n2 < kl + vl)
+            throw UdaError("corrupt record header in a fetched segment");
         p += n1 + n2 + kl + vl;
     }
 }

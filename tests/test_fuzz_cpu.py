@@ -152,3 +152,20 @@ def test_segment_parser_on_mutated_segments(L, seed, flips, chunk):
     for s in (bytes(data), bytes(data[:cut])):
         rc, _ = _parse_segment(L, s, chunk)
         assert rc >= -1
+
+
+def test_segment_parser_rejects_lengths_no_record_can_have(L):
+    """A header whose key or value length exceeds an int (Hadoop's own limit), chosen so that naive size arithmetic wraps:
+    rejected, never turned into a negative length or a small wrapped total. A segment that stops without its EOF marker,
+    even at a record boundary, is rejected too (silently delivering the shorter stream would lose records)."""
+    from uda_b200.utils import ifile, vint
+    good = ifile.encode_segment([(b"k1", b"v1"), (b"k2", b"v2")], with_crc=False)
+    assert _parse_segment(L, good, 3)[0] == 2
+    for kl, vl in ((2**63 - 1, 2**63 - 1), (2**62, 5), (5, 2**31), (2**32 + 2, 2), (2**64 - 2**32 - 0 if False else 2**40, 2**40)):
+        bad = ifile.encode_record(b"k1", b"v1") + vint.encode_vlong(kl) + vint.encode_vlong(vl) + b"xxxxxxxx" + ifile.EOF_MARKER
+        for chunk in (1, 7, 4096):
+            assert _parse_segment(L, bad, chunk)[0] == -1, (kl, vl, chunk)
+    assert _parse_segment(L, good[:-2], 4096)[0] == -1            # both records intact, EOF marker missing
+    assert _parse_segment(L, good[:-1], 4096)[0] == -1            # half an EOF marker
+    assert _parse_segment(L, b"", 16)[0] == 0                     # a partition of zero bytes is empty, not truncated
+    assert _parse_segment(L, ifile.EOF_MARKER, 1)[0] == 0         # an empty partition is just the marker
