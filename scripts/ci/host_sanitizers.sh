@@ -42,4 +42,17 @@ if [ "$kind" = "thread" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
     fi
     grep -q " passed" "$log" && ! grep -q " failed" "$log" || { tail -30 "$log"; exit 1; }
 fi
+if [ "$kind" = "undefined" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
+    # parsers, decoders and the plumbing under UBSAN (signed overflow, misaligned access, bad shifts in the hand-written codecs)
+    ub_lib="$(/usr/bin/g++ -print-file-name=libubsan.so)"
+    stdcpp="$(/usr/bin/g++ -print-file-name=libstdc++.so.6)"
+    UDA_B200_SKIP_BUILD=1 UDA_B200_RUNTIME_LIB="$root/build/undefined/libuda.so" LD_PRELOAD="$ub_lib $stdcpp" \
+        UBSAN_OPTIONS="halt_on_error=0:print_stacktrace=1:log_path=$tmp/ubsan" \
+        python -m pytest tests/test_fuzz_cpu.py tests/test_runtime_cpu.py -x -q -p no:cacheprovider \
+        -k "not reader_bench and not regression_driver and not cpu_merge_bench" | tail -1
+    if ls "$tmp"/ubsan.* > /dev/null 2>&1; then
+        grep -h "runtime error" "$tmp"/ubsan.* | sort | uniq -c | head -20
+        exit 1
+    fi
+fi
 echo "host sanitizer run ($kind): ok"
