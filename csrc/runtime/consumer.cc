@@ -454,6 +454,7 @@ bool Segment::next() {
                 if ((size_t)(end_ - p_) >= total) {
                     rec_.key = p_ + n1 + n2; rec_.klen = (int)kl;
                     rec_.val = rec_.key + kl; rec_.vlen = (int)vl;
+                    rec_.raw = p_; rec_.size = total;
                     p_ += total;
                     return true;
                 }
@@ -492,6 +493,7 @@ bool Segment::next() {
             const uint8_t* b = carry_.data();
             rec_.key = b + n1 + n2; rec_.klen = (int)kl;
             rec_.val = rec_.key + kl; rec_.vlen = (int)vl;
+            rec_.raw = b; rec_.size = total;
             return true;
         }
     }
@@ -727,33 +729,28 @@ void Consumer::fetching_phase(MergeHeap* heap, int count, int* progress) {
 void Consumer::merging_phase(MergeHeap* heap, const std::function<void(const uint8_t*, size_t)>& sink, bool final_stream) {
     int cur = 0;
     size_t used = 0;
+    uint64_t pending = 0;   // records in the open block: the shared counter moves once per block, not once per record
     auto flush = [&] {
+        if (final_stream && pending) emitted_ += pending;  // spill passes of the hybrid merge are not deliveries
+        pending = 0;
         if (used) sink(staging_[cur].data(), used);
         cur ^= 1;
         used = 0;
+        if (stop_) throw UdaError("stopped while merging");
     };
     while (!heap->empty()) {
-        if (stop_) throw UdaError("stopped while merging");
         const Record& r = heap->top();
-        const size_t need = (size_t)vint_size(r.klen) + vint_size(r.vlen) + r.klen + r.vlen;
-        if (need > kStagingBytes) {  // a single record larger than a block travels alone
+        const size_t need = r.size;   // the record as it lies in its source: header + key + value, one copy
+        if (need > kStagingBytes) {   // a single record larger than a block travels alone, straight from where it lies
             flush();
-            std::vector<uint8_t> big(need);
-            size_t o = vint_encode(big.data(), r.klen);
-            o += vint_encode(big.data() + o, r.vlen);
-            memcpy(big.data() + o, r.key, r.klen);
-            memcpy(big.data() + o + r.klen, r.val, r.vlen);
-            sink(big.data(), need);
+            if (final_stream) ++emitted_;
+            sink(r.raw, need);
         } else {
             if (used + need > kStagingBytes) flush();  // blocks always hold whole records
-            uint8_t* d = staging_[cur].data() + used;
-            size_t o = vint_encode(d, r.klen);
-            o += vint_encode(d + o, r.vlen);
-            memcpy(d + o, r.key, r.klen);
-            memcpy(d + o + r.klen, r.val, r.vlen);
+            memcpy(staging_[cur].data() + used, r.raw, need);
             used += need;
+            ++pending;
         }
-        if (final_stream) ++emitted_;  // spill passes of the hybrid merge are not deliveries
         heap->advance();
     }
     if (used + 2 > kStagingBytes) flush();

@@ -169,6 +169,9 @@ private:
 struct Record {
     const uint8_t* key = nullptr; int klen = 0;
     const uint8_t* val = nullptr; int vlen = 0;
+    // the record as it lies in its source: VInt(klen) VInt(vlen) key value, `size` bytes from `raw` (the merged stream
+    // carries exactly these bytes, so emitting a record is one copy)
+    const uint8_t* raw = nullptr; size_t size = 0;
 };
 
 // Iterates the records of one source; a record that straddles two blocks is joined in a carry buffer.
