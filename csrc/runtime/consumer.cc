@@ -731,9 +731,9 @@ void Consumer::merging_phase(MergeHeap* heap, const std::function<void(const uin
     size_t used = 0;
     uint64_t pending = 0;   // records in the open block: the shared counter moves once per block, not once per record
     auto flush = [&] {
-        if (final_stream && pending) emitted_ += pending;  // spill passes of the hybrid merge are not deliveries
-        pending = 0;
         if (used) sink(staging_[cur].data(), used);
+        if (final_stream && pending) emitted_ += pending;  // counted once delivered; spill passes of the hybrid merge are not deliveries
+        pending = 0;
         cur ^= 1;
         used = 0;
         if (stop_) throw UdaError("stopped while merging");
@@ -743,8 +743,8 @@ void Consumer::merging_phase(MergeHeap* heap, const std::function<void(const uin
         const size_t need = r.size;   // the record as it lies in its source: header + key + value, one copy
         if (need > kStagingBytes) {   // a single record larger than a block travels alone, straight from where it lies
             flush();
-            if (final_stream) ++emitted_;
             sink(r.raw, need);
+            if (final_stream) ++emitted_;
         } else {
             if (used + need > kStagingBytes) flush();  // blocks always hold whole records
             memcpy(staging_[cur].data() + used, r.raw, need);
