@@ -216,11 +216,8 @@ snappy_uncompress_fn load_snappy() {
     return fn;
 }
 
-lzo_decompress_fn load_lzo(const HostCallbacks* host) {
-    static lzo_decompress_fn fn = nullptr;
-    static bool tried = false;
-    if (tried) return fn;
-    tried = true;
+lzo_decompress_fn resolve_lzo(const HostCallbacks* host) {
+    lzo_decompress_fn fn = nullptr;
     void* h = nullptr;
     for (const char* name : {"liblzo2.so.2", "liblzo2.so"}) if ((h = dlopen(name, RTLD_LAZY))) break;
     if (!h) return nullptr;
@@ -234,6 +231,12 @@ lzo_decompress_fn load_lzo(const HostCallbacks* host) {
     }
     fn = (lzo_decompress_fn)dlsym(h, sym.c_str());
     if (!fn) fn = (lzo_decompress_fn)dlsym(h, "lzo1x_decompress_safe");
+    return fn;
+}
+// resolved once per process by whichever reduce task decompresses first (several merge / decompress threads may race here:
+// the initialisation of a function-local static is the synchronisation)
+lzo_decompress_fn load_lzo(const HostCallbacks* host) {
+    static const lzo_decompress_fn fn = resolve_lzo(host);
     return fn;
 }
 }  // namespace
@@ -389,8 +392,45 @@ bool FetchSource::next_block(const uint8_t** data, size_t* len) {
     return true;
 }
 
-DecompressingSource::DecompressingSource(std::unique_ptr<ByteSource> inner, Codec codec, long long raw_total, const HostCallbacks* host)
-    : inner_(std::move(inner)), codec_(codec), raw_left_(raw_total), host_(host) {}
+DecompressWorker::DecompressWorker() {
+    th_ = std::thread([this] {
+        for (;;) {
+            std::function<void()> job;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return stop_ || !q_.empty(); });
+                if (q_.empty()) return;   // stop_ and nothing left
+                job = std::move(q_.front());
+                q_.pop_front();
+            }
+            job();   // jobs catch their own errors and park them in their source
+        }
+    });
+}
+DecompressWorker::~DecompressWorker() {
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        stop_ = true;
+    }
+    cv_.notify_all();
+    if (th_.joinable()) th_.join();
+}
+void DecompressWorker::submit(std::function<void()> job) {
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        q_.push_back(std::move(job));
+    }
+    cv_.notify_one();
+}
+
+DecompressingSource::DecompressingSource(std::unique_ptr<ByteSource> inner, Codec codec, long long raw_total, const HostCallbacks* host,
+                                         DecompressWorker* worker)
+    : inner_(std::move(inner)), codec_(codec), raw_left_(raw_total), host_(host), worker_(worker) {}
+
+DecompressingSource::~DecompressingSource() {
+    std::unique_lock<std::mutex> lk(mu_);
+    cv_.wait(lk, [&] { return state_[0] != PENDING && state_[1] != PENDING; });   // a job still holds `this`
+}
 
 bool DecompressingSource::read_exact(uint8_t* dst, size_t n) {
     while (n) {
@@ -402,7 +442,7 @@ bool DecompressingSource::read_exact(uint8_t* dst, size_t n) {
     return true;
 }
 
-bool DecompressingSource::next_block(const uint8_t** data, size_t* len) {
+bool DecompressingSource::decode_into(std::vector<uint8_t>* plain) {
     uint8_t hdr[8];
     if (!read_exact(hdr, 8)) return false;  // clean end (or only the trailing IFile checksum was left)
     const uint32_t raw = (uint32_t)hdr[0] << 24 | (uint32_t)hdr[1] << 16 | (uint32_t)hdr[2] << 8 | hdr[3];
@@ -411,10 +451,55 @@ bool DecompressingSource::next_block(const uint8_t** data, size_t* len) {
     if (raw > (1u << 30) || comp > (1u << 30)) throw UdaError("corrupt compressed block header");
     comp_.resize(comp);
     if (!read_exact(comp_.data(), comp)) throw UdaError("compressed block is truncated");
-    plain_.resize(raw);
-    if (!codec_decompress(codec_, comp_.data(), comp, plain_.data(), raw, host_)) throw UdaError("decompression failed");
-    *data = plain_.data();
-    *len = raw;
+    plain->resize(raw);
+    if (!codec_decompress(codec_, comp_.data(), comp, plain->data(), raw, host_)) throw UdaError("decompression failed");
+    return true;
+}
+
+void DecompressingSource::schedule(int slot) {
+    state_[slot] = PENDING;
+    worker_->submit([this, slot] {
+        SlotState result = READY;
+        std::string err;
+        try {
+            if (!decode_into(&ahead_[slot])) result = END;
+        } catch (const UdaError& e) {
+            result = ERROR;
+            err = e.info();
+        } catch (const std::exception& e) {
+            result = ERROR;
+            err = e.what();
+        }
+        std::lock_guard<std::mutex> lk(mu_);
+        if (result == ERROR) error_ = err;
+        state_[slot] = result;
+        cv_.notify_all();   // under the lock: the destructor may free this object as soon as it sees no PENDING slot
+    });
+}
+
+bool DecompressingSource::next_block(const uint8_t** data, size_t* len) {
+    if (!worker_) {
+        if (!decode_into(&plain_)) return false;
+        *data = plain_.data();
+        *len = plain_.size();
+        return true;
+    }
+    std::unique_lock<std::mutex> lk(mu_);
+    if (!started_) {
+        started_ = true;
+        schedule(0);
+    }
+    const int s = next_;
+    cv_.wait(lk, [&] { return state_[s] != PENDING; });
+    if (state_[s] == ERROR) throw UdaError(error_);
+    if (state_[s] == END || state_[s] == EMPTY) return false;
+    // the block the caller held until now (the other slot) is free again: decode the one after this into it
+    state_[s ^ 1] = EMPTY;
+    schedule(s ^ 1);
+    state_[s] = EMPTY;      // READY consumed; the buffer stays untouched until the caller comes back (only s ^ 1 is being written)
+    next_ = s ^ 1;
+    *data = ahead_[s].data();
+    *len = ahead_[s].size();
     return true;
 }
 
@@ -657,6 +742,8 @@ void Consumer::on_init(const HadoopCmd& cmd) {
     initialised_ = true;
     if (opt_.merge_approach == 3)
         warm_thread_ = spawn_guarded("device-warm-up", nullptr, nullptr, [] { DeviceMerge::instance().warm_up(); });
+    // mapred.uda.decompress.ahead=false decodes every block inside the merge thread instead (the A/B switch of the benchmark)
+    if (codec_ != Codec::NONE && conf_get(host_, "mapred.uda.decompress.ahead", "true") != "false") decomp_ = std::make_unique<DecompressWorker>();
     merge_thread_ = std::thread([this] { merge_thread_main(); });
 }
 
@@ -690,7 +777,7 @@ std::unique_ptr<ByteSource> Consumer::make_source(const FetchOrder& o) {
     auto fs = std::make_unique<FetchSource>(client_.get(), pool_.get(), o.host, r, plan_.buffer_size);
     fs->start();
     if (codec_ == Codec::NONE) return fs;
-    return std::make_unique<DecompressingSource>(std::move(fs), codec_, -1, host_);
+    return std::make_unique<DecompressingSource>(std::move(fs), codec_, -1, host_, decomp_.get());
 }
 
 void Consumer::fetching_phase(MergeHeap* heap, int count, int* progress) {
@@ -1022,6 +1109,7 @@ void Consumer::exit_msg() {
     if (client_) client_->stop();  // fails in-flight fetches so that a blocked merge thread wakes up
     if (merge_thread_.joinable()) merge_thread_.join();
     if (warm_thread_.joinable()) warm_thread_.join();
+    decomp_.reset();   // every source is gone with the merge thread: nothing is queued any more
     pool_.reset();
     client_.reset();
     log_close();

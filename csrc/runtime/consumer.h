@@ -19,6 +19,7 @@
 // decompressing adaptor) under a record reader that joins straddling records in a carry buffer.
 #pragma once
 #include <atomic>
+#include <deque>
 #include <condition_variable>
 #include <functional>
 #include <list>
@@ -131,9 +132,28 @@ private:
 };
 
 // Hadoop block-compressed stream -> plain bytes: [u32 BE rawLen][u32 BE compLen][compLen bytes]...
+// The reduce task's decompress thread (reference: DecompressorWrapper's thread, src/Merger/DecompressorWrapper.cc:168-197):
+// every compressed segment keeps its next block being decoded here while the merge consumes the current one.
+class DecompressWorker {
+public:
+    DecompressWorker();
+    ~DecompressWorker();   // finishes the queued jobs, then joins
+    void submit(std::function<void()> job);
+
+private:
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::deque<std::function<void()>> q_;
+    bool stop_ = false;
+    std::thread th_;
+};
+
 class DecompressingSource : public ByteSource {
 public:
-    DecompressingSource(std::unique_ptr<ByteSource> inner, Codec codec, long long raw_total, const HostCallbacks* host);
+    // worker == nullptr: every block is decoded inside next_block() on the caller's thread
+    DecompressingSource(std::unique_ptr<ByteSource> inner, Codec codec, long long raw_total, const HostCallbacks* host,
+                        DecompressWorker* worker = nullptr);
+    ~DecompressingSource() override;
     bool next_block(const uint8_t** data, size_t* len) override;
     long long size_hint() const override {   // rawLength of the index record, learnt by the inner fetch from the first ack
         auto* fs = dynamic_cast<const FetchSource*>(inner_.get());
@@ -149,6 +169,18 @@ private:
     const uint8_t* cur_ = nullptr;
     size_t cur_len_ = 0;
     std::vector<uint8_t> comp_, plain_;
+    // decode-ahead (worker_ != nullptr): two plain buffers; the inner source, comp_, cur_ are touched by one job at a time
+    enum SlotState { EMPTY, PENDING, READY, END, ERROR };
+    bool decode_into(std::vector<uint8_t>* plain);   // one block: false at the clean end, throws on corruption
+    void schedule(int slot);                         // caller holds mu_
+    DecompressWorker* worker_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::vector<uint8_t> ahead_[2];
+    SlotState state_[2] = {EMPTY, EMPTY};
+    std::string error_;
+    int next_ = 0;          // slot the consumer takes next
+    bool started_ = false;
 };
 
 // Spill file written by an LPQ merge (plain merged-stream framing, EOF marker at the end)
@@ -270,6 +302,7 @@ private:
     Codec codec_ = Codec::NONE;
     MemoryPlan plan_;
     std::unique_ptr<InputClient> client_;
+    std::unique_ptr<DecompressWorker> decomp_;   // only for compressed map outputs; outlives every source (reset after the merge thread)
     std::unique_ptr<BufferPool> pool_;
     std::mutex mu_;
     std::condition_variable cv_;

@@ -35,6 +35,11 @@ if [ "$kind" = "thread" ] && [ "${UDA_SAN_PYTESTS:-1}" = "1" ]; then
         TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 log_path=$tmp/tsan" \
         python -m pytest tests/test_runtime_cpu.py tests/test_device_merge_mock_cpu.py -x -q -p no:cacheprovider -k "plumbing or queues or thread_wrapper or mock" > "$log" 2>&1 || true
     tail -1 "$log"
+    # the native benchmark as a stress: several reducers in one process, compressed map outputs (decompress threads), hybrid merge
+    for args in "--tcp --maps 8 --reducers 3 --records 600000 --codec lzo" "--tcp --maps 8 --reducers 3 --records 600000 --codec snappy --approach 2" \
+                "--maps 16 --records 600000 --approach 2"; do
+        TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 log_path=$tmp/tsan" "build/thread/cpu_merge_bench" x $args --steps 2 --warmup 0 --check | tail -1
+    done
     if ls "$tmp"/tsan.* > /dev/null 2>&1; then
         grep -h -A12 "WARNING: ThreadSanitizer" "$tmp"/tsan.* | head -80
         grep -h "SUMMARY: ThreadSanitizer" "$tmp"/tsan.* | sort | uniq -c

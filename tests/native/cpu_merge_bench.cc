@@ -8,6 +8,8 @@
 //     (approach 3 = the device merge: needs a GPU, or UDA_KERNELS_LIB pointing at the host-only mock)
 //   baseline/_ref/bin/ref_merger           --maps 8 --records 20000000 --steps 3 --warmup 1 [--check]
 //
+//   ... --codec snappy|lzo      the map outputs are block-compressed (256 KiB blocks); the reducer decompresses them
+//
 //   build/bin/cpu_merge_bench <libuda.so> --tcp --maps 4 --reducers 2 --records 10000000    (BASELINE config 1, native)
 //     the map outputs are written as Hadoop file.out files, a provider role of this process serves them over TCP
 //     loop-back (index look-up, chunk pool, disk reader, fetch protocol with credits) and --reducers consumer roles
@@ -30,12 +32,31 @@
 #include <vector>
 
 #include "../../include/uda_rt_api.h"
+#include "../../csrc/runtime/consumer.h"
 #include "../../csrc/runtime/transport.h"
 
 namespace {
 
 constexpr int KEY = 10, VAL = 90, REC = 102;
-std::vector<std::vector<char>> g_maps;
+std::vector<std::vector<char>> g_maps;       // what the "provider" holds per segment: plain, or codec blocks when --codec is given
+std::vector<long long> g_plain_len;          // plain length of every segment (rawLength of its index record)
+std::string g_codec;                         // "", "snappy" or "lzo"
+constexpr size_t kCodecBlock = 256 * 1024;   // io.compression.codec.{snappy,lzo}.buffersize default
+
+// plain segment -> Hadoop block framing [u32 BE rawLen][u32 BE compLen][bytes]... with this runtime's own compressors
+void compress_segment(std::vector<char>* seg) {
+    std::vector<char> out;
+    std::vector<uint8_t> blk;
+    for (size_t off = 0; off < seg->size(); off += kCodecBlock) {
+        const size_t n = std::min(kCodecBlock, seg->size() - off);
+        if (g_codec == "snappy") uda::snappy_compress((const uint8_t*)seg->data() + off, n, &blk);
+        else uda::lzo1x_compress((const uint8_t*)seg->data() + off, n, &blk);
+        const uint32_t hdr[2] = {__builtin_bswap32((uint32_t)n), __builtin_bswap32((uint32_t)blk.size())};
+        out.insert(out.end(), (const char*)hdr, (const char*)hdr + 8);
+        out.insert(out.end(), (const char*)blk.data(), (const char*)blk.data() + blk.size());
+    }
+    seg->swap(out);
+}
 
 inline uint64_t splitmix(uint64_t& s) {
     uint64_t z = (s += 0x9E3779B97F4A7C15ull);
@@ -133,7 +154,7 @@ private:
             memcpy(j.dest, seg.data() + j.req.map_offset, (size_t)n);
             if (g_verbose) { copy_busy_ += now_s() - tc; ++copies_; }
             uda::FetchAck ack;
-            ack.raw_length = total;
+            ack.raw_length = g_plain_len[(size_t)m];
             ack.part_length = total;
             ack.sent = n;
             ack.file_offset = 0;
@@ -197,7 +218,11 @@ void on_failure(void* user) {
     g_sink.failed = true;
     g_sink.cv.notify_all();
 }
-int on_conf(void*, const char*, const char*, char*, int) { return 0; }
+bool g_inline_decompress = false;   // --inline-decompress: no decompress thread (A/B of the decode-ahead)
+int on_conf(void*, const char* name, const char*, char* out, int cap) {
+    if (g_inline_decompress && strcmp(name, "mapred.uda.decompress.ahead") == 0) { snprintf(out, (size_t)cap, "false"); return 1; }
+    return 0;
+}
 
 struct StepResult { double seconds; long long bytes, blocks, records; int check_ok; };
 
@@ -220,7 +245,7 @@ bool write_mofs(const std::string& dir, int maps) {
             const std::vector<char>& seg = g_maps[(size_t)(m * g_reducers + r)];
             const char crc[4] = {0, 0, 0, 0};
             if (fwrite(seg.data(), 1, seg.size(), f) != seg.size() || fwrite(crc, 1, 4, f) != 4) { fclose(f); return false; }
-            g_mof_index[(size_t)m][(size_t)r] = MofIndex{pos, (long long)seg.size(), (long long)seg.size() + 4};
+            g_mof_index[(size_t)m][(size_t)r] = MofIndex{pos, g_plain_len[(size_t)(m * g_reducers + r)], (long long)seg.size() + 4};
             pos += (long long)seg.size() + 4;
         }
         fclose(f);
@@ -252,7 +277,7 @@ bool run_job(int maps, int approach, bool check, int port, StepResult* out) {
     bool ok = true;
     for (int r = 0; r < R && ok; ++r) {
         long long expect = 2;
-        for (int m = 0; m < maps; ++m) expect += (long long)g_maps[(size_t)(m * R + r)].size() - 2;
+        for (int m = 0; m < maps; ++m) expect += g_plain_len[(size_t)(m * R + r)] - 2;
         g_sinks[(size_t)r].reset(check, expect);
         cb.user = &g_sinks[(size_t)r];
         uda_role_t h = uda_rt_start(1, (int)(sizeof(argv) / sizeof(argv[0])), argv, 0 /* logging off */, 0, &cb);
@@ -260,8 +285,10 @@ bool run_job(int maps, int approach, bool check, int port, StepResult* out) {
         roles.push_back(h);
         char init[512];
         const long long shuffle_mem = (long long)maps * 2 * (1 << 20) + (64LL << 20);
-        snprintf(init, sizeof(init), "13:7:%d:job_ref_0001:attempt_ref_0001_r_%06d_0:0:%d:%d:org.apache.hadoop.io.ByteWritable:null:0:%lld:1:/tmp",
-                 maps, r, 1 << 20, 16 << 10, shuffle_mem);
+        const char* codec_class = g_codec == "snappy" ? "org.apache.hadoop.io.compress.SnappyCodec"
+                                  : g_codec == "lzo" ? "com.hadoop.compression.lzo.LzoCodec" : "null";
+        snprintf(init, sizeof(init), "13:7:%d:job_ref_0001:attempt_ref_0001_r_%06d_0:0:%d:%d:org.apache.hadoop.io.ByteWritable:%s:%d:%lld:1:/tmp",
+                 maps, r, 1 << 20, 16 << 10, codec_class, g_codec.empty() ? 0 : (int)kCodecBlock, shuffle_mem);
         ok = uda_rt_do_command(h, init) == 0;
         for (int m = 0; ok && m < maps; ++m) {
             char fetch[256];
@@ -318,19 +345,29 @@ int main(int argc, char** argv) {
         else if (a == "--budget-s") budget_s = atof(val());
         else if (a == "--check") check = true;
         else if (a == "--tcp") tcp = true;
+        else if (a == "--codec") g_codec = val();
+        else if (a == "--inline-decompress") g_inline_decompress = true;
     }
-    if (maps < 1 || records < 1 || g_reducers < 1 || (approach < 1 || approach > 3)) { fprintf(stderr, "bad arguments\n"); return 2; }
+    if (maps < 1 || records < 1 || g_reducers < 1 || (approach < 1 || approach > 3) || (!g_codec.empty() && g_codec != "snappy" && g_codec != "lzo")) {
+        fprintf(stderr, "bad arguments\n");
+        return 2;
+    }
     g_verbose = getenv("UDA_BENCH_VERBOSE") != nullptr;
     const double t_begin = now_s();
     const int R = g_reducers, nseg = maps * R;
     g_maps.resize((size_t)nseg);
+    g_plain_len.assign((size_t)nseg, 0);
     g_sinks.resize((size_t)R);
     {
         // `records` is the total of the job (what bench.py calls records per GPU for one reducer), spread over maps x reducers
         std::vector<std::thread> th;
         for (int sgi = 0; sgi < nseg; ++sgi) {
             const long long n = records / nseg + (sgi < records % nseg ? 1 : 0);
-            th.emplace_back([=] { build_map(sgi, n, seed); });
+            th.emplace_back([=] {
+                build_map(sgi, n, seed);
+                g_plain_len[(size_t)sgi] = (long long)g_maps[(size_t)sgi].size();
+                if (!g_codec.empty()) compress_segment(&g_maps[(size_t)sgi]);
+            });
             if (th.size() == 16) { for (auto& t : th) t.join(); th.clear(); }
         }
         for (auto& t : th) t.join();

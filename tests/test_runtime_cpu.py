@@ -635,6 +635,35 @@ def test_lzo1x_round_trip(L, n):
             assert m < n // 4
 
 
+@pytest.mark.parametrize("ahead", ["true", "false"])
+def test_corrupt_compressed_block_fails_the_task(built, tmp_path, L, ahead, monkeypatch):
+    """A compressed block that does not decode (here: its Snappy length prefix is wrong) fails the fetch of that map output
+    and through it the task -- with the decompress thread (the error is parked in the source and rethrown on the merge
+    thread) and with inline decoding alike."""
+    L.uda_rt_snappy_compress.restype = C.c_longlong
+
+    def comp(b):
+        out = _buf(len(b) + len(b) // 6 + 64)
+        n = L.uda_rt_snappy_compress(bytes(b), C.c_longlong(len(b)), out, C.c_longlong(len(out)))
+        return out.raw[:n]
+
+    mofs, truth = _make_mofs(str(tmp_path), 3, 1, 400, seed=8, compress=comp)
+    path, idx = mofs["attempt_m_000001_0"]
+    data = bytearray(open(path, "rb").read())
+    second_block = idx[0].start_offset + 8 + struct.unpack(">I", data[idx[0].start_offset + 4:idx[0].start_offset + 8])[0]
+    data[second_block + 8] ^= 0x7F                      # first byte of the second block's Snappy stream: the varint length
+    open(path, "wb").write(bytes(data))
+    real = bridge.NativeRole.__init__
+
+    def init_with_conf(self, is_net_merger, argv, *a, **kw):
+        if is_net_merger:
+            kw["conf"] = {**(kw.get("conf") or {}), "mapred.uda.decompress.ahead": ahead}
+        real(self, is_net_merger, argv, *a, **kw)
+
+    monkeypatch.setattr(bridge.NativeRole, "__init__", init_with_conf)
+    _run_job(str(tmp_path), 3, 1, 0, prebuilt=(mofs, truth), codec="org.apache.hadoop.io.compress.SnappyCodec", expect_failure=True)
+
+
 def test_plumbing_lzo_compressed_segments(built, tmp_path, L):
     """LZO map outputs through provider -> consumer without liblzo2 on the box: the built-in LZO1X decoder serves."""
     L.uda_rt_lzo1x_compress.restype = C.c_longlong

@@ -35,6 +35,8 @@ _KEYS = {
     "log_to_unique_file": ("mapred.uda.log.to.unique.file", bool),
     "developer_mode": ("mapred.rdma.developer.mode", bool),
     "blocked_threads_per_disk": ("mapred.uda.provider.blocked.threads.per.disk", int),
+    "provider_reader": ("mapred.uda.provider.reader", str),
+    "decompress_ahead": ("mapred.uda.decompress.ahead", bool),
     "local_dirs": ("mapred.local.dir", list),
     "map_output_key_class": ("mapred.mapoutput.key.class", str),
     "child_java_opts": ("mapred.child.java.opts", str),
@@ -90,6 +92,8 @@ class UdaConfig:
     log_to_unique_file: bool = False
     developer_mode: bool = False
     blocked_threads_per_disk: int = 1
+    provider_reader: str = "aio"            # aio | blocked (csrc/runtime/reader.cc)
+    decompress_ahead: bool = True           # compressed map outputs: decode the next block of every segment on the reduce task's decompress thread
     local_dirs: List[str] = field(default_factory=lambda: ["/tmp"])
     map_output_key_class: str = "org.apache.hadoop.io.Text"
     child_java_opts: str = "-Xmx200m"
