@@ -119,7 +119,10 @@ JNIEnv g_env;
 
 // ------------------------------------------------------------------------------------------ transport
 struct CopyJob { client_part_req_t* req; char* buff; int len; };
+bool g_verbose = false;   // UDA_BENCH_VERBOSE=1: how busy the stand-in transport was (it must not be what limits the reducer)
 struct CopyThread {
+    double busy_s = 0;
+    long long copies = 0;
     std::mutex mu;
     std::condition_variable cv;
     std::deque<CopyJob> q;
@@ -145,7 +148,9 @@ struct CopyThread {
             long long n = total - off;
             if (n > job.len) n = job.len;
             if (n < 0) n = 0;
+            const double tc = g_verbose ? now_s() : 0;
             memcpy(job.buff, seg.bytes.data() + off, (size_t)n);   // the "RDMA write" into the registered buffer
+            if (g_verbose) { busy_s += now_s() - tc; ++copies; }
             // ack text the provider sends: rawLength:partLength:sent:mofOffset:mofPath:  (parsed by update_fetch_req)
             snprintf(req->recvd_msg, sizeof(req->recvd_msg), "%lld:%lld:%lld:%lld:%s:", total, total, n, 0LL, "mem");
             owner->comp_fetch_req(req);
@@ -319,6 +324,9 @@ StepResult run_reduce_task(int maps, bool check) {
     r.blocks = g_sink.blocks;
     r.records = g_sink.records;
     r.check_ok = g_sink.check_ok ? 1 : 0;
+    if (g_verbose)
+        fprintf(stderr, "copy thread (stand-in transport): %.3f s busy in %lld copies during a %.3f s reduce task\n", g_copy.busy_s, g_copy.copies,
+                r.seconds);
     reduce_exit_msg_handler();   // joins the merge thread, frees the pools (outside the timed span, like the JVM's exit)
     return r;
 }
@@ -356,6 +364,7 @@ bool run_in_child(int maps, bool check, StepResult* out) {
 }  // namespace
 
 int main(int argc, char** argv) {
+    g_verbose = getenv("UDA_BENCH_VERBOSE") != NULL;
     int maps = 8, steps = 5, warmup = 1;
     long long records = 1000000;
     uint64_t seed = 1234;
