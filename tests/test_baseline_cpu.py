@@ -52,3 +52,30 @@ def test_bench_reference_arm_prints_the_contract_line(built):
         return
     assert d["impl"] == "reference" and d["value"] > 0 and d["steps"] == 2 and d["validated"] is True and d["gpu_launches"] == 0
     assert d["config"]["runs_per_reducer"] == 4 and "unmodified" in d["config"]["reference_code"]
+
+
+def test_reference_arm_sources_are_byte_identical_to_the_reference():
+    """The reference arm compiles the reference's own files: every copied file still hashes to its manifest entry, and to the
+    file in the reference tree when that tree is mounted."""
+    import hashlib
+    import os
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    man = root / "baseline" / "_ref" / "MANIFEST.txt"
+    if not man.exists():
+        import pytest
+        pytest.skip("reference arm not built on this machine")
+    ref = Path(os.environ.get("UDA_REFERENCE_DIR", "/root/reference"))
+    entries = [l.split(None, 1) for l in man.read_text().splitlines() if l.strip()]
+    assert len(entries) >= 12
+    checked_against_tree = 0
+    for digest, rel in entries:
+        rel = rel.strip()
+        copy = root / "baseline" / "_ref" / rel
+        assert hashlib.sha256(copy.read_bytes()).hexdigest() == digest, rel
+        orig = ref / rel
+        if orig.exists():
+            assert hashlib.sha256(orig.read_bytes()).hexdigest() == digest, rel
+            checked_against_tree += 1
+    assert checked_against_tree == len(entries) or not ref.exists()
+    assert any(rel.strip().endswith("Merger/StreamRW.cc") for _, rel in entries) and any("MergeQueue.h" in rel for _, rel in entries)
