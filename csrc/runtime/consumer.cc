@@ -611,15 +611,19 @@ void MergeHeap::sift_up(size_t i) {
     }
 }
 void MergeHeap::sift_down(size_t i) {
+    // the sinking node travels in a local: children move up into the hole, one store per level instead of a swap
     const size_t n = heap_.size();
+    Node x = std::move(heap_[i]);
     for (;;) {
-        size_t l = 2 * i + 1, r = l + 1, m = i;
-        if (l < n && less(heap_[l], heap_[m])) m = l;
-        if (r < n && less(heap_[r], heap_[m])) m = r;
-        if (m == i) return;
-        std::swap(heap_[i], heap_[m]);
-        i = m;
+        const size_t l = 2 * i + 1;
+        if (l >= n) break;
+        const size_t r = l + 1;
+        const size_t c = (r < n && less(heap_[r], heap_[l])) ? r : l;
+        if (!less(heap_[c], x)) break;
+        heap_[i] = std::move(heap_[c]);
+        i = c;
     }
+    heap_[i] = std::move(x);
 }
 void MergeHeap::insert(std::unique_ptr<Segment> s) {
     if (!s->next()) return;  // empty partition: nothing to merge, buffers go back to the pool
